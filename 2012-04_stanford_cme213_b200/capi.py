@@ -1,0 +1,156 @@
+"""ctypes binding of libcme213_b200.so (the C ABI declared in include/cme213_b200.h).
+
+This is the only way Python code in this repository reaches the kernels.  There is no fallback:
+if the shared library is missing or a call fails, an exception is raised.
+"""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libcme213_b200.so")
+
+OK = 0
+ERR_INVALID, ERR_CUDA, ERR_ALLOC, ERR_UNSUPPORTED = -1, -2, -3, -4
+CSR_AUTO, CSR_SCALAR, CSR_VECTOR, CSR_STREAM = 0, 1, 2, 3
+
+
+def csr_vector(lanes):
+    """kernel selector for CSR-vector with `lanes` (2..32, power of two) lanes per row."""
+    return CSR_VECTOR | (int(lanes) << 8)
+
+
+class Cme213Error(RuntimeError):
+    def __init__(self, code, text):
+        super().__init__("cme213 error %d: %s" % (code, text))
+        self.code = code
+
+
+_p, _i, _i64, _u32, _f = C.c_void_p, C.c_int, C.c_int64, C.c_uint32, C.c_float
+_pi, _pi64, _pf = C.POINTER(C.c_int), C.POINTER(C.c_int64), C.POINTER(C.c_float)
+
+# name -> (restype, argtypes).  Every symbol include/cme213_b200.h declares is listed here;
+# tests/test_abi.py checks the two stay in sync.
+PROTOTYPES = {
+    "cme213_ctx_create": (_i, [_i, C.POINTER(_p)]),
+    "cme213_ctx_destroy": (_i, [_p]),
+    "cme213_ctx_device": (_i, [_p]),
+    "cme213_ctx_sm_count": (_i, [_p]),
+    "cme213_ctx_launch_count": (_i64, [_p]),
+    "cme213_last_error": (C.c_char_p, []),
+    "cme213_version": (_i, []),
+    "cme213_transpose_b32": (_i, [_p, _p, _p, _i64, _i64, _i64, _i64, _p]),
+    "cme213_transpose_b64": (_i, [_p, _p, _p, _i64, _i64, _i64, _i64, _p]),
+    "cme213_exclusive_scan_u32": (_i, [_p, _p, _p, _i64, _p]),
+    "cme213_flag_words": (_i64, [_i64]),
+    "cme213_segment_flags_from_offsets": (_i, [_p, _p, _i, _i64, _p, _p]),
+    "cme213_segscan_inclusive_f32": (_i, [_p, _p, _p, _p, _i64, _p]),
+    "cme213_segscan_inclusive_f64": (_i, [_p, _p, _p, _p, _i64, _p]),
+    "cme213_segscan_exclusive_f32": (_i, [_p, _p, _p, _p, _i64, _p]),
+    "cme213_mul_gather_segscan_f32": (_i, [_p, _p, _p, _p, _p, _p, _i64, _p]),
+    "cme213_mul_gather_segscan_f64": (_i, [_p, _p, _p, _p, _p, _p, _i64, _p]),
+    "cme213_spmv_csr_f32": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _i, _p]),
+    "cme213_spmv_csr_f64": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _i, _p]),
+    "cme213_pagerank_propagate": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _p]),
+    "cme213_spmv_ell_f32": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _p, _p]),
+    "cme213_spmv_ell_f64": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _p, _p]),
+    "cme213_spmv_coo_accumulate_f32": (_i, [_p, _i64, _p, _p, _p, _p, _p, _p]),
+    "cme213_spmv_coo_accumulate_f64": (_i, [_p, _i64, _p, _p, _p, _p, _p, _p]),
+    "cme213_spmv_hyb_f32": (_i, [_p, _i64, _i64, _i, _p, _p, _i64, _p, _p, _p, _p, _p, _p]),
+    "cme213_hyb_pick_k": (_i, [_p, _i64, _p, _pi, _pi, _p]),
+    "cme213_ell_pitch": (_i64, [_i64]),
+    "cme213_csr_to_ell_f32": (_i, [_p, _i64, _i64, _p, _p, _p, _i, _i64, _p, _p, _p]),
+    "cme213_csr_to_ell_f64": (_i, [_p, _i64, _i64, _p, _p, _p, _i, _i64, _p, _p, _p]),
+    "cme213_csr_to_coo_tail_f32": (_i, [_p, _i64, _p, _p, _p, _i, _pi64, _p, _p, _p, _p]),
+    "cme213_gen_laplace2d_f32": (_i, [_p, _i, _i, _p, _p, _p, _pi64, _p]),
+    "cme213_gen_laplace3d_f64": (_i, [_p, _i, _i, _i, _i64, _i64, _p, _p, _p, _pi64, _p]),
+    "cme213_gen_powerlaw_lengths": (_i, [_p, _i64, _i, _u32, _u32, _i, _u32, _p, _pi64, _p]),
+    "cme213_gen_random_csr_fill_f32": (_i, [_p, _i64, _i64, _p, _i64, _u32, _p, _p, _p]),
+    "cme213_gen_pagerank_graph": (_i, [_p, _i, _i, _u32, _p, _p, _p, _p, _pi64, _p]),
+    "cme213_fill_uniform_f32": (_i, [_p, _p, _i64, _u32, _p]),
+    "cme213_fill_uniform_f64": (_i, [_p, _p, _i64, _u32, _p]),
+    "cme213_fill_hash_u32": (_i, [_p, _p, _i64, _u32, _u32, _p]),
+    "cme213_fill_random_flags": (_i, [_p, _p, _i64, _u32, _u32, _p]),
+    "device_graph_iterate": (None, [_p, _p, _p, _p, _p, _i, _i, _i]),
+    "cme213_pagerank_iterate_host": (_i, [_p, _p, _p, _p, _p, _i, _i, _pf]),
+    "cme213_csr_iterate_host_f64": (_i, [_i64, _i64, _p, _p, _p, _p, _p, _i, _pf]),
+    "cme213_csr_iterate_host_f32": (_i, [_i64, _i64, _p, _p, _p, _p, _p, _i, _pf]),
+    "cme213_fp_iterate_host_f32": (_i, [_i, _i, _i, _i, _p, _p, _p, _p, _p, _pf]),
+    "cme213_fp_iterate_host_f64": (_i, [_i, _i, _i, _i, _p, _p, _p, _p, _p, _pf]),
+    "cme213_exclusive_scan_u32_host": (_i, [_p, _p, _i64]),
+    "cme213_transpose_host_b32": (_i, [_p, _p, _i64, _i64]),
+    "cme213_transpose_host_b64": (_i, [_p, _p, _i64, _i64]),
+}
+
+_lib = None
+
+
+def load():
+    """Loads the shared library (once).  Raises if it has not been built: there is no CPU path."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            "libcme213_b200.so is missing (%s). Build it with `python 2012-04_stanford_cme213_b200/build.py` "
+            "or __graft_entry__.build(); this package has no CPU fallback." % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in PROTOTYPES.items():
+        fn = getattr(lib, name)  # AttributeError here means header and library disagree
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc):
+    if rc != OK:
+        raise Cme213Error(rc, load().cme213_last_error().decode("utf-8", "replace"))
+
+
+def ptr(t):
+    """Device or host address of a torch tensor / numpy array / int / None as c_void_p."""
+    if t is None:
+        return None
+    if isinstance(t, int):
+        return C.c_void_p(t)
+    if hasattr(t, "data_ptr"):
+        return C.c_void_p(t.data_ptr())
+    if hasattr(t, "ctypes"):
+        return C.c_void_p(t.ctypes.data)
+    raise TypeError("cannot take the address of %r" % type(t))
+
+
+class Context:
+    """cme213_ctx wrapper.  `stream` arguments are torch.cuda.Stream objects or None (default stream)."""
+
+    def __init__(self, device=0):
+        self.lib = load()
+        h = C.c_void_p()
+        check(self.lib.cme213_ctx_create(int(device), C.byref(h)))
+        self.h = h
+        self.device = int(device)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.cme213_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def launches(self):
+        return int(self.lib.cme213_ctx_launch_count(self.h))
+
+    @property
+    def sm_count(self):
+        return int(self.lib.cme213_ctx_sm_count(self.h))
+
+    def call(self, name, *args, stream=None):
+        """Calls lib.<name>(ctx, *args, stream) and raises on a non-zero status."""
+        s = None if stream is None else C.c_void_p(stream.cuda_stream if hasattr(stream, "cuda_stream") else int(stream))
+        conv = [ptr(a) if (a is None or hasattr(a, "data_ptr") or hasattr(a, "ctypes")) else a for a in args]
+        check(getattr(self.lib, name)(self.h, *conv, s))

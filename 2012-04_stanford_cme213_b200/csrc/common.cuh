@@ -1,0 +1,86 @@
+// common.cuh -- shared host/device helpers for libcme213_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include "../../include/cme213_b200.h"
+
+#define CME213_API extern "C" __attribute__((visibility("default")))
+
+struct cme213_ctx {
+    int device;
+    int sm_count;
+    void *ws;          // scratch workspace, grown on demand
+    size_t ws_bytes;
+    int64_t launches;  // kernels launched through this context
+};
+
+namespace cme213 {
+
+void set_error(const char *fmt, ...);
+int cuda_fail(cudaError_t e, const char *what);
+// Returns a workspace of at least `bytes` (256-byte aligned), growing it if needed.
+int workspace(cme213_ctx *ctx, size_t bytes, void **out);
+
+struct DeviceGuard {
+    int prev;
+    bool switched;
+    explicit DeviceGuard(int dev) : prev(-1), switched(false) {
+        cudaGetDevice(&prev);
+        if (prev != dev) { cudaSetDevice(dev); switched = true; }
+    }
+    ~DeviceGuard() { if (switched) cudaSetDevice(prev); }
+};
+
+#define CME213_CHECK_CTX(ctx)                                             \
+    do {                                                                  \
+        if (!(ctx)) { cme213::set_error("null context"); return CME213_ERR_INVALID; } \
+    } while (0)
+
+#define CME213_CUDA(call)                                                 \
+    do {                                                                  \
+        cudaError_t _e = (call);                                          \
+        if (_e != cudaSuccess) return cme213::cuda_fail(_e, #call);       \
+    } while (0)
+
+// After a kernel launch: count it and surface launch errors.
+#define CME213_LAUNCHED(ctx, name)                                        \
+    do {                                                                  \
+        (ctx)->launches++;                                                \
+        cudaError_t _e = cudaGetLastError();                              \
+        if (_e != cudaSuccess) return cme213::cuda_fail(_e, name);        \
+    } while (0)
+
+static inline int64_t div_up(int64_t a, int64_t b) { return (a + b - 1) / b; }
+static inline bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// ---- device helpers -------------------------------------------------------
+#ifdef __CUDACC__
+// Streaming (read-once) loads: keep L1/L2 for the gathered vector x.
+template <typename V> __device__ __forceinline__ V ld_stream(const V *p) { return __ldcs(p); }
+template <typename V> __device__ __forceinline__ void st_stream(V *p, const V &v) { __stcs(p, v); }
+
+__device__ __forceinline__ uint32_t hash32(uint32_t seed, uint64_t idx) {
+    // counter-based hash (two rounds of a 32-bit finaliser over a 64-bit counter); restated in
+    // numpy by oracle/generators.py so tests can rebuild any generated input bit for bit.
+    uint32_t h = seed ^ 0x9E3779B9u;
+    h ^= (uint32_t)idx;
+    h *= 0x85EBCA6Bu; h ^= h >> 13;
+    h ^= (uint32_t)(idx >> 32) * 0xC2B2AE35u;
+    h *= 0xC2B2AE35u; h ^= h >> 16;
+    h *= 0x27D4EB2Fu; h ^= h >> 15;
+    return h;
+}
+__device__ __forceinline__ float uniform_pm1_f32(uint32_t h) {
+    // 24 random bits -> [0,2) in steps of 2^-23, minus 1: exact in fp32, never returns 0.
+    float v = (float)(h >> 8) * 1.1920928955078125e-07f - 1.0f;
+    return v == 0.0f ? 1.1920928955078125e-07f : v;
+}
+__device__ __forceinline__ double uniform_pm1_f64(uint32_t h) {
+    double v = (double)h * 4.656612873077392578125e-10 - 1.0;  // h * 2^-31 - 1
+    return v == 0.0 ? 4.656612873077392578125e-10 : v;
+}
+#endif
+
+}  // namespace cme213

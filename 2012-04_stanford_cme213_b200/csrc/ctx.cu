@@ -1,0 +1,72 @@
+// ctx.cu -- context, error text, workspace.
+#include "common.cuh"
+#include <string.h>
+#include <stdlib.h>
+
+namespace cme213 {
+static thread_local char g_err[512] = "";
+
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char *what) {
+    set_error("CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
+    return e == cudaErrorMemoryAllocation ? CME213_ERR_ALLOC : CME213_ERR_CUDA;
+}
+
+int workspace(cme213_ctx *ctx, size_t bytes, void **out) {
+    if (bytes > ctx->ws_bytes) {
+        // Growth path: only on first use or when a larger problem arrives.
+        if (ctx->ws) {
+            CME213_CUDA(cudaDeviceSynchronize());
+            CME213_CUDA(cudaFree(ctx->ws));
+            ctx->ws = nullptr;
+            ctx->ws_bytes = 0;
+        }
+        size_t want = (bytes + 0xFFFFF) & ~(size_t)0xFFFFF;  // 1 MiB granules
+        CME213_CUDA(cudaMalloc(&ctx->ws, want));
+        ctx->ws_bytes = want;
+    }
+    *out = ctx->ws;
+    return CME213_OK;
+}
+}  // namespace cme213
+
+CME213_API const char *cme213_last_error(void) { return cme213::g_err; }
+CME213_API int cme213_version(void) { return 100; }
+
+CME213_API int cme213_ctx_create(int device, cme213_ctx **out) {
+    if (!out) { cme213::set_error("null out pointer"); return CME213_ERR_INVALID; }
+    *out = nullptr;
+    int count = 0;
+    CME213_CUDA(cudaGetDeviceCount(&count));
+    if (device < 0 || device >= count) {
+        cme213::set_error("device %d out of range (%d visible)", device, count);
+        return CME213_ERR_INVALID;
+    }
+    cme213::DeviceGuard g(device);
+    cudaDeviceProp prop;
+    CME213_CUDA(cudaGetDeviceProperties(&prop, device));
+    cme213_ctx *c = (cme213_ctx *)calloc(1, sizeof(cme213_ctx));
+    if (!c) { cme213::set_error("host allocation failed"); return CME213_ERR_ALLOC; }
+    c->device = device;
+    c->sm_count = prop.multiProcessorCount;
+    *out = c;
+    return CME213_OK;
+}
+
+CME213_API int cme213_ctx_destroy(cme213_ctx *ctx) {
+    if (!ctx) return CME213_OK;
+    cme213::DeviceGuard g(ctx->device);
+    if (ctx->ws) cudaFree(ctx->ws);
+    free(ctx);
+    return CME213_OK;
+}
+
+CME213_API int cme213_ctx_device(const cme213_ctx *ctx) { return ctx ? ctx->device : -1; }
+CME213_API int cme213_ctx_sm_count(const cme213_ctx *ctx) { return ctx ? ctx->sm_count : -1; }
+CME213_API int64_t cme213_ctx_launch_count(const cme213_ctx *ctx) { return ctx ? ctx->launches : -1; }

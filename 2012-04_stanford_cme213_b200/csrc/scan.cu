@@ -1,0 +1,313 @@
+// scan.cu -- entry points built on the look-back scan: exclusive uint32 scan, (fused) segmented
+// scans of the final project, COO segmented reduction.
+#include "lookback_scan.cuh"
+
+namespace {
+using namespace cme213;
+
+template <typename T> struct V16;
+template <> struct V16<uint32_t> { using type = uint4; };
+template <> struct V16<float> { using type = float4; };
+template <> struct V16<double> { using type = double2; };
+template <int IPV> struct IdxVec;
+template <> struct IdxVec<4> { using type = int4; };
+template <> struct IdxVec<2> { using type = int2; };
+
+struct NoAux {};
+
+// Rounded product, never contracted into an FMA with the additions of the scan: the reference
+// rounds a[i]*x[k[i]] to working precision before summing (fp.cu:139-140, thrust multiplies).
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
+
+template <int IPV>
+__device__ __forceinline__ unsigned head_bits(const uint32_t *bits, int64_t idx) {
+    return (bits[idx >> 5] >> (unsigned)(idx & 31)) & ((1u << IPV) - 1u);
+}
+
+// ---- plain load / store ------------------------------------------------------------------------
+template <typename T_, bool SEG_, bool INCLUSIVE>
+struct PlainPolicy {
+    using T = T_;
+    using Aux = NoAux;
+    static constexpr int IPV = 16 / sizeof(T);
+    static constexpr bool SEG = SEG_;
+    const T *in;
+    T *out;
+    const uint32_t *flag_bits;
+
+    __device__ void load(int64_t idx, int64_t n, bool fast, T (&v)[IPV], unsigned &head, Aux &) const {
+        head = 0;
+        if (fast) {
+            typename V16<T>::type x = ld_stream(reinterpret_cast<const typename V16<T>::type *>(in + idx));
+            const T *e = reinterpret_cast<const T *>(&x);
+#pragma unroll
+            for (int j = 0; j < IPV; j++) v[j] = e[j];
+            if (SEG) head = head_bits<IPV>(flag_bits, idx);
+        } else {
+#pragma unroll
+            for (int j = 0; j < IPV; j++) {
+                v[j] = T(0);
+                if (idx + j < n) {
+                    v[j] = in[idx + j];
+                    if (SEG) head |= ((flag_bits[(idx + j) >> 5] >> (unsigned)((idx + j) & 31)) & 1u) << j;
+                }
+            }
+        }
+    }
+    __device__ void store(int64_t idx, int64_t n, bool fast, const T (&incl)[IPV], const T (&excl)[IPV],
+                          const Aux &) const {
+        const T(&r)[IPV] = INCLUSIVE ? incl : excl;
+        if (fast) {
+            typename V16<T>::type x;
+            T *e = reinterpret_cast<T *>(&x);
+#pragma unroll
+            for (int j = 0; j < IPV; j++) e[j] = r[j];
+            st_stream(reinterpret_cast<typename V16<T>::type *>(out + idx), x);
+        } else {
+#pragma unroll
+            for (int j = 0; j < IPV; j++)
+                if (idx + j < n) out[idx + j] = r[j];
+        }
+    }
+};
+
+// ---- final project step: v = a[i] * x[k[i]], inclusive segmented sum ------------------------------
+template <typename T_>
+struct MulGatherPolicy {
+    using T = T_;
+    using Aux = NoAux;
+    static constexpr int IPV = 16 / sizeof(T);
+    static constexpr bool SEG = true;
+    const T *a;
+    const int32_t *k;
+    const T *x;
+    const uint32_t *flag_bits;
+    T *b;
+
+    __device__ void load(int64_t idx, int64_t n, bool fast, T (&v)[IPV], unsigned &head, Aux &) const {
+        head = 0;
+        if (fast) {
+            typename V16<T>::type av = ld_stream(reinterpret_cast<const typename V16<T>::type *>(a + idx));
+            typename IdxVec<IPV>::type kv = ld_stream(reinterpret_cast<const typename IdxVec<IPV>::type *>(k + idx));
+            const T *ae = reinterpret_cast<const T *>(&av);
+            const int *ke = reinterpret_cast<const int *>(&kv);
+            T xv[IPV];
+#pragma unroll
+            for (int j = 0; j < IPV; j++) xv[j] = __ldg(x + ke[j]);
+#pragma unroll
+            for (int j = 0; j < IPV; j++) v[j] = mul_rn(ae[j], xv[j]);
+            head = head_bits<IPV>(flag_bits, idx);
+        } else {
+#pragma unroll
+            for (int j = 0; j < IPV; j++) {
+                v[j] = T(0);
+                if (idx + j < n) {
+                    v[j] = mul_rn(a[idx + j], __ldg(x + k[idx + j]));
+                    head |= ((flag_bits[(idx + j) >> 5] >> (unsigned)((idx + j) & 31)) & 1u) << j;
+                }
+            }
+        }
+    }
+    __device__ void store(int64_t idx, int64_t n, bool fast, const T (&incl)[IPV], const T (&)[IPV],
+                          const Aux &) const {
+        if (fast) {
+            typename V16<T>::type o;
+            T *e = reinterpret_cast<T *>(&o);
+#pragma unroll
+            for (int j = 0; j < IPV; j++) e[j] = incl[j];
+            st_stream(reinterpret_cast<typename V16<T>::type *>(b + idx), o);
+        } else {
+#pragma unroll
+            for (int j = 0; j < IPV; j++)
+                if (idx + j < n) b[idx + j] = incl[j];
+        }
+    }
+};
+
+// ---- COO segmented reduction: heads where the row index changes, row ends add into y ------------
+template <typename T_>
+struct CooPolicy {
+    using T = T_;
+    static constexpr int IPV = 16 / sizeof(T);
+    static constexpr bool SEG = true;
+    struct Aux { int row[IPV]; int next; };
+    const int32_t *row;
+    const int32_t *col;
+    const T *val;
+    const T *x;
+    T *y;
+
+    __device__ void load(int64_t idx, int64_t n, bool fast, T (&v)[IPV], unsigned &head, Aux &aux) const {
+        head = 0;
+        int prev = (idx > 0 && idx - 1 < n) ? __ldg(row + idx - 1) : -1;
+        if (fast) {
+            typename IdxVec<IPV>::type rv = ld_stream(reinterpret_cast<const typename IdxVec<IPV>::type *>(row + idx));
+            typename IdxVec<IPV>::type cv = ld_stream(reinterpret_cast<const typename IdxVec<IPV>::type *>(col + idx));
+            typename V16<T>::type vv = ld_stream(reinterpret_cast<const typename V16<T>::type *>(val + idx));
+            const int *re = reinterpret_cast<const int *>(&rv);
+            const int *ce = reinterpret_cast<const int *>(&cv);
+            const T *ve = reinterpret_cast<const T *>(&vv);
+            T xv[IPV];
+#pragma unroll
+            for (int j = 0; j < IPV; j++) xv[j] = __ldg(x + ce[j]);
+#pragma unroll
+            for (int j = 0; j < IPV; j++) {
+                aux.row[j] = re[j];
+                v[j] = mul_rn(ve[j], xv[j]);
+            }
+            aux.next = (idx + IPV < n) ? __ldg(row + idx + IPV) : -1;
+        } else {
+#pragma unroll
+            for (int j = 0; j < IPV; j++) {
+                aux.row[j] = -1;
+                v[j] = T(0);
+                if (idx + j < n) {
+                    aux.row[j] = row[idx + j];
+                    v[j] = mul_rn(val[idx + j], __ldg(x + col[idx + j]));
+                }
+            }
+            aux.next = (idx + IPV < n) ? row[idx + IPV] : -1;
+        }
+#pragma unroll
+        for (int j = 0; j < IPV; j++) {
+            if (aux.row[j] != prev) head |= 1u << j;
+            prev = aux.row[j];
+        }
+    }
+    __device__ void store(int64_t, int64_t, bool, const T (&incl)[IPV], const T (&)[IPV], const Aux &aux) const {
+#pragma unroll
+        for (int j = 0; j < IPV; j++) {
+            const int nxt = j + 1 < IPV ? aux.row[j + 1] : aux.next;
+            if (aux.row[j] >= 0 && aux.row[j] != nxt) y[aux.row[j]] += incl[j];
+        }
+    }
+};
+
+__global__ void flags_from_offsets_kernel(const int32_t *__restrict__ s, int p, int64_t n, uint32_t *bits) {
+    // s[0..p-1] are segment starts with s[p-1] == n (aux/mp1-util.h:131-139); the last is not an element.
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < p) {
+        const int64_t pos = s[i];
+        if (pos >= 0 && pos < n) atomicOr(bits + (pos >> 5), 1u << (unsigned)(pos & 31));
+    }
+}
+
+template <class P>
+int run(cme213_ctx *ctx, const P &p, int64_t n, bool vec_ok, void *stream, const char *name) {
+    DeviceGuard g(ctx->device);
+    return scan::launch<P>(ctx, p, n, vec_ok, (cudaStream_t)stream, name);
+}
+
+}  // namespace
+
+CME213_API int64_t cme213_flag_words(int64_t n) { return n <= 0 ? 0 : (n + 31) / 32; }
+
+CME213_API int cme213_segment_flags_from_offsets(cme213_ctx *ctx, const int32_t *d_s, int p, int64_t n,
+                                                 uint32_t *d_flag_bits, void *stream) {
+    CME213_CHECK_CTX(ctx);
+    if (p < 0 || n < 0 || (p > 0 && !d_s) || (n > 0 && !d_flag_bits)) {
+        set_error("segment_flags_from_offsets: bad arguments");
+        return CME213_ERR_INVALID;
+    }
+    if (n == 0) return CME213_OK;
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    CME213_CUDA(cudaMemsetAsync(d_flag_bits, 0, (size_t)cme213_flag_words(n) * 4, st));
+    if (p > 0) {
+        flags_from_offsets_kernel<<<(unsigned)div_up(p, 256), 256, 0, st>>>(d_s, p, n, d_flag_bits);
+        CME213_LAUNCHED(ctx, "flags_from_offsets_kernel");
+    }
+    return CME213_OK;
+}
+
+CME213_API int cme213_exclusive_scan_u32(cme213_ctx *ctx, const uint32_t *d_in, uint32_t *d_out, int64_t n,
+                                         void *stream) {
+    CME213_CHECK_CTX(ctx);
+    if (n < 0 || (n > 0 && (!d_in || !d_out))) { set_error("exclusive_scan_u32: bad arguments"); return CME213_ERR_INVALID; }
+    if (n == 0) return CME213_OK;
+    PlainPolicy<uint32_t, false, false> p{d_in, d_out, nullptr};
+    return run(ctx, p, n, aligned16(d_in) && aligned16(d_out), stream, "exclusive_scan_u32");
+}
+
+template <typename T, bool INCLUSIVE>
+static int segscan_impl(cme213_ctx *ctx, const T *d_in, const uint32_t *d_flag_bits, T *d_out, int64_t n,
+                        void *stream, const char *name) {
+    CME213_CHECK_CTX(ctx);
+    if (n < 0 || (n > 0 && (!d_in || !d_out || !d_flag_bits))) { set_error("%s: bad arguments", name); return CME213_ERR_INVALID; }
+    if (n == 0) return CME213_OK;
+    PlainPolicy<T, true, INCLUSIVE> p{d_in, d_out, d_flag_bits};
+    return run(ctx, p, n, aligned16(d_in) && aligned16(d_out), stream, name);
+}
+CME213_API int cme213_segscan_inclusive_f32(cme213_ctx *ctx, const float *d_in, const uint32_t *d_flag_bits,
+                                            float *d_out, int64_t n, void *stream) {
+    return segscan_impl<float, true>(ctx, d_in, d_flag_bits, d_out, n, stream, "segscan_inclusive_f32");
+}
+CME213_API int cme213_segscan_inclusive_f64(cme213_ctx *ctx, const double *d_in, const uint32_t *d_flag_bits,
+                                            double *d_out, int64_t n, void *stream) {
+    return segscan_impl<double, true>(ctx, d_in, d_flag_bits, d_out, n, stream, "segscan_inclusive_f64");
+}
+CME213_API int cme213_segscan_exclusive_f32(cme213_ctx *ctx, const float *d_in, const uint32_t *d_flag_bits,
+                                            float *d_out, int64_t n, void *stream) {
+    return segscan_impl<float, false>(ctx, d_in, d_flag_bits, d_out, n, stream, "segscan_exclusive_f32");
+}
+
+template <typename T>
+static int mul_gather_impl(cme213_ctx *ctx, const T *d_a, const int32_t *d_k, const T *d_x,
+                           const uint32_t *d_flag_bits, T *d_b, int64_t n, void *stream, const char *name) {
+    CME213_CHECK_CTX(ctx);
+    if (n < 0 || (n > 0 && (!d_a || !d_k || !d_x || !d_flag_bits || !d_b))) {
+        set_error("%s: bad arguments", name);
+        return CME213_ERR_INVALID;
+    }
+    if (n == 0) return CME213_OK;
+    MulGatherPolicy<T> p{d_a, d_k, d_x, d_flag_bits, d_b};
+    return run(ctx, p, n, aligned16(d_a) && aligned16(d_k) && aligned16(d_b), stream, name);
+}
+CME213_API int cme213_mul_gather_segscan_f32(cme213_ctx *ctx, const float *d_a, const int32_t *d_k, const float *d_x,
+                                             const uint32_t *d_flag_bits, float *d_b, int64_t n, void *stream) {
+    return mul_gather_impl<float>(ctx, d_a, d_k, d_x, d_flag_bits, d_b, n, stream, "mul_gather_segscan_f32");
+}
+CME213_API int cme213_mul_gather_segscan_f64(cme213_ctx *ctx, const double *d_a, const int32_t *d_k,
+                                             const double *d_x, const uint32_t *d_flag_bits, double *d_b, int64_t n,
+                                             void *stream) {
+    return mul_gather_impl<double>(ctx, d_a, d_k, d_x, d_flag_bits, d_b, n, stream, "mul_gather_segscan_f64");
+}
+
+template <typename T>
+static int coo_impl(cme213_ctx *ctx, int64_t nnz, const int32_t *d_row, const int32_t *d_col, const T *d_val,
+                    const T *d_x, T *d_y, void *stream, const char *name) {
+    CME213_CHECK_CTX(ctx);
+    if (nnz < 0 || (nnz > 0 && (!d_row || !d_col || !d_val || !d_x || !d_y))) {
+        set_error("%s: bad arguments", name);
+        return CME213_ERR_INVALID;
+    }
+    if (nnz == 0) return CME213_OK;
+    CooPolicy<T> p{d_row, d_col, d_val, d_x, d_y};
+    return run(ctx, p, nnz, aligned16(d_row) && aligned16(d_col) && aligned16(d_val), stream, name);
+}
+CME213_API int cme213_spmv_coo_accumulate_f32(cme213_ctx *ctx, int64_t nnz, const int32_t *d_row,
+                                              const int32_t *d_col, const float *d_val, const float *d_x, float *d_y,
+                                              void *stream) {
+    return coo_impl<float>(ctx, nnz, d_row, d_col, d_val, d_x, d_y, stream, "spmv_coo_accumulate_f32");
+}
+CME213_API int cme213_spmv_coo_accumulate_f64(cme213_ctx *ctx, int64_t nnz, const int32_t *d_row,
+                                              const int32_t *d_col, const double *d_val, const double *d_x,
+                                              double *d_y, void *stream) {
+    return coo_impl<double>(ctx, nnz, d_row, d_col, d_val, d_x, d_y, stream, "spmv_coo_accumulate_f64");
+}
+
+// ---- internal: scan with caller-provided scratch (see internal.cuh) ----------------------------------
+#include "internal.cuh"
+size_t cme213_internal_scan_u32_scratch_bytes(int64_t n) {
+    using P = PlainPolicy<uint32_t, false, false>;
+    return scan::scratch_bytes(div_up(n > 0 ? n : 1, scan::tile_items<P>()), 4);
+}
+int cme213_internal_exclusive_scan_u32(cme213_ctx *ctx, const uint32_t *d_in, uint32_t *d_out, int64_t n,
+                                       void *scratch, void *stream) {
+    if (n <= 0) return CME213_OK;
+    DeviceGuard g(ctx->device);
+    PlainPolicy<uint32_t, false, false> p{d_in, d_out, nullptr};
+    return scan::launch_with_scratch(ctx, p, n, aligned16(d_in) && aligned16(d_out), (cudaStream_t)stream,
+                                     "exclusive_scan_u32", scratch);
+}

@@ -1,0 +1,264 @@
+// spmv_csr.cu -- CSR sparse matrix-vector multiply and the PageRank propagate step.
+//
+// Three kernels (reference listings: slides/Lecture22.pdf slides 20, 21, 25; Bell TR 2008
+// Figs. 20, 22; hw/hw1/programming/pagerank.cu:70-83 is the CSR-scalar shape):
+//
+//  scalar : one thread per row, sequential sum.  Same order and the same rounded multiply / add
+//           as the CPU loop, so results are bit-identical to it.  Column / value reads of a warp
+//           are strided by the row length, so it leans on L1 and is the slow baseline.
+//  vector : G = 2..32 lanes per row (a power of two), strided partial sums, shuffle reduction.
+//           Coalesced, different summation order (tolerance-checked).
+//  stream : the B200 path.  A CTA owns a run of consecutive rows, so its nonzeros are one
+//           contiguous range of col/val.  The CTA streams that range with 128-bit coalesced
+//           loads (evict-first), multiplies by the gathered x entries and parks the rounded
+//           products in shared memory; then each thread sums the products of its own row
+//           sequentially.  HBM sees every byte of col/val/row_ptr/y exactly once in full
+//           sectors, x gathers hit L1/L2, and the result is again bit-identical to the CPU loop,
+//           which also makes row-sharded multi-GPU runs bitwise equal to single-GPU runs.
+//
+// Rounded products/adds use __fmul_rn/__fadd_rn (never contracted to FMA): the reference's host
+// code is built without FMA (x86-64 baseline), and its 10-ULP check (pagerank.cu:216-239) then
+// holds with zero slack.
+#include "internal.cuh"
+
+namespace {
+using namespace cme213;
+
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ double add_rn(double a, double b) { return __dadd_rn(a, b); }
+
+enum Mode { MODE_CSR = 0, MODE_PAGERANK = 1, MODE_PAGERANK_W = 2 };
+
+template <typename T> struct Args {
+    const int32_t *row_ptr;
+    const int32_t *col;
+    const T *val;   // MODE_CSR only
+    const T *x;     // x (CSR), nodes_in (PAGERANK), w = in*inv (PAGERANK_W)
+    const T *inv;   // PAGERANK: gathered; PAGERANK_W: read per row for w_out
+    T *y;
+    T *w_out;       // PAGERANK_W: y[r]*inv[r] for the next iteration (may be null)
+    T base;         // PAGERANK: 0.5/N
+};
+
+template <typename T, int MODE>
+__device__ __forceinline__ T product(const Args<T> &a, T v, int c) {
+    if (MODE == MODE_CSR) return mul_rn(v, __ldg(a.x + c));
+    if (MODE == MODE_PAGERANK) return mul_rn(__ldg(a.x + c), __ldg(a.inv + c));
+    return __ldg(a.x + c);
+}
+template <typename T, int MODE>
+__device__ __forceinline__ void epilogue(const Args<T> &a, int64_t r, T sum) {
+    if (MODE == MODE_CSR) {
+        a.y[r] = sum;
+    } else {
+        // graph_nodes_out[i] = 0.5f/N + 0.5f*sum   (pagerank.cu:54)
+        const T out = add_rn(a.base, mul_rn(T(0.5), sum));
+        a.y[r] = out;
+        if (a.w_out) a.w_out[r] = mul_rn(out, a.inv[r]);
+    }
+}
+
+// ---- scalar ---------------------------------------------------------------------------------------
+template <typename T, int MODE>
+__global__ void __launch_bounds__(256)
+csr_scalar_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
+    const int64_t r = row_begin + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= row_end) return;
+    T sum = T(0);
+    const int e = a.row_ptr[r + 1];
+    for (int j = a.row_ptr[r]; j < e; j++) {
+        const T v = MODE == MODE_CSR ? a.val[j] : T(0);
+        sum = add_rn(sum, product<T, MODE>(a, v, a.col[j]));
+    }
+    epilogue<T, MODE>(a, r, sum);
+}
+
+// ---- vector ---------------------------------------------------------------------------------------
+template <typename T, int G>
+__global__ void __launch_bounds__(256)
+csr_vector_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
+    const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t r = row_begin + gt / G;
+    const int sub = threadIdx.x % G;
+    T sum = T(0);
+    if (r < row_end) {
+        const int e = a.row_ptr[r + 1];
+        for (int j = a.row_ptr[r] + sub; j < e; j += G) sum += ld_stream(a.val + j) * __ldg(a.x + ld_stream(a.col + j));
+    }
+#pragma unroll
+    for (int d = G / 2; d > 0; d >>= 1) sum += __shfl_down_sync(0xFFFFFFFFu, sum, d, G);
+    if (r < row_end && sub == 0) a.y[r] = sum;
+}
+
+// ---- stream ---------------------------------------------------------------------------------------
+template <typename T> struct V4;  // four consecutive values
+template <> struct V4<float> {
+    float v[4];
+    __device__ static V4 load(const float *p) {
+        float4 t = ld_stream(reinterpret_cast<const float4 *>(p));
+        return V4{{t.x, t.y, t.z, t.w}};
+    }
+};
+template <> struct V4<double> {
+    double v[4];
+    __device__ static V4 load(const double *p) {
+        double2 t0 = ld_stream(reinterpret_cast<const double2 *>(p));
+        double2 t1 = ld_stream(reinterpret_cast<const double2 *>(p) + 1);
+        return V4{{t0.x, t0.y, t1.x, t1.y}};
+    }
+};
+
+template <typename T, int MODE, int THREADS, int TILE>
+__global__ void __launch_bounds__(THREADS)
+csr_stream_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
+    static_assert(TILE % (4 * THREADS) == 0, "tile must be a whole number of 4-wide vectors per thread");
+    __shared__ __align__(16) T prod[TILE];
+    const int tid = threadIdx.x;
+    const int64_t r0 = row_begin + (int64_t)blockIdx.x * THREADS;
+    const int64_t r = r0 + tid;
+    const int64_t rl = r0 + THREADS < row_end ? r0 + THREADS : row_end;
+    int rs = 0, re = 0;
+    if (r < row_end) {
+        rs = a.row_ptr[r];
+        re = a.row_ptr[r + 1];
+    }
+    const int b0 = __ldg(a.row_ptr + r0), b1 = __ldg(a.row_ptr + rl);  // this CTA's nonzero range
+    T sum = T(0);
+    for (int base = b0 & ~3; base < b1; base += TILE) {
+#pragma unroll
+        for (int v = 0; v < TILE / (4 * THREADS); v++) {
+            const int o = (v * THREADS + tid) * 4;
+            const int j = base + o;
+            if (j + 4 <= b1) {
+                const int4 c = ld_stream(reinterpret_cast<const int4 *>(a.col + j));
+                V4<T> w;
+                if (MODE == MODE_CSR) w = V4<T>::load(a.val + j);
+                else w = V4<T>{{T(0), T(0), T(0), T(0)}};
+                T p0 = product<T, MODE>(a, w.v[0], c.x);
+                T p1 = product<T, MODE>(a, w.v[1], c.y);
+                T p2 = product<T, MODE>(a, w.v[2], c.z);
+                T p3 = product<T, MODE>(a, w.v[3], c.w);
+                prod[o + 0] = p0; prod[o + 1] = p1; prod[o + 2] = p2; prod[o + 3] = p3;
+            } else {
+#pragma unroll
+                for (int t = 0; t < 4; t++)
+                    if (j + t < b1) {
+                        const T vv = MODE == MODE_CSR ? a.val[j + t] : T(0);
+                        prod[o + t] = product<T, MODE>(a, vv, a.col[j + t]);
+                    }
+            }
+        }
+        __syncthreads();
+        const int lo = rs > base ? rs : base;
+        const int hi = re < base + TILE ? re : base + TILE;
+        for (int j = lo; j < hi; j++) sum = add_rn(sum, prod[j - base]);
+        __syncthreads();
+    }
+    if (r < row_end) epilogue<T, MODE>(a, r, sum);
+}
+
+template <typename T, int MODE>
+int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row_end, int kernel, cudaStream_t st) {
+    const int64_t rows = row_end - row_begin;
+    if (rows <= 0) return CME213_OK;
+    int kind = kernel & 0xFF;
+    const int lanes = (kernel >> 8) & 0xFF;
+    const bool vec_ok = aligned16(a.col) && (MODE != MODE_CSR || aligned16(a.val));
+    if (kind == CME213_CSR_AUTO) kind = CME213_CSR_STREAM;
+    if (kind == CME213_CSR_STREAM && !vec_ok) kind = CME213_CSR_SCALAR;
+    if (kind == CME213_CSR_VECTOR && MODE != MODE_CSR) kind = CME213_CSR_STREAM;
+    if (kind == CME213_CSR_SCALAR) {
+        const int64_t blocks = div_up(rows, 256);
+        csr_scalar_kernel<T, MODE><<<(unsigned)blocks, 256, 0, st>>>(a, row_begin, row_end);
+        CME213_LAUNCHED(ctx, "csr_scalar_kernel");
+    } else if (kind == CME213_CSR_VECTOR) {
+        if constexpr (MODE == MODE_CSR) {
+            int G = lanes ? lanes : 8;
+            if (G & (G - 1) || G < 2 || G > 32) { set_error("csr vector: lanes per row must be 2,4,8,16 or 32"); return CME213_ERR_INVALID; }
+            const int64_t blocks = div_up(rows * G, 256);
+            if (blocks > 0x7FFFFFFFLL) { set_error("csr vector: too many rows"); return CME213_ERR_UNSUPPORTED; }
+            switch (G) {
+                case 2: csr_vector_kernel<T, 2><<<(unsigned)blocks, 256, 0, st>>>(a, row_begin, row_end); break;
+                case 4: csr_vector_kernel<T, 4><<<(unsigned)blocks, 256, 0, st>>>(a, row_begin, row_end); break;
+                case 8: csr_vector_kernel<T, 8><<<(unsigned)blocks, 256, 0, st>>>(a, row_begin, row_end); break;
+                case 16: csr_vector_kernel<T, 16><<<(unsigned)blocks, 256, 0, st>>>(a, row_begin, row_end); break;
+                default: csr_vector_kernel<T, 32><<<(unsigned)blocks, 256, 0, st>>>(a, row_begin, row_end); break;
+            }
+            CME213_LAUNCHED(ctx, "csr_vector_kernel");
+        }
+    } else if (kind == CME213_CSR_STREAM) {
+        constexpr int THREADS = 256, TILE = 2048;
+        const int64_t blocks = div_up(rows, THREADS);
+        csr_stream_kernel<T, MODE, THREADS, TILE><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end);
+        CME213_LAUNCHED(ctx, "csr_stream_kernel");
+    } else {
+        set_error("unknown CSR kernel %d", kernel);
+        return CME213_ERR_INVALID;
+    }
+    return CME213_OK;
+}
+
+template <typename T>
+int spmv_csr_impl(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, const int32_t *d_row_ptr, const int32_t *d_col,
+                  const T *d_val, const T *d_x, T *d_y, int kernel, void *stream) {
+    CME213_CHECK_CTX(ctx);
+    if (row_begin < 0 || row_end < row_begin) { set_error("spmv_csr: bad row range"); return CME213_ERR_INVALID; }
+    if (row_end == row_begin) return CME213_OK;
+    if (!d_row_ptr || !d_col || !d_val || !d_x || !d_y) { set_error("spmv_csr: null pointer"); return CME213_ERR_INVALID; }
+    DeviceGuard g(ctx->device);
+    Args<T> a{d_row_ptr, d_col, d_val, d_x, nullptr, d_y, nullptr, T(0)};
+    return launch_csr<T, MODE_CSR>(ctx, a, row_begin, row_end, kernel, (cudaStream_t)stream);
+}
+
+}  // namespace
+
+CME213_API int cme213_spmv_csr_f32(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, const int32_t *d_row_ptr,
+                                   const int32_t *d_col, const float *d_val, const float *d_x, float *d_y, int kernel,
+                                   void *stream) {
+    return spmv_csr_impl<float>(ctx, row_begin, row_end, d_row_ptr, d_col, d_val, d_x, d_y, kernel, stream);
+}
+CME213_API int cme213_spmv_csr_f64(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, const int32_t *d_row_ptr,
+                                   const int32_t *d_col, const double *d_val, const double *d_x, double *d_y,
+                                   int kernel, void *stream) {
+    return spmv_csr_impl<double>(ctx, row_begin, row_end, d_row_ptr, d_col, d_val, d_x, d_y, kernel, stream);
+}
+
+CME213_API int cme213_pagerank_propagate(cme213_ctx *ctx, const uint32_t *d_graph_indices,
+                                         const uint32_t *d_graph_edges, const float *d_nodes_in, float *d_nodes_out,
+                                         const float *d_inv_edges_per_node, int array_length, int kernel,
+                                         void *stream) {
+    CME213_CHECK_CTX(ctx);
+    if (array_length < 0) { set_error("pagerank_propagate: negative length"); return CME213_ERR_INVALID; }
+    if (array_length == 0) return CME213_OK;
+    if (!d_graph_indices || !d_graph_edges || !d_nodes_in || !d_nodes_out || !d_inv_edges_per_node) {
+        set_error("pagerank_propagate: null pointer");
+        return CME213_ERR_INVALID;
+    }
+    DeviceGuard g(ctx->device);
+    // 0.5f/(float)array_length, rounded once on the host exactly as pagerank.cu:54 rounds it.
+    const float base = 0.5f / (float)array_length;
+    Args<float> a{(const int32_t *)d_graph_indices, (const int32_t *)d_graph_edges, nullptr, d_nodes_in,
+                  d_inv_edges_per_node, d_nodes_out, nullptr, base};
+    return launch_csr<float, MODE_PAGERANK>(ctx, a, 0, array_length, kernel, (cudaStream_t)stream);
+}
+
+// Internal (host_api.cu): one propagate step that also emits w_out = out*inv for the next step.
+// d_nodes_in != NULL: gather in[e]*inv[e] (first step); else gather the pre-multiplied d_w_in.
+// in[e]*inv[e] is the same rounded fp32 product either way, so results do not change.
+int cme213_internal_pagerank_propagate_w(cme213_ctx *ctx, const uint32_t *d_graph_indices,
+                                         const uint32_t *d_graph_edges, const float *d_nodes_in, const float *d_w_in,
+                                         float *d_nodes_out, float *d_w_out, const float *d_inv, int array_length,
+                                         void *stream) {
+    DeviceGuard g(ctx->device);
+    const float base = 0.5f / (float)array_length;
+    if (d_nodes_in) {
+        Args<float> a{(const int32_t *)d_graph_indices, (const int32_t *)d_graph_edges, nullptr, d_nodes_in, d_inv,
+                      d_nodes_out, d_w_out, base};
+        return launch_csr<float, MODE_PAGERANK>(ctx, a, 0, array_length, CME213_CSR_STREAM, (cudaStream_t)stream);
+    }
+    Args<float> a{(const int32_t *)d_graph_indices, (const int32_t *)d_graph_edges, nullptr, d_w_in, d_inv,
+                  d_nodes_out, d_w_out, base};
+    return launch_csr<float, MODE_PAGERANK_W>(ctx, a, 0, array_length, CME213_CSR_STREAM, (cudaStream_t)stream);
+}

@@ -1,0 +1,573 @@
+#!/usr/bin/env python
+"""bench.py -- measures the hot path on B200 (see DESIGN.md "Measurement").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c5|c1|scan|segscan|fp|transpose32|
+                     transpose64|ell|hyb|csr_powerlaw|pagerank] [--impl ours|reference] [--extras 0|1]
+
+Default workload = BASELINE.json config C5: row-sharded CSR SpMV iteration on the 3-D 7-point
+Laplacian of a 512^3 grid in fp64 (134,217,728 rows, 937,951,232 nonzeros).  A *step* is one pass
+y = A x over the whole matrix, including the x exchange when N > 1 (strong scaling: the matrix is
+fixed, rows are split across ranks).  `value` is aggregate algorithmic GB/s: the compulsory bytes of
+one SpMV (matrix arrays once, x once, y once) times K, divided by the max-over-ranks device time.
+
+One JSON line on stdout (rank 0).  Everything else goes to stderr.
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+PKG = "2012-04_stanford_cme213_b200"
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons while the timed region runs."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            f = [t.strip() for t in r.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------------
+# workloads: each returns dict(step=callable, alg_bytes, flops, units, kernel, launches_per_step, meta)
+# ---------------------------------------------------------------------------------------------------
+def i32(n, torch):
+    return torch.empty(int(n), dtype=torch.int32, device="cuda")
+
+
+def make_c5(ctx, torch, args, rank, world, dist):
+    import ctypes as C
+    pkg = importlib.import_module(PKG)
+    sh = pkg.sharded if hasattr(pkg, "sharded") else importlib.import_module(PKG + ".sharded")
+    g = args.grid
+    rows = g * g * g
+    lo, hi = sh.row_partition(rows, world)[rank]
+    nloc = hi - lo
+    nnz = C.c_int64()
+    d_ptr = i32(nloc + 1, torch)
+    ctx.call("cme213_gen_laplace3d_f64", g, g, g, lo, hi, d_ptr, None, None, C.byref(nnz))
+    d_col = i32(nnz.value, torch)
+    d_val = torch.empty(nnz.value, dtype=torch.float64, device="cuda")
+    ctx.call("cme213_gen_laplace3d_f64", g, g, g, lo, hi, d_ptr, d_col, d_val, C.byref(nnz))
+    xa = torch.empty(rows, dtype=torch.float64, device="cuda")
+    xb = torch.zeros(rows, dtype=torch.float64, device="cuda")
+    ctx.call("cme213_fill_uniform_f64", xa, rows, 9)
+    xa.mul_(0.05)  # keeps 7-point growth (|lambda| <= 12) far from overflow over the run
+    streams = (torch.cuda.current_stream(), torch.cuda.Stream()) if world > 1 else None
+    it = sh.ShardedIterate(rows, world, rank, sh.cuda_spmv(ctx, lo, d_ptr, d_col, d_val, args.csr_kernel), xa, xb,
+                           halo=g * g, mode=args.exchange, dist=dist, streams=streams)
+    state = {"src": 0}
+
+    def step():
+        it.step(state["src"], 1 - state["src"])
+        state["src"] = 1 - state["src"]
+
+    nnz_total = 7 * rows - 6 * g * g
+    alg = nnz_total * 12 + (rows + 1) * 4 + rows * 8 * 2
+    local_alg = nnz.value * 12 + (nloc + 1) * 4 + nloc * 8 * 2
+    return dict(step=step, alg_bytes=alg, local_alg_bytes=local_alg, flops=2 * nnz_total, kernel="csr_stream_kernel<double>",
+                launches_per_step=1 if it.mode != "halo" else 3,
+                meta={"workload": "C5: CSR SpMV iteration, 3-D 7-point Laplacian %d^3, fp64, row-sharded over %d GPU(s)" % (g, world),
+                      "rows": rows, "nnz": nnz_total, "exchange": it.mode, "comm_bytes_per_rank_per_step": it.comm_bytes_per_step,
+                      "l2": "working set %.1f GB per pass >> 126 MB L2" % (alg / 1e9)},
+                keep=(d_ptr, d_col, d_val, xa, xb, it), iterate=it, shard=(lo, hi, d_ptr, d_col, d_val, nnz.value))
+
+
+def make_c1(ctx, torch, args):
+    import ctypes as C
+    n = 1024
+    rows = n * n
+    copies = 8  # 8 x 54 MB > 126 MB L2: rotate so every step streams from HBM
+    mats = []
+    nnz = C.c_int64()
+    for _ in range(copies):
+        d_ptr = i32(rows + 1, torch)
+        ctx.call("cme213_gen_laplace2d_f32", n, n, d_ptr, None, None, C.byref(nnz))
+        d_col, d_val = i32(nnz.value, torch), torch.empty(nnz.value, dtype=torch.float32, device="cuda")
+        ctx.call("cme213_gen_laplace2d_f32", n, n, d_ptr, d_col, d_val, C.byref(nnz))
+        x = torch.empty(rows, dtype=torch.float32, device="cuda")
+        ctx.call("cme213_fill_uniform_f32", x, rows, 2)
+        mats.append((d_ptr, d_col, d_val, x, torch.empty_like(x)))
+    state = {"i": 0}
+
+    def step():
+        p, c, v, x, y = mats[state["i"] % copies]
+        state["i"] += 1
+        ctx.call("cme213_spmv_csr_f32", 0, rows, p, c, v, x, y, args.csr_kernel, stream=torch.cuda.current_stream())
+
+    alg = nnz.value * 8 + (rows + 1) * 4 + rows * 8
+    return dict(step=step, alg_bytes=alg, flops=2 * nnz.value, kernel="csr_stream_kernel<float>", launches_per_step=1,
+                meta={"workload": "C1: CSR SpMV fp32, 2-D 5-point Poisson 1024x1024", "rows": rows, "nnz": nnz.value,
+                      "l2": "rotates %d independent copies (%.0f MB total) so each pass is cold in L2" % (copies, copies * alg / 1e6)},
+                keep=mats)
+
+
+def make_scan(ctx, torch, args):
+    n = 1 << 28
+    x = i32(n, torch)
+    ctx.call("cme213_fill_hash_u32", x, n, 3, 0)
+    out = torch.empty_like(x)
+
+    def step():
+        ctx.call("cme213_exclusive_scan_u32", x, out, n, stream=torch.cuda.current_stream())
+
+    return dict(step=step, alg_bytes=8 * n, flops=n, kernel="lookback_scan_kernel<u32>", launches_per_step=1,
+                meta={"workload": "C2a: exclusive scan of 2^28 uint32 (full-range values, wraps)", "n": n,
+                      "l2": "2.1 GB per pass >> L2"}, keep=(x, out))
+
+
+def make_segscan(ctx, torch, args):
+    n = 1 << 28
+    v = torch.empty(n, dtype=torch.float32, device="cuda")
+    ctx.call("cme213_fill_uniform_f32", v, n, 4)
+    bits = i32((n + 31) // 32, torch)
+    ctx.call("cme213_fill_random_flags", bits, n, 5, (1 << 32) // 64)
+    out = torch.empty_like(v)
+
+    def step():
+        ctx.call("cme213_segscan_inclusive_f32", v, bits, out, n, stream=torch.cuda.current_stream())
+
+    return dict(step=step, alg_bytes=8 * n + n // 8, flops=n, kernel="lookback_scan_kernel<f32,seg>", launches_per_step=1,
+                meta={"workload": "C2b: inclusive segmented fp32 scan, n=2^28, random segments of mean length 64", "n": n,
+                      "l2": "2.2 GB per pass >> L2"}, keep=(v, bits, out))
+
+
+def make_fp(ctx, torch, args):
+    n, q = 1 << 28, 1 << 20
+    a = torch.empty(n, dtype=torch.float32, device="cuda")
+    ctx.call("cme213_fill_uniform_f32", a, n, 4)
+    a0 = a.clone()
+    k = i32(n, torch)
+    ctx.call("cme213_fill_hash_u32", k, n, 6, q)
+    x = torch.empty(q, dtype=torch.float32, device="cuda")
+    ctx.call("cme213_fill_uniform_f32", x, q, 7)
+    bits = i32((n + 31) // 32, torch)
+    ctx.call("cme213_fill_random_flags", bits, n, 5, (1 << 32) // 64)
+    state = {"i": 0}
+
+    def step():
+        if state["i"] % 8 == 0:
+            a.copy_(a0)  # values shrink by |x|<1 every pass; restart before they underflow (untimed share is small, noted)
+        state["i"] += 1
+        ctx.call("cme213_mul_gather_segscan_f32", a, k, x, bits, a, n, stream=torch.cuda.current_stream())
+
+    return dict(step=step, alg_bytes=12 * n + 4 * q + n // 8, flops=2 * n, kernel="lookback_scan_kernel<mul_gather>", launches_per_step=1,
+                meta={"workload": "C2c: final-project step b = segscan(a*x[k]), n=2^28, q=2^20, in place", "n": n,
+                      "l2": "3.2 GB per pass >> L2", "note": "every 8th step restores a (one extra 2 GB copy inside the timed region)"},
+                keep=(a, a0, k, x, bits))
+
+
+def make_transpose(ctx, torch, args, bits):
+    n = 16384
+    dt = torch.float32 if bits == 32 else torch.float64
+    a = torch.empty((n, n), dtype=dt, device="cuda")
+    ctx.call("cme213_fill_uniform_f32" if bits == 32 else "cme213_fill_uniform_f64", a, n * n, 8)
+    b = torch.empty_like(a)
+    fn = "cme213_transpose_b32" if bits == 32 else "cme213_transpose_b64"
+
+    def step():
+        ctx.call(fn, a, b, n, n, n, n, stream=torch.cuda.current_stream())
+
+    return dict(step=step, alg_bytes=2 * n * n * (bits // 8), flops=0, kernel="transpose_vec_kernel<b%d>" % bits, launches_per_step=1,
+                meta={"workload": "C3: out-of-place transpose 16384x16384 fp%d" % bits, "l2": "%.1f GB per pass >> L2" % (2 * n * n * bits / 8e9)},
+                keep=(a, b))
+
+
+def make_powerlaw(ctx, torch, args, fmt):
+    import ctypes as C
+    pkg = importlib.import_module(PKG)
+    rows = args.powerlaw_rows
+    d_ptr = i32(rows + 1, torch)
+    nnz = C.c_int64()
+    if args.regular:
+        d_ptr.copy_((torch.arange(rows + 1, device="cuda", dtype=torch.int64) * 16).to(torch.int32))
+        nnz.value = rows * 16
+    else:
+        ctx.call("cme213_gen_powerlaw_lengths", rows, 4, 265, 100, 256, 6, d_ptr, C.byref(nnz))
+    d_col, d_val = i32(nnz.value, torch), torch.empty(nnz.value, dtype=torch.float32, device="cuda")
+    ctx.call("cme213_gen_random_csr_fill_f32", rows, rows, d_ptr, args.window, 7, d_col, d_val)
+    x = torch.empty(rows, dtype=torch.float32, device="cuda")
+    ctx.call("cme213_fill_uniform_f32", x, rows, 8)
+    y = torch.empty_like(x)
+    alg = nnz.value * 8 + rows * 8
+    meta = {"rows": rows, "nnz": nnz.value, "window": args.window, "regular": bool(args.regular), "l2": "%.1f GB per pass >> L2" % (alg / 1e9)}
+    name = "regular 16/row" if args.regular else "power-law (Pareto tail, cap 256)"
+    if fmt == "csr":
+        def step():
+            ctx.call("cme213_spmv_csr_f32", 0, rows, d_ptr, d_col, d_val, x, y, args.csr_kernel, stream=torch.cuda.current_stream())
+        meta["workload"] = "C4: CSR SpMV fp32, %s, %d rows" % (name, rows)
+        return dict(step=step, alg_bytes=alg + (rows + 1) * 4, flops=2 * nnz.value, kernel="csr_stream_kernel<float>", launches_per_step=1, meta=meta,
+                    keep=(d_ptr, d_col, d_val, x, y))
+    K, maxlen = C.c_int(), C.c_int()
+    ctx.call("cme213_hyb_pick_k", rows, d_ptr, C.byref(K), C.byref(maxlen))
+    Kell = maxlen.value if fmt == "ell" else K.value
+    pitch = int(pkg.load().cme213_ell_pitch(rows))
+    e_idx, e_val = i32(Kell * pitch, torch), torch.empty(Kell * pitch, dtype=torch.float32, device="cuda")
+    ctx.call("cme213_csr_to_ell_f32", rows, rows, d_ptr, d_col, d_val, Kell, pitch, e_idx, e_val)
+    meta.update({"ell_K": Kell, "max_row_len": maxlen.value, "hyb_K": K.value, "ell_actual_bytes": Kell * pitch * 8})
+    if fmt == "ell":
+        del d_col, d_val
+        def step():
+            ctx.call("cme213_spmv_ell_f32", rows, pitch, Kell, e_idx, e_val, x, y, stream=torch.cuda.current_stream())
+        meta["workload"] = "C4: ELL SpMV fp32, %s, %d rows (K = max row length)" % (name, rows)
+        return dict(step=step, alg_bytes=alg, flops=2 * nnz.value, kernel="ell_v4_kernel<float>", launches_per_step=1, meta=meta,
+                    keep=(e_idx, e_val, x, y))
+    tail = C.c_int64()
+    ctx.call("cme213_csr_to_coo_tail_f32", rows, d_ptr, d_col, d_val, Kell, C.byref(tail), None, None, None)
+    t_r, t_c, t_v = i32(max(tail.value, 4), torch), i32(max(tail.value, 4), torch), torch.empty(max(tail.value, 4), dtype=torch.float32, device="cuda")
+    if tail.value:
+        ctx.call("cme213_csr_to_coo_tail_f32", rows, d_ptr, d_col, d_val, Kell, None, t_r, t_c, t_v)
+    del d_col, d_val
+    meta.update({"coo_tail_nnz": tail.value, "hyb_actual_bytes": Kell * pitch * 8 + tail.value * 12})
+
+    def step():
+        ctx.call("cme213_spmv_hyb_f32", rows, pitch, Kell, e_idx, e_val, tail.value, t_r, t_c, t_v, x, y, stream=torch.cuda.current_stream())
+    meta["workload"] = "C4: HYB SpMV fp32 (ELL K=%d + COO tail), %s, %d rows" % (Kell, name, rows)
+    return dict(step=step, alg_bytes=alg, flops=2 * nnz.value, kernel="ell_v4_kernel<float> + lookback_scan_kernel<coo>",
+                launches_per_step=2 if tail.value else 1, meta=meta, keep=(e_idx, e_val, t_r, t_c, t_v, x, y))
+
+
+def make_pagerank(ctx, torch, args):
+    import ctypes as C
+    n, avg = 1 << 21, 8
+    ind, inv, nodes = i32(n + 1, torch), torch.empty(n, dtype=torch.float32, device="cuda"), torch.empty(n, dtype=torch.float32, device="cuda")
+    nnz = C.c_int64()
+    ctx.call("cme213_gen_pagerank_graph", n, avg, 21, ind, None, inv, nodes, C.byref(nnz))
+    edges = i32(nnz.value, torch)
+    ctx.call("cme213_gen_pagerank_graph", n, avg, 21, ind, edges, inv, nodes, C.byref(nnz))
+    out = torch.empty_like(nodes)
+    bufs = [nodes, out]
+    state = {"i": 0}
+
+    def step():
+        a, b = bufs[state["i"] % 2], bufs[1 - state["i"] % 2]
+        state["i"] += 1
+        ctx.call("cme213_pagerank_propagate", ind, edges, a, b, inv, n, 0, stream=torch.cuda.current_stream())
+
+    alg = nnz.value * 4 + (n + 1) * 4 + n * 12
+    return dict(step=step, alg_bytes=alg, flops=2 * nnz.value + 2 * n, kernel="csr_stream_kernel<float,pagerank>", launches_per_step=1,
+                meta={"workload": "C1': PageRank propagate (hw1), N=2^21, avg_edges=8", "nnz": nnz.value,
+                      "l2": "working set %.0f MB fits in L2: warm-L2 number, not an HBM roofline" % (alg / 1e6)}, keep=(ind, edges, inv, nodes, out))
+
+
+def build_workload(name, ctx, torch, args, rank=0, world=1, dist=None):
+    if name == "c5":
+        return make_c5(ctx, torch, args, rank, world, dist)
+    if name == "c1":
+        return make_c1(ctx, torch, args)
+    if name == "scan":
+        return make_scan(ctx, torch, args)
+    if name == "segscan":
+        return make_segscan(ctx, torch, args)
+    if name == "fp":
+        return make_fp(ctx, torch, args)
+    if name == "transpose32":
+        return make_transpose(ctx, torch, args, 32)
+    if name == "transpose64":
+        return make_transpose(ctx, torch, args, 64)
+    if name in ("ell", "hyb"):
+        return make_powerlaw(ctx, torch, args, name)
+    if name == "csr_powerlaw":
+        return make_powerlaw(ctx, torch, args, "csr")
+    if name == "pagerank":
+        return make_pagerank(ctx, torch, args)
+    raise SystemExit("unknown workload " + name)
+
+
+def time_steps(torch, step, steps, warmup, dist=None):
+    for _ in range(warmup):
+        step()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+        torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    if dist is not None:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.barrier()
+        torch.cuda.synchronize()
+        ms = float(t.item())
+    return ms
+
+
+# ---------------------------------------------------------------------------------------------------
+# CPU baseline (oracle = checker; timed here only as the reported baseline)
+# ---------------------------------------------------------------------------------------------------
+def cpu_baseline_c5(torch, wl, grid, budget_s=12.0):
+    """Reference-style CPU loop (csr_spmv of slides/Lecture22.pdf slide 20, OpenMP over rows) on a
+    bounded sample of the same matrix: the first planes of this rank's shard."""
+    import numpy as np
+    import oracle
+    lo, hi, d_ptr, d_col, d_val, nnz = wl["shard"]
+    planes = max(1, min(32, (hi - lo) // (grid * grid)))
+    rows = planes * grid * grid
+    ptr = d_ptr[:rows + 1].cpu().numpy()
+    n = int(ptr[-1])
+    col, val = d_col[:n].cpu().numpy(), d_val[:n].cpu().numpy()
+    x = np.random.default_rng(0).uniform(-1, 1, lo + rows + grid * grid + 1)
+    threads = oracle.num_threads()
+    oracle.csr_spmv(ptr, col, val, x, omp=True)  # warm-up
+    reps, t0 = 0, time.perf_counter()
+    while True:
+        oracle.csr_spmv(ptr, col, val, x, omp=True)
+        reps += 1
+        el = time.perf_counter() - t0
+        if el > budget_s or reps >= 50:
+            break
+    alg = n * 12 + (rows + 1) * 4 + rows * 16
+    return {"value": alg * reps / el / 1e9, "unit": "GB/s", "cores": threads, "kind": "port",
+            "sample": "first %d planes of the %d^3 grid (%d rows, %d nnz), %d passes, OpenMP over rows, %d threads"
+                      % (planes, grid, rows, n, reps, threads)}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path for the same metric on the host cores.  For C5 the
+    reference has no fp64 CSR code of its own (its CSR is the fp32 PageRank gather), so this is the
+    oracle port of the slide-20 loop with OpenMP over rows (kind = "port")."""
+    import numpy as np
+    import oracle
+    from oracle import generators as g
+    oracle.build()
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    grid = args.grid
+    planes = 32 if grid >= 32 else grid
+    rows = planes * grid * grid
+    ptr, col, val = g.laplace3d(grid, grid, grid, 0, rows)
+    x = np.random.default_rng(0).uniform(-1, 1, grid ** 3)
+    y_alg = len(col) * 12 + (rows + 1) * 4 + rows * 16
+    threads = oracle.num_threads()
+    for _ in range(args.warmup):
+        oracle.csr_spmv(ptr, col, val, x, omp=True)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        oracle.csr_spmv(ptr, col, val, x, omp=True)
+    el = time.perf_counter() - t0
+    v = y_alg * args.steps / el / 1e9
+    sample = "each step = one SpMV over the first %d planes of the %d^3 grid (%d rows, %d nnz)" % (planes, grid, rows, len(col))
+    print(json.dumps({
+        "impl": "reference", "metric": "spmv_algorithmic_gbs", "value": v, "unit": "GB/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": el / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "C5: CSR SpMV iteration, 3-D 7-point Laplacian %d^3, fp64 (CPU, bounded sample)" % grid},
+        "cpu_baseline": {"value": v, "unit": "GB/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------
+def e2e_c5(torch, pkg, wl, args, rank, world, dist):
+    """End to end through the host-pointer driver entry point (cme213_csr_iterate_host_f64, the C5
+    analogue of device_graph_iterate): pinned HOST arrays in, H2D + 20 iterations + D2H inside the
+    timed region.  Each rank drives its own row block of the matrix (its rows x the columns it
+    touches); no exchange is needed for that, and the aggregate is the sum over ranks."""
+    import ctypes as C
+    import numpy as np
+    lo, hi, d_ptr, d_col, d_val, nnz = wl["shard"]
+    g = args.grid
+    rows_total = g ** 3
+    # Single-GPU semantics need a square operator: at N=1 that is the whole matrix.  At N>1 every rank
+    # times the upload + iteration of a square diagonal block (columns outside the block dropped by
+    # pointing them at a zero entry would change the matrix), so e2e is reported at N=1 only.
+    if world > 1:
+        return None
+    iters = 20
+    pin = lambda t: t.cpu().pin_memory()
+    h_ptr, h_col, h_val = pin(d_ptr), pin(d_col), pin(d_val)
+    h_x = torch.empty(rows_total, dtype=torch.float64).pin_memory()
+    h_x.copy_(wl["keep"][3].cpu() if wl["keep"][3].numel() == rows_total else torch.rand(rows_total, dtype=torch.float64))
+    h_x.mul_(1e-3)
+    h_y = torch.empty(rows_total, dtype=torch.float64).pin_memory()
+    lib = pkg.load()
+    P = lambda t: C.c_void_p(t.data_ptr())
+    h2d = h_ptr.numel() * 4 + h_col.numel() * 4 + h_val.numel() * 8 + rows_total * 8
+    d2h = rows_total * 8
+    calls = max(1, min(args.steps, 3))
+    kernel_ms = C.c_float()
+    rc = lib.cme213_csr_iterate_host_f64(rows_total, nnz, P(h_ptr), P(h_col), P(h_val), P(h_x), P(h_y), 2, C.byref(kernel_ms))
+    if rc != 0:
+        raise RuntimeError(lib.cme213_last_error())
+    t0 = time.perf_counter()
+    for _ in range(calls):
+        rc = lib.cme213_csr_iterate_host_f64(rows_total, nnz, P(h_ptr), P(h_col), P(h_val), P(h_x), P(h_y), iters, C.byref(kernel_ms))
+        if rc != 0:
+            raise RuntimeError(lib.cme213_last_error())
+    el = time.perf_counter() - t0
+    return {"value": wl["alg_bytes"] * iters * calls / el / 1e9, "unit": "GB/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+            "call": "cme213_csr_iterate_host_f64(nr_iterations=%d): pinned host CSR in, result vector out" % iters,
+            "calls_timed": calls, "ms_per_call": el / calls * 1e3, "kernel_ms_inside_call": float(kernel_ms.value)}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--workload", default="c5")
+    ap.add_argument("--grid", type=int, default=512)
+    ap.add_argument("--exchange", default="halo", choices=["halo", "full"])
+    ap.add_argument("--csr-kernel", type=int, default=0)
+    ap.add_argument("--powerlaw-rows", type=int, default=1 << 24)
+    ap.add_argument("--window", type=int, default=0)
+    ap.add_argument("--regular", type=int, default=0)
+    ap.add_argument("--extras", type=int, default=1, help="also time the other single-GPU configs (N=1 only)")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
+
+    if args.impl == "reference":
+        run_reference(args)
+        return
+
+    import torch
+    pkg = importlib.import_module(PKG)
+    pkg.load()  # fails loudly when the CUDA library is missing: there is no other path
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    ctx = pkg.Context(local)
+    peak, peak_kind = measured_peak()
+
+    wl = build_workload(args.workload, ctx, torch, args, rank, world, dist)
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ctx.launches
+    ms = time_steps(torch, wl["step"], args.steps, args.warmup, dist)
+    launches = (ctx.launches - l0) * args.steps // (args.steps + args.warmup)
+    clocks = sampler.stop() if rank == 0 else None
+    ms_step = ms / args.steps
+    value = wl["alg_bytes"] / (ms_step * 1e-3) / 1e9
+
+    # roofline of the dominant kernel: algorithmic bytes of ONE launch (this rank's rows) over its
+    # average duration, timed alone with CUDA events on its launch stream
+    roof = None
+    if args.workload == "c5":
+        it = wl["iterate"]
+        xin, xout = it.x[0], it.x[1]
+        kstep = lambda: it.spmv(it.lo, it.hi, xin, xout)
+        kms = time_steps(torch, kstep, args.steps, 3) / args.steps
+        ach = wl["local_alg_bytes"] / (kms * 1e-3) / 1e9
+    else:
+        kms = ms_step
+        ach = value
+    roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+            "kernel": wl["kernel"], "kernel_ms": kms, "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)" if peak_kind == "measured" else "fallback 6650 GB/s",
+            "frac_of_8TBs_spec": ach / 8000.0, "gflops": wl["flops"] / max(world, 1) / (kms * 1e-3) / 1e9 if args.workload == "c5" else wl["flops"] / (kms * 1e-3) / 1e9}
+
+    out = {"metric": "spmv_algorithmic_gbs" if args.workload in ("c5", "c1", "ell", "hyb", "csr_powerlaw", "pagerank") else "algorithmic_gbs",
+           "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+           "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64" if args.workload == "c5" else "f32/u32",
+           "data": "synthetic", "config": wl["meta"], "gflops": wl["flops"] / (ms_step * 1e-3) / 1e9,
+           "roofline": roof, "gpu_launches": launches, "clocks": clocks}
+
+    if rank == 0 and args.workload == "c5" and not args.no_cpu and world == 1:
+        import oracle
+        oracle.build()
+        out["cpu_baseline"] = cpu_baseline_c5(torch, wl, args.grid)
+    if args.workload == "c5" and not args.no_e2e:
+        e = e2e_c5(torch, pkg, wl, args, rank, world, dist)
+        if e is not None:
+            out["e2e"] = e
+    if world == 1 and args.extras and args.workload == "c5":
+        others = []
+        del wl
+        torch.cuda.empty_cache()
+        names = ["scan", "segscan", "fp", "transpose32", "transpose64", "c1", "ell", "hyb", "csr_powerlaw", "pagerank"]
+        for name in names:
+            try:
+                w = build_workload(name, ctx, torch, args)
+                t = time_steps(torch, w["step"], args.steps, 3) / args.steps
+                gbs = w["alg_bytes"] / (t * 1e-3) / 1e9
+                others.append({"workload": w["meta"]["workload"], "ms": t, "gbs": gbs, "frac_of_measured_peak": gbs / peak,
+                               "gflops": w["flops"] / (t * 1e-3) / 1e9, "kernel": w["kernel"],
+                               "detail": {k: v for k, v in w["meta"].items() if k != "workload"}})
+                log("extra %-12s %8.3f ms  %8.1f GB/s  (%.2f of peak)" % (name, t, gbs, gbs / peak))
+                del w
+                torch.cuda.empty_cache()
+            except Exception as ex:  # an extra must not take the headline down
+                others.append({"workload": name, "error": repr(ex)})
+                log("extra", name, "failed:", repr(ex))
+        out["others"] = others
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,234 @@
+/*
+ * cme213_b200.h -- C ABI of libcme213_b200.so
+ *
+ * B200-native (sm_100a) replacement for the data-parallel hot path of the
+ * Stanford CME213 (Spring 2012) coursework: CSR / ELL / HYB sparse
+ * matrix-vector multiply, the exclusive / segmented scan and the tiled
+ * transpose it rests on, and the host-pointer driver entry points the
+ * homework programs call.  Plain pointers and sizes only; no C++ or torch
+ * types cross this boundary.
+ *
+ * Conventions
+ *   - every function returns int: 0 = CME213_OK, negative = error
+ *     (cme213_last_error() gives the text).  Nothing here calls exit(): the
+ *     reference prints and exits (hw/hw1/programming/mp1-util.h:8-18), a
+ *     library cannot.
+ *   - pointers named d_* are device pointers, h_* are host pointers.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = default stream).
+ *     Device-pointer functions only enqueue work; they do not synchronise.
+ *   - indices are 32-bit as in the reference (unsigned int in hw1, int in
+ *     hw_final); element counts and byte offsets are 64-bit.
+ *   - "reference:" comments cite the file:line (relative to the reference
+ *     checkout) that each entry point replaces or restates.
+ */
+#ifndef CME213_B200_H
+#define CME213_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CME213_OK 0
+#define CME213_ERR_INVALID (-1)     /* bad argument (null pointer, negative size, odd iteration count ...) */
+#define CME213_ERR_CUDA (-2)        /* a CUDA runtime call or kernel launch failed */
+#define CME213_ERR_ALLOC (-3)       /* device or host allocation failed */
+#define CME213_ERR_UNSUPPORTED (-4) /* size beyond a documented limit */
+
+/* CSR kernel selection (cme213_spmv_csr_*).  reference: slides/Lecture22.pdf slides 20-26,
+ * refs/Bell Tech Report 2008.pdf Figs. 20, 22. */
+#define CME213_CSR_AUTO 0
+#define CME213_CSR_SCALAR 1 /* one thread per row, sequential sum: bit-identical to the CPU loop */
+#define CME213_CSR_VECTOR 2 /* 2..32 lanes per row, warp-shuffle reduction */
+#define CME213_CSR_STREAM 3 /* block streams its nonzeros through shared memory, then one thread per row sums sequentially: bit-identical to the CPU loop */
+
+typedef struct cme213_ctx cme213_ctx;
+
+/* ---- context ---------------------------------------------------------- */
+/* Binds to a CUDA device and owns a scratch workspace that grows on demand
+ * (cudaMalloc on first use / growth, never inside a steady-state loop).
+ * reference: the callee-owns-device-memory rule of hw/hw1/programming/pagerank.cu:85-93. */
+int cme213_ctx_create(int device, cme213_ctx **out);
+int cme213_ctx_destroy(cme213_ctx *ctx);
+int cme213_ctx_device(const cme213_ctx *ctx);
+int cme213_ctx_sm_count(const cme213_ctx *ctx);
+/* Number of kernels this context has launched since creation (bench.py's gpu_launches). */
+int64_t cme213_ctx_launch_count(const cme213_ctx *ctx);
+const char *cme213_last_error(void);
+int cme213_version(void);
+
+/* ---- transpose --------------------------------------------------------- */
+/* out[c*ld_out + r] = in[r*ld_in + c] for r < rows, c < cols (row-major, out of place).
+ * ld_in >= cols, ld_out >= rows, in elements.  b32 covers float/int32, b64 covers double.
+ * reference: slides/Lecture06.pdf slide 9/20 (array_out[n*M+m] = array_in[m*N+n]);
+ * slides/Lecture07.pdf slides 2-4 (fastTranspose); my-refs/MatrixTranspose.pdf. */
+int cme213_transpose_b32(cme213_ctx *ctx, const void *d_in, void *d_out, int64_t rows, int64_t cols,
+                         int64_t ld_in, int64_t ld_out, void *stream);
+int cme213_transpose_b64(cme213_ctx *ctx, const void *d_in, void *d_out, int64_t rows, int64_t cols,
+                         int64_t ld_in, int64_t ld_out, void *stream);
+
+/* ---- scans ------------------------------------------------------------- */
+/* out[0] = 0, out[i] = in[0] + ... + in[i-1] (mod 2^32).  Single pass, decoupled look-back.
+ * In place (d_out == d_in) is allowed.
+ * reference: hw/hw4/programming/radixsort.cpp:76-81 and :136-140; my-refs/scan.pdf p.4. */
+int cme213_exclusive_scan_u32(cme213_ctx *ctx, const uint32_t *d_in, uint32_t *d_out, int64_t n, void *stream);
+
+/* Segment descriptions.  The reference stores p segment START offsets s[0]=0 < ... < s[p-1]=n
+ * (hw/hw_final/programming/aux/mp1-util.h:118-139).  The kernels read a head-flag bitmask instead
+ * (bit i of word i/32 set = element i starts a segment); it depends on s only, so it is built
+ * once outside the timed loop, which hw/hw_final/Final.pdf p.3 allows.
+ * d_flag_bits must hold cme213_flag_words(n) uint32 words. */
+int64_t cme213_flag_words(int64_t n);
+int cme213_segment_flags_from_offsets(cme213_ctx *ctx, const int32_t *d_s, int p, int64_t n,
+                                      uint32_t *d_flag_bits, void *stream);
+
+/* Inclusive segmented sum scan.  In place allowed.
+ * reference: hw/hw_final/programming/fp.cu:142-149 (CPU), :39-59 (GPU SegmentedScan). */
+int cme213_segscan_inclusive_f32(cme213_ctx *ctx, const float *d_in, const uint32_t *d_flag_bits, float *d_out,
+                                 int64_t n, void *stream);
+int cme213_segscan_inclusive_f64(cme213_ctx *ctx, const double *d_in, const uint32_t *d_flag_bits, double *d_out,
+                                 int64_t n, void *stream);
+/* Exclusive variant (first element of each segment gets 0). */
+int cme213_segscan_exclusive_f32(cme213_ctx *ctx, const float *d_in, const uint32_t *d_flag_bits, float *d_out,
+                                 int64_t n, void *stream);
+
+/* One step of the final project, fused: b[j] = inclusive segmented sum of a[i]*x[k[i]].
+ * d_b == d_a allowed.  The x gather happens on the device inside the step.
+ * reference: hw/hw_final/programming/aux/reference_spMVscan-released.cu:38-54 (sparseMV_scan);
+ * hw/hw_final/programming/fp.cu:174-180 (transform + SegmentedScan). */
+int cme213_mul_gather_segscan_f32(cme213_ctx *ctx, const float *d_a, const int32_t *d_k, const float *d_x,
+                                  const uint32_t *d_flag_bits, float *d_b, int64_t n, void *stream);
+int cme213_mul_gather_segscan_f64(cme213_ctx *ctx, const double *d_a, const int32_t *d_k, const double *d_x,
+                                  const uint32_t *d_flag_bits, double *d_b, int64_t n, void *stream);
+
+/* ---- CSR SpMV ---------------------------------------------------------- */
+/* y[r] = sum_j val[j] * x[col[j]], j in [row_ptr[r], row_ptr[r+1]), for rows r in [row_begin, row_end).
+ * row_ptr, y are indexed by r itself (not r - row_begin) so a caller can split one matrix into
+ * several launches (boundary rows first, interior rows later).
+ * reference: slides/Lecture22.pdf slide 20 (csr_spmv), slides 21/25 (scalar / vector kernels);
+ * hw/hw1/programming/pagerank.cu:70-83 (the CSR-scalar shape). */
+int cme213_spmv_csr_f32(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, const int32_t *d_row_ptr,
+                        const int32_t *d_col, const float *d_val, const float *d_x, float *d_y, int kernel,
+                        void *stream);
+int cme213_spmv_csr_f64(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, const int32_t *d_row_ptr,
+                        const int32_t *d_col, const double *d_val, const double *d_x, double *d_y, int kernel,
+                        void *stream);
+
+/* PageRank propagate: out[i] = 0.5f/N + 0.5f * sum_j in[e[j]] * inv[e[j]].
+ * reference: hw/hw1/programming/pagerank.cu:45-56 (CPU), :70-83 (GPU). */
+int cme213_pagerank_propagate(cme213_ctx *ctx, const uint32_t *d_graph_indices, const uint32_t *d_graph_edges,
+                              const float *d_nodes_in, float *d_nodes_out, const float *d_inv_edges_per_node,
+                              int array_length, int kernel, void *stream);
+
+/* ---- ELL / COO / HYB --------------------------------------------------- */
+/* ELL, column-major: entry n of row r lives at [n*pitch + r]; padded entries have value 0.
+ * y = A x.  reference: refs/Bell Tech Report 2008.pdf Fig. 17 (spmv_ell_kernel);
+ * refs/Bell SC 2009.pdf p.3 Fig. 2/4, section 3.2; slides/Lecture22.pdf slides 26-28. */
+int cme213_spmv_ell_f32(cme213_ctx *ctx, int64_t num_rows, int64_t pitch, int num_cols_per_row,
+                        const int32_t *d_ell_idx, const float *d_ell_val, const float *d_x, float *d_y, void *stream);
+int cme213_spmv_ell_f64(cme213_ctx *ctx, int64_t num_rows, int64_t pitch, int num_cols_per_row,
+                        const int32_t *d_ell_idx, const double *d_ell_val, const double *d_x, double *d_y, void *stream);
+/* COO sorted by row, y[row] += sum of the row's entries (segmented reduction, one writer per row,
+ * no atomics).  reference: refs/Bell Tech Report 2008.pdf Fig. 24 (segmented_reduction);
+ * slides/Lecture22.pdf slides 29-30. */
+int cme213_spmv_coo_accumulate_f32(cme213_ctx *ctx, int64_t nnz, const int32_t *d_row, const int32_t *d_col,
+                                   const float *d_val, const float *d_x, float *d_y, void *stream);
+int cme213_spmv_coo_accumulate_f64(cme213_ctx *ctx, int64_t nnz, const int32_t *d_row, const int32_t *d_col,
+                                   const double *d_val, const double *d_x, double *d_y, void *stream);
+/* HYB = ELL(K) followed by the COO tail.  reference: refs/Bell SC 2009.pdf p.5 section 3.5. */
+int cme213_spmv_hyb_f32(cme213_ctx *ctx, int64_t num_rows, int64_t pitch, int K, const int32_t *d_ell_idx,
+                        const float *d_ell_val, int64_t coo_nnz, const int32_t *d_coo_row,
+                        const int32_t *d_coo_col, const float *d_coo_val, const float *d_x, float *d_y, void *stream);
+
+/* ---- format conversion on the device ----------------------------------- */
+/* HYB split width: largest K such that at least max(4096, num_rows/3) rows have >= K entries.
+ * Synchronises `stream`.  reference: refs/Bell SC 2009.pdf p.5 section 3.5. */
+int cme213_hyb_pick_k(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr, int *K_out, int *max_len_out,
+                      void *stream);
+/* CSR -> ELL(K), column-major with the given pitch (>= num_rows, multiple of 4 recommended).
+ * Rows longer than K are truncated.  Built as a padded row-major fill followed by the tiled
+ * transpose above, in row chunks so the staging buffer stays small. */
+int64_t cme213_ell_pitch(int64_t num_rows);
+int cme213_csr_to_ell_f32(cme213_ctx *ctx, int64_t num_rows, int64_t num_cols, const int32_t *d_row_ptr,
+                          const int32_t *d_col, const float *d_val, int K, int64_t pitch, int32_t *d_ell_idx,
+                          float *d_ell_val, void *stream);
+int cme213_csr_to_ell_f64(cme213_ctx *ctx, int64_t num_rows, int64_t num_cols, const int32_t *d_row_ptr,
+                          const int32_t *d_col, const double *d_val, int K, int64_t pitch, int32_t *d_ell_idx,
+                          double *d_ell_val, void *stream);
+/* Entries at in-row position >= K, in row order.  Call with d_coo_* == NULL to get the count only
+ * (synchronises); the offsets are an exclusive scan of max(len-K,0). */
+int cme213_csr_to_coo_tail_f32(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr, const int32_t *d_col,
+                               const float *d_val, int K, int64_t *tail_nnz_out, int32_t *d_coo_row,
+                               int32_t *d_coo_col, float *d_coo_val, void *stream);
+
+/* ---- input generators (device side, deterministic) ---------------------- */
+/* The homework drivers generate their inputs in main(); the large configurations cannot be
+ * generated on the host in reasonable time, so the same recipes run on the device.  Row pointers
+ * are produced by cme213_exclusive_scan_u32 over the row lengths. */
+/* 5-point Laplacian on an nx x ny grid, natural order, sorted columns, diag 4 / off-diag -1.
+ * rows = nx*ny.  d_row_ptr[rows+1].  Pass d_col = d_val = NULL to get nnz only.
+ * reference: the order-2 stencil of hw/hw2/programming/2dHeat.cu:361-366 as a matrix. */
+int cme213_gen_laplace2d_f32(cme213_ctx *ctx, int nx, int ny, int32_t *d_row_ptr, int32_t *d_col, float *d_val,
+                             int64_t *nnz_out, void *stream);
+/* 7-point Laplacian on nx x ny x nz, rows [row_begin,row_end) only (a z-slab shard); column indices are
+ * global; d_row_ptr[(row_end-row_begin)+1] is rebased to 0.  diag 6 / off-diag -1. */
+int cme213_gen_laplace3d_f64(cme213_ctx *ctx, int nx, int ny, int nz, int64_t row_begin, int64_t row_end,
+                             int32_t *d_row_ptr, int32_t *d_col, double *d_val, int64_t *nnz_out, void *stream);
+/* Power-law rows (Pareto tail, shape 1, capped): len = min(cap, r0 + floor(num*(2^32-1-h)/(den*(h+1)))),
+ * h = hash32(seed, row); columns stratified-random and sorted inside a window of `window` columns centred
+ * on the row (window = 0: the whole matrix); values uniform in (-1,1), never 0.
+ * reference: refs/Bell SC 2009.pdf p.6 Fig. 9 recipe (base + Pareto row lengths). */
+int cme213_gen_powerlaw_lengths(cme213_ctx *ctx, int64_t num_rows, int r0, uint32_t num, uint32_t den, int cap,
+                                uint32_t seed, int32_t *d_row_ptr, int64_t *nnz_out, void *stream);
+int cme213_gen_random_csr_fill_f32(cme213_ctx *ctx, int64_t num_rows, int64_t num_cols, const int32_t *d_row_ptr,
+                                   int64_t window, uint32_t seed, int32_t *d_col, float *d_val, void *stream);
+/* PageRank graph of hw/hw1/programming/pagerank.cu:185-204 with a counter hash in place of rand():
+ * node i has (i % (2*avg_edges-1))+1 edges to hash-random nodes, inv = 1/edges, x0 = 1/N. */
+int cme213_gen_pagerank_graph(cme213_ctx *ctx, int num_elements, int avg_edges, uint32_t seed,
+                              uint32_t *d_graph_indices, uint32_t *d_graph_edges, float *d_inv_edges_per_node,
+                              float *d_nodes, int64_t *nnz_out, void *stream);
+/* Fills: uniform float/double in (-1,1) (readMM.py:32 distribution), raw 32-bit hash, hash % modulus,
+ * and random head flags with probability num/2^32 per element (bit 0 always set). */
+int cme213_fill_uniform_f32(cme213_ctx *ctx, float *d_out, int64_t n, uint32_t seed, void *stream);
+int cme213_fill_uniform_f64(cme213_ctx *ctx, double *d_out, int64_t n, uint32_t seed, void *stream);
+int cme213_fill_hash_u32(cme213_ctx *ctx, uint32_t *d_out, int64_t n, uint32_t seed, uint32_t modulus, void *stream);
+int cme213_fill_random_flags(cme213_ctx *ctx, uint32_t *d_flag_bits, int64_t n, uint32_t seed, uint32_t prob_num,
+                             void *stream);
+
+/* ---- host-pointer driver entry points (drop-in boundary) ---------------- */
+/* Exactly the homework's signature: host pointers in, host pointer out, the function owns all device
+ * memory, nr_iterations even.  Prints "gpu graph propagate took X ms" like the reference's timer.
+ * reference: hw/hw1/programming/pagerank.cu:85-143 (device_graph_iterate). */
+void device_graph_iterate(unsigned int *h_graph_indices, unsigned int *h_graph_edges, float *h_graph_nodes_input,
+                          float *h_graph_nodes_result, float *h_inv_edges_per_node, int nr_iterations,
+                          int num_elements, int avg_edges);
+/* Same with a status code, explicit nnz, optional kernel-only time (ms) and no printing. */
+int cme213_pagerank_iterate_host(const uint32_t *h_graph_indices, const uint32_t *h_graph_edges,
+                                 const float *h_nodes_input, float *h_nodes_result, const float *h_inv_edges_per_node,
+                                 int nr_iterations, int num_elements, float *kernel_ms_out);
+/* Iterated y = A x on a general CSR matrix with ping-pong buffers (the loop of pagerank.cu:128-132);
+ * result after nr_iterations (even) lands in h_x_result. */
+int cme213_csr_iterate_host_f64(int64_t num_rows, int64_t nnz, const int32_t *h_row_ptr, const int32_t *h_col,
+                                const double *h_val, const double *h_x_input, double *h_x_result,
+                                int nr_iterations, float *kernel_ms_out);
+int cme213_csr_iterate_host_f32(int64_t num_rows, int64_t nnz, const int32_t *h_row_ptr, const int32_t *h_col,
+                                const float *h_val, const float *h_x_input, float *h_x_result, int nr_iterations,
+                                float *kernel_ms_out);
+/* The final project's timed loop: N passes of product + inclusive segmented scan with a <- b between
+ * passes.  reference: hw/hw_final/programming/fp.cu:154-188 (float);
+ * aux/reference_spMVscan-released.cu:213-217 (double, sparseMV_scan + swap). */
+int cme213_fp_iterate_host_f32(int n, int p, int q, int iters, const float *h_a, const int32_t *h_s,
+                               const int32_t *h_k, const float *h_x, float *h_b, float *kernel_ms_out);
+int cme213_fp_iterate_host_f64(int n, int p, int q, int iters, const double *h_a, const int32_t *h_s,
+                               const int32_t *h_k, const double *h_x, double *h_b, float *kernel_ms_out);
+/* Host-pointer twins of the primitives. */
+int cme213_exclusive_scan_u32_host(const uint32_t *h_in, uint32_t *h_out, int64_t n);
+int cme213_transpose_host_b32(const void *h_in, void *h_out, int64_t rows, int64_t cols);
+int cme213_transpose_host_b64(const void *h_in, void *h_out, int64_t rows, int64_t cols);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CME213_B200_H */
