@@ -1,23 +1,32 @@
 // lookback_scan.cuh -- single-pass (segmented) prefix sum with decoupled look-back.
 //
-// One kernel serves every scan on the hot path; a policy object supplies how a 16-byte vector of
-// items is produced (plain load, a[i]*x[k[i]] gather-multiply, COO product with row-change head
-// flags) and consumed (exclusive / inclusive store, COO row-end accumulate into y).
+// One kernel family serves every scan on the hot path; a policy object supplies how a 16-byte
+// vector of items is produced (plain load, a[i]*x[k[i]] gather-multiply, COO product with
+// row-change head flags) and consumed (exclusive / inclusive store, COO row-end accumulate).
 //
-// Structure of one tile (256 threads, 4 vectors of 16 bytes per thread):
+// Tile = THREADS threads x VECS vectors of 16 bytes.  Sub-tile i is the i-th run of THREADS
+// consecutive vectors: thread t owns vector i*THREADS + t, so a warp's 128-bit accesses cover 512
+// contiguous bytes.  Per tile:
 //   1. the tile index comes from an atomic ticket, so a tile can only wait on tiles that have
 //      already started (forward progress does not depend on blockIdx scheduling order);
-//   2. sub-tile i (i = 0..3) is the i-th run of 256 consecutive vectors: thread t owns vector
-//      i*256 + t of the tile, so every LDG.128/STG.128 of a warp covers 512 contiguous bytes;
-//   3. each thread reduces its vectors, each warp scans its 32 per-thread aggregates with
-//      shuffles (4 independent chains), and the 8 warps x 4 sub-tiles = 32 warp aggregates are
-//      scanned by one more warp-wide shuffle scan (done redundantly by every warp: one barrier);
-//   4. warp 0 publishes the tile aggregate, walks back over predecessor descriptors 32 at a time
-//      until it meets an inclusive prefix (or, for segmented scans, a tile that contains a
-//      segment head), publishes the tile's inclusive prefix and hands the exclusive prefix to
-//      the other warps;
-//   5. every thread finishes its items in registers and stores them.
-// Each element is read once and written once; descriptors add 8-20 bytes per 4096 elements.
+//   2. each thread reduces its vectors, each warp scans its 32 thread aggregates with shuffles
+//      (VECS independent chains) and parks its VECS warp aggregates in shared memory;
+//   3. warp 0 scans the WARPS*VECS warp aggregates, publishes the tile aggregate, walks back over
+//      predecessor descriptors 32 at a time until it meets an inclusive prefix (or, for segmented
+//      scans, a tile that contains a segment head), publishes the tile's inclusive prefix and hands
+//      the exclusive prefix to the other warps;
+//   4. every thread finishes its items in registers and stores them with 128-bit stores.
+// Each element is read once and written once; descriptors add 8-20 bytes per tile.
+//
+// Two front ends share that core:
+//   * lookback_scan_bulk_kernel (the B200 path): a persistent CTA keeps a ring of STAGES tiles in
+//     shared memory, filled by 1-D bulk async copies (cp.async.bulk + mbarrier complete_tx, the TMA
+//     engine's linear mode; SASS UBLKCP).  The loads of the next tiles are in flight while warp 0
+//     sits in the look-back of the current one, so the bytes in flight per SM no longer depend on
+//     the look-back latency -- which is what held the first version of this kernel to half of HBM
+//     bandwidth (profiles/r01_notes.md).
+//   * lookback_scan_kernel: one CTA per tile, direct global loads.  Any alignment, any size; used
+//     for unaligned pointers and small inputs.
 //
 // Background reading in the reference tree: slides/Lecture16.pdf slides 19-27 (warp scan,
 // block scan), slides/Lecture21.pdf (head-flag segmented scan), my-refs/nvr-2008-003.pdf
@@ -25,13 +34,10 @@
 // reference; its multi-level up-sweep/down-sweep costs a second pass over the data.
 #pragma once
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace cme213 {
 namespace scan {
-
-constexpr int THREADS = 256;
-constexpr int WARPS = THREADS / 32;
-constexpr int VECS = 4;  // 16-byte vectors per thread; WARPS * VECS must be 32
 
 constexpr unsigned ST_INVALID = 0, ST_AGG = 1, ST_PREFIX = 2;
 
@@ -79,6 +85,37 @@ __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p) {
 }
 __device__ __forceinline__ void st_release_u32(unsigned *p, unsigned v) {
     asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// ---- mbarrier / bulk-copy primitives (sm_90+; the linear mode of the TMA engine) ------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_load(void *smem_dst, const void *gmem_src, unsigned bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
 }
 
 template <typename T, int BYTES = sizeof(T)> struct Desc;
@@ -133,47 +170,141 @@ __device__ __forceinline__ T warp_scan_inclusive(T x, int lane, int lo) {
     return x;
 }
 
+// Decoupled look-back of `tile` (> 0) by one warp.  Each lane inspects DPL predecessor descriptors per
+// round (a window of 32*DPL tiles, nearest predecessor first: lane l holds tiles tile-1-l*DPL-q), spins
+// until all of them are published, and the warp sums everything up to and including the nearest
+// terminator: a tile that already carries its inclusive prefix, or (segmented) one that contains a
+// segment head -- nothing older can reach this tile.  Returns the exclusive prefix in every lane.
+template <typename T, bool SEG, int DPL>
+__device__ __forceinline__ T lookback(const Scratch &scratch, int64_t tile, int lane) {
+    T carry = T(0);
+    int64_t base = tile - 1;
+    while (true) {
+        unsigned st[DPL], df[DPL];
+        T dv[DPL];
+        bool invalid;
+        do {
+            invalid = false;
+#pragma unroll
+            for (int q = 0; q < DPL; q++) {
+                const int64_t pred = base - (int64_t)lane * DPL - q;
+                if (pred >= 0) {
+                    Desc<T>::read(scratch, pred, st[q], dv[q], df[q]);
+                } else {
+                    st[q] = ST_PREFIX; dv[q] = T(0); df[q] = 0;
+                }
+                invalid |= st[q] == ST_INVALID;
+            }
+        } while (__any_sync(0xFFFFFFFFu, invalid));
+        // lane-local: nearest first, older values go on the left of the sum
+        T c = T(0);
+        bool found = false;
+#pragma unroll
+        for (int q = 0; q < DPL; q++) {
+            if (!found) {
+                c = dv[q] + c;
+                found = st[q] == ST_PREFIX || (SEG && df[q]);
+            }
+        }
+        const unsigned term = __ballot_sync(0xFFFFFFFFu, found);
+        const int first = term ? __ffs(term) - 1 : 31;
+        if (lane > first) c = T(0);
+        // inside the window only the terminator itself may contain a head, so a plain tree sum with
+        // the older lanes on the left is the segmented sum
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            T o = __shfl_down_sync(0xFFFFFFFFu, c, d);
+            if (lane + d < 32) c = o + c;
+        }
+        carry = c + carry;
+        if (term) break;
+        base -= 32 * DPL;
+    }
+    return __shfl_sync(0xFFFFFFFFu, carry, 0);
+}
+
 // Policy concept:
 //   using T; using Aux (per-vector state carried from load to store, may be empty);
 //   static constexpr int IPV (items per 16-byte vector); static constexpr bool SEG;
+//   static constexpr int NIN;  number of input arrays streamed through shared memory by the bulk kernel
+//   static constexpr int in_bytes(int s);  element size of input stream s
+//   const void *in_ptr(int s) const;       its base pointer
 //   __device__ void load(int64_t idx, int64_t n, bool fast, T (&v)[IPV], unsigned &head, Aux &aux) const;
+//       from global memory; `fast` = whole tile in range and 16-byte vector accesses allowed
+//   __device__ void load_smem(const unsigned char *const (&in)[NIN], int vec, int nvec, int64_t idx, int64_t n,
+//                             T (&v)[IPV], unsigned &head, Aux &aux) const;
+//       from the staged copies: in[s] is stream s of this tile, `vec` the vector's index in the tile
 //   __device__ void store(int64_t idx, int64_t n, bool fast, const T (&incl)[IPV], const T (&excl)[IPV],
 //                         const Aux &aux) const;
-// `idx` is the index of the first item of the vector (a multiple of IPV); `fast` means the whole
-// tile is in range and vector accesses are allowed.  Out-of-range items must load as 0 / no flag.
-template <class P>
-__global__ void __launch_bounds__(THREADS)
-lookback_scan_kernel(P p, int64_t n, Scratch scratch, int vec_ok) {
+// `idx` is the index of the first item of the vector (a multiple of IPV).  Out-of-range items must
+// load as 0 / no flag.
+
+// Shared state of the per-tile core.
+template <class P, int THREADS, int VECS> struct CoreSmem {
+    static constexpr int NAGG = (THREADS / 32) * VECS;
+    typename P::T agg_v[NAGG];
+    typename P::T excl_v[NAGG];       // exclusive prefix over aggregates [0, g) since the last head
+    typename P::T carry;
+    unsigned char agg_f[NAGG];
+    unsigned char excl_f[NAGG];       // any head among aggregates [0, g)
+};
+
+// One warp scans 32*PL (flag, value) entries held PL per lane in order (lane l owns entries
+// l*PL .. l*PL+PL-1).  hb bit k set = entry k starts (or contains) a segment head.  Outputs, per
+// entry: the exclusive prefix since the last head, and whether any head precedes it; plus the
+// inclusive total since the last head and whether any head exists at all (same in every lane).
+template <typename T, bool SEG, int PL>
+__device__ __forceinline__ void warp_array_scan(const T (&a)[PL], unsigned hb, int lane, T (&excl)[PL],
+                                                unsigned &head_before, T &total, bool &any_head) {
+    T inc[PL];
+    unsigned fb = 0;  // bit k: a head among this lane's entries [0, k]
+    T run = T(0);
+#pragma unroll
+    for (int k = 0; k < PL; k++) {
+        const bool f = SEG && ((hb >> k) & 1u);
+        run = (k == 0 || f) ? a[k] : run + a[k];
+        if (f) fb |= 0xFFFFFFFFu << k;
+        inc[k] = run;
+    }
+    const unsigned m = SEG ? __ballot_sync(0xFFFFFFFFu, fb != 0) : 0u;
+    const int lo = SEG ? 31 - __clz(m & (0xFFFFFFFFu >> (31 - lane))) : -1;
+    const T tot = warp_scan_inclusive<T, SEG>(run, lane, lo);
+    total = __shfl_sync(0xFFFFFFFFu, tot, 31);
+    any_head = m != 0;
+    T prev = __shfl_up_sync(0xFFFFFFFFu, tot, 1);
+    if (lane == 0) prev = T(0);
+    const bool head_prev = SEG && (m & ((1u << lane) - 1u)) != 0;
+    head_before = 0;
+#pragma unroll
+    for (int k = 0; k < PL; k++) {
+        const bool head_in_lane = k > 0 && ((fb >> (k - 1)) & 1u);
+        T e = prev;
+        if (k > 0) e = head_in_lane ? inc[k - 1] : prev + inc[k - 1];
+        excl[k] = e;
+        if (head_prev || head_in_lane) head_before |= 1u << k;
+    }
+}
+
+// Steps 2-3 of the header comment.  On return cst[i] is the value to add in front of vector i's first
+// item (already reset where a head precedes it).  `between` runs after the first barrier on every
+// thread (the bulk kernel refills its ring there).  `get_carry(tile_agg, tile_has_head)` is called by
+// warp 0 (all lanes) once the tile aggregate is known and returns the tile's exclusive prefix: the
+// two front ends differ only there (decoupled look-back vs. one scanner per wave).
+template <class P, int THREADS, int VECS, class Between, class GetCarry>
+__device__ __forceinline__ void tile_core(CoreSmem<P, THREADS, VECS> &sm, const typename P::T (&v)[VECS][P::IPV],
+                                          const unsigned (&hf)[VECS], typename P::T (&cst)[VECS], Between between,
+                                          GetCarry get_carry) {
     using T = typename P::T;
     constexpr int IPV = P::IPV;
     constexpr bool SEG = P::SEG;
-    constexpr int64_t TILE_ITEMS = (int64_t)THREADS * VECS * IPV;
-    static_assert(WARPS * VECS == 32, "warp aggregates must fill exactly one warp");
-
-    __shared__ unsigned s_tile;
-    __shared__ T s_wagg_v[32];
-    __shared__ unsigned s_wagg_f[32];
-    __shared__ T s_carry;
-
+    constexpr int WARPS = THREADS / 32;
+    constexpr int NAGG = WARPS * VECS;
+    constexpr int PL = NAGG / 32;
+    static_assert(NAGG % 32 == 0, "warp aggregates must fill whole lanes of one warp");
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) s_tile = atomicAdd(scratch.ticket, 1u);
-    __syncthreads();
-    const int64_t tile = s_tile;
-    const int64_t tile_base = tile * TILE_ITEMS;
-    const bool fast = vec_ok && (tile_base + TILE_ITEMS <= n);
 
-    // ---- 1. load -------------------------------------------------------------------------
-    T v[VECS][IPV];
-    unsigned hf[VECS];
-    typename P::Aux aux[VECS];
-#pragma unroll
-    for (int i = 0; i < VECS; i++) {
-        const int64_t idx = tile_base + ((int64_t)i * THREADS + tid) * IPV;
-        p.load(idx, n, fast, v[i], hf[i], aux[i]);
-    }
-    // ---- 2. per-thread aggregates, warp scans -------------------------------------------------
-    T wv[VECS];          // inclusive scan of thread aggregates within the warp
-    unsigned wm[VECS];   // ballot of "this thread's vector contains a head"
+    T wv[VECS];
+    unsigned wm[VECS];
 #pragma unroll
     for (int i = 0; i < VECS; i++) {
         T a = v[i][0];
@@ -184,76 +315,38 @@ lookback_scan_kernel(P p, int64_t n, Scratch scratch, int vec_ok) {
         wv[i] = warp_scan_inclusive<T, SEG>(a, lane, lo);
         wm[i] = m;
         if (lane == 31) {
-            s_wagg_v[i * WARPS + warp] = wv[i];
-            s_wagg_f[i * WARPS + warp] = (m != 0);
+            sm.agg_v[i * WARPS + warp] = wv[i];
+            sm.agg_f[i * WARPS + warp] = (unsigned char)(m != 0);
         }
     }
     __syncthreads();
-    // ---- 3. scan of the 32 warp aggregates (every warp, redundantly) --------------------------
-    const T gv = s_wagg_v[lane];
-    const unsigned gm = SEG ? __ballot_sync(0xFFFFFFFFu, s_wagg_f[lane] != 0) : 0u;
-    const int glo = SEG ? 31 - __clz(gm & (0xFFFFFFFFu >> (31 - lane))) : -1;
-    const T ginc = warp_scan_inclusive<T, SEG>(gv, lane, glo);
-    const T tile_agg = __shfl_sync(0xFFFFFFFFu, ginc, 31);
-    const unsigned tile_f = (gm != 0);
-
-    // ---- 4. decoupled look-back (warp 0) ------------------------------------------------------
+    between();
     if (warp == 0) {
-        T carry = T(0);
-        if (tile == 0) {
-            if (lane == 0) Desc<T>::publish(scratch, 0, ST_PREFIX, tile_agg, tile_f);
-        } else {
-            if (lane == 0) Desc<T>::publish(scratch, tile, ST_AGG, tile_agg, tile_f);
-            int64_t base = tile - 1;
-            while (true) {
-                const int64_t pred = base - lane;
-                unsigned st;
-                T dv;
-                unsigned df;
-                do {
-                    if (pred >= 0) {
-                        Desc<T>::read(scratch, pred, st, dv, df);
-                    } else {
-                        st = ST_PREFIX; dv = T(0); df = 0;
-                    }
-                } while (__any_sync(0xFFFFFFFFu, st == ST_INVALID));
-                // a predecessor ends the walk if it carries a full prefix, or (segmented) if it
-                // contains a segment head: nothing older can reach this tile.
-                const unsigned term = __ballot_sync(0xFFFFFFFFu, st == ST_PREFIX || (SEG && df));
-                const int first = term ? __ffs(term) - 1 : 31;
-                T c = lane <= first ? dv : T(0);
-                // lanes 0..first hold tiles base..base-first (newest first); inside that window
-                // only the oldest may contain a head, so a plain tree sum (older on the left) is
-                // the segmented sum.
+        T a[PL], e[PL];
+        unsigned hb = 0, before;
 #pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {
-                    T o = __shfl_down_sync(0xFFFFFFFFu, c, d);
-                    if (lane + d < 32) c = o + c;
-                }
-                carry = c + carry;
-                if (term) break;
-                base -= 32;
-            }
-            carry = __shfl_sync(0xFFFFFFFFu, carry, 0);
-            if (lane == 0) {
-                const T inc = (SEG && tile_f) ? tile_agg : carry + tile_agg;
-                Desc<T>::publish(scratch, tile, ST_PREFIX, inc, tile_f);
-            }
+        for (int k = 0; k < PL; k++) {
+            a[k] = sm.agg_v[lane * PL + k];
+            if (SEG && sm.agg_f[lane * PL + k]) hb |= 1u << k;
         }
-        if (lane == 0) s_carry = carry;
+        T tile_agg;
+        bool tile_f;
+        warp_array_scan<T, SEG, PL>(a, hb, lane, e, before, tile_agg, tile_f);
+        const T carry = get_carry(tile_agg, tile_f);  // publishes the aggregate first: successors wait for it
+#pragma unroll
+        for (int k = 0; k < PL; k++) {
+            sm.excl_v[lane * PL + k] = e[k];
+            sm.excl_f[lane * PL + k] = (unsigned char)((before >> k) & 1u);
+        }
+        if (lane == 0) sm.carry = carry;
     }
     __syncthreads();
-    const T carry_tile = s_carry;
-
-    // ---- 5. finish in registers and store -----------------------------------------------------
+    const T carry_tile = sm.carry;
 #pragma unroll
     for (int i = 0; i < VECS; i++) {
-        const int g = i * WARPS + warp;  // position of this warp's aggregate in the tile order
-        // exclusive prefix over the warp aggregates before g, and whether any of them had a head
-        T e = __shfl_sync(0xFFFFFFFFu, ginc, g > 0 ? g - 1 : 0);
-        if (g == 0) e = T(0);
-        const bool head_before_warp = SEG && (gm & ((1u << g) - 1u)) != 0;
-        // exclusive prefix over the lanes before this one inside the warp
+        const int g = i * WARPS + warp;
+        const T e = sm.excl_v[g];
+        const bool head_before_warp = SEG && sm.excl_f[g];
         T w = __shfl_up_sync(0xFFFFFFFFu, wv[i], 1);
         if (lane == 0) w = T(0);
         const bool head_before_lane = SEG && (wm[i] & ((1u << lane) - 1u)) != 0;
@@ -262,48 +355,398 @@ lookback_scan_kernel(P p, int64_t n, Scratch scratch, int vec_ok) {
             c = e + c;
             if (!head_before_warp) c = carry_tile + c;
         }
+        cst[i] = c;
+    }
+}
+
+template <class P, int VECS>
+__device__ __forceinline__ void finish_and_store(const P &p, int64_t tile_base, int threads, int64_t n, bool fast,
+                                                 const typename P::T (&v)[VECS][P::IPV], const unsigned (&hf)[VECS],
+                                                 const typename P::T (&cst)[VECS], const typename P::Aux (&aux)[VECS]) {
+    using T = typename P::T;
+    constexpr int IPV = P::IPV;
+#pragma unroll
+    for (int i = 0; i < VECS; i++) {
+        T c = cst[i];
         T incl[IPV], excl[IPV];
 #pragma unroll
         for (int j = 0; j < IPV; j++) {
-            if (SEG && ((hf[i] >> j) & 1u)) c = T(0);
+            if (P::SEG && ((hf[i] >> j) & 1u)) c = T(0);
             excl[j] = c;
             c = c + v[i][j];
             incl[j] = c;
         }
-        const int64_t idx = tile_base + ((int64_t)i * THREADS + tid) * IPV;
+        const int64_t idx = tile_base + ((int64_t)i * threads + threadIdx.x) * IPV;
         p.store(idx, n, fast, incl, excl, aux[i]);
+    }
+}
+
+// ---- front end 1: one CTA per tile, direct loads, decoupled look-back ----------------------------------
+template <class P, int THREADS, int VECS, int MIN_BLOCKS>
+__global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
+lookback_scan_kernel(P p, int64_t n, Scratch scratch, int vec_ok) {
+    using T = typename P::T;
+    constexpr int IPV = P::IPV;
+    constexpr bool SEG = P::SEG;
+    constexpr int64_t TILE_ITEMS = (int64_t)THREADS * VECS * IPV;
+    __shared__ unsigned s_tile;
+    __shared__ CoreSmem<P, THREADS, VECS> core;
+    const int tid = threadIdx.x, lane = tid & 31;
+    if (tid == 0) s_tile = atomicAdd(scratch.ticket, 1u);
+    __syncthreads();
+    const int64_t tile = s_tile;
+    const int64_t tile_base = tile * TILE_ITEMS;
+    const bool fast = vec_ok && (tile_base + TILE_ITEMS <= n);
+    T v[VECS][IPV];
+    unsigned hf[VECS];
+    typename P::Aux aux[VECS];
+#pragma unroll
+    for (int i = 0; i < VECS; i++) p.load(tile_base + ((int64_t)i * THREADS + tid) * IPV, n, fast, v[i], hf[i], aux[i]);
+    T cst[VECS];
+    tile_core<P, THREADS, VECS>(core, v, hf, cst, [] {}, [&](T tile_agg, bool tile_f) -> T {
+        if (lane == 0) Desc<T>::publish(scratch, tile, tile == 0 ? ST_PREFIX : ST_AGG, tile_agg, tile_f);
+        if (tile == 0) return T(0);
+        const T carry = lookback<T, SEG, 1>(scratch, tile, lane);
+        if (lane == 0) Desc<T>::publish(scratch, tile, ST_PREFIX, (SEG && tile_f) ? tile_agg : carry + tile_agg, tile_f);
+        return carry;
+    });
+    finish_and_store<P, VECS>(p, tile_base, THREADS, n, fast, v, hf, cst, aux);
+}
+
+// ---- front end 2: persistent CTAs, ring of bulk-async-copied tiles, one scanner per wave ----------------
+template <class P, int THREADS, int VECS> struct BulkLayout {
+    static constexpr int TILE_VECS = THREADS * VECS;
+    static constexpr int TILE_ITEMS = TILE_VECS * P::IPV;
+    __host__ __device__ static constexpr int stream_off(int s) {
+        int o = 0;
+        for (int i = 0; i < s; i++) o += TILE_ITEMS * P::in_bytes(i);
+        return o;
+    }
+    static constexpr int STAGE_BYTES = stream_off(P::NIN);
+};
+
+// Cross-CTA state of the wave protocol: slot arrays of {value, flag, ready}.
+//   A[tile]  aggregate of the tile (written by its owner)
+//   X[tile]  exclusive prefix of the tile (written by the wave's scanner)
+//   W[wave]  inclusive prefix at the end of the wave (written by the wave's scanner)
+// 4-byte values live in one 64-bit word (value | flag<<32 | ready<<33, one relaxed store publishes
+// it); 8-byte values in two such words, one per half.
+struct SlotArr {
+    unsigned long long *val;
+};
+struct WaveScratch {
+    SlotArr A, X, W;
+    unsigned long long *trace;  // debug only (CME213_SCAN_TRACE): per CTA, per wave, 8 globaltimer stamps
+};
+constexpr int TRACE_MAX_IT = 256;
+static inline size_t wave_scratch_bytes(int64_t tiles, int64_t waves, int value_bytes) {
+    const size_t t = (size_t)((tiles + 63) & ~(int64_t)63), w = (size_t)((waves + 63) & ~(int64_t)63);
+    return (2 * t + w) * (value_bytes == 4 ? 8 : 16);
+}
+static inline WaveScratch wave_scratch_carve(void *base, int64_t tiles, int64_t waves, int value_bytes) {
+    const size_t t = (size_t)((tiles + 63) & ~(int64_t)63);
+    const size_t per = value_bytes == 4 ? 1 : 2;
+    WaveScratch s;
+    s.A.val = (unsigned long long *)base;
+    s.X.val = s.A.val + t * per;
+    s.W.val = s.X.val + t * per;
+    s.trace = nullptr;
+    (void)waves;
+    return s;
+}
+
+template <typename T, int BYTES = sizeof(T)> struct Slot;
+template <typename T> struct Slot<T, 4> {
+    __device__ static void publish(const SlotArr &s, int64_t i, T v, unsigned f) {
+        unsigned bits;
+        memcpy(&bits, &v, 4);
+        st_relaxed_u64(s.val + i, (unsigned long long)bits | ((unsigned long long)(f & 1u) << 32) | (1ull << 33));
+    }
+    __device__ static bool read(const SlotArr &s, int64_t i, T &v, unsigned &f) {
+        const unsigned long long d = ld_relaxed_u64(s.val + i);
+        const unsigned bits = (unsigned)d;
+        memcpy(&v, &bits, 4);
+        f = (unsigned)(d >> 32) & 1u;
+        return (d >> 33) & 1ull;
+    }
+};
+template <typename T> struct Slot<T, 8> {
+    // two self-validating words (low half | ready, high half | flag | ready): no ordering between them
+    // is needed, so no release store -- a fence here would wait for the CTA's data stores still in flight.
+    __device__ static void publish(const SlotArr &s, int64_t i, T v, unsigned f) {
+        unsigned long long bits;
+        memcpy(&bits, &v, 8);
+        st_relaxed_u64(s.val + 2 * i, (bits & 0xFFFFFFFFull) | (1ull << 33));
+        st_relaxed_u64(s.val + 2 * i + 1, (bits >> 32) | ((unsigned long long)(f & 1u) << 32) | (1ull << 33));
+    }
+    __device__ static bool read(const SlotArr &s, int64_t i, T &v, unsigned &f) {
+        const unsigned long long lo = ld_relaxed_u64(s.val + 2 * i), hi = ld_relaxed_u64(s.val + 2 * i + 1);
+        const unsigned long long bits = (lo & 0xFFFFFFFFull) | (hi << 32);
+        memcpy(&v, &bits, 8);
+        f = (unsigned)(hi >> 32) & 1u;
+        return ((lo >> 33) & (hi >> 33) & 1ull) != 0;
+    }
+};
+
+// Tiles are dealt round-robin: CTA b handles tiles b, b+G, b+2G, ...  (G = gridDim.x <= 32*DPL), so
+// "wave" w = tiles [wG, (w+1)G) is worked on by all CTAs at the same time; they are co-resident
+// (cooperative launch).  Every CTA publishes its tile aggregate; one CTA per wave (the job rotates)
+// waits for the wave's G aggregates, scans them (one warp, coalesced reads, nobody else reads them),
+// adds the running prefix of the previous wave and hands every tile its exclusive prefix.  Each CTA
+// then polls only its own slot.  All cross-CTA words carry their own ready bit, so no fence or
+// atomic is needed (a fence would stall on the CTA's data stores that are still in flight).  Compared with every tile walking back over its
+// predecessors' descriptors this keeps the L2 lines holding the descriptors from becoming a
+// hot spot: with all tiles of a wave arriving together, 148 warps re-reading the same few lines
+// took ~15 us per round trip (profiles/r01_notes.md).
+template <class P, int THREADS, int VECS, int STAGES, int DPL>
+__global__ void __launch_bounds__(THREADS, (THREADS <= 512 ? 2 : 1))
+lookback_scan_bulk_kernel(P p, int64_t n, int64_t num_tiles, WaveScratch ws) {
+    using T = typename P::T;
+    using L = BulkLayout<P, THREADS, VECS>;
+    constexpr int IPV = P::IPV;
+    constexpr bool SEG = P::SEG;
+    extern __shared__ __align__(128) unsigned char ring[];  // STAGES * STAGE_BYTES
+    __shared__ __align__(8) uint64_t full_bar[STAGES];
+    __shared__ CoreSmem<P, THREADS, VECS> core;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const bool filler = tid == THREADS - 32;                 // lane 0 of the last warp feeds the ring
+    const int64_t G = gridDim.x;
+
+    // start the copies of tile t into `stage`
+    auto fill = [&](int stage, int64_t t) {
+        if (t >= num_tiles) return;
+        const int64_t base = t * L::TILE_ITEMS;
+        if (base + L::TILE_ITEMS <= n) {
+            mbar_expect_tx(&full_bar[stage], (unsigned)L::STAGE_BYTES);
+#pragma unroll
+            for (int s = 0; s < P::NIN; s++)
+                bulk_load(ring + (size_t)stage * L::STAGE_BYTES + L::stream_off(s),
+                          (const unsigned char *)p.in_ptr(s) + base * P::in_bytes(s), (unsigned)(L::TILE_ITEMS * P::in_bytes(s)),
+                          &full_bar[stage]);
+        } else {
+            mbar_arrive(&full_bar[stage]);  // ragged last tile: read straight from global with guards
+        }
+    };
+
+    if (filler) {
+        for (int s = 0; s < STAGES; s++) mbar_init(&full_bar[s], 1);
+        mbar_fence_init();
+        for (int s = 0; s < STAGES; s++) fill(s, (int64_t)s * G + blockIdx.x);
+    }
+    __syncthreads();
+
+    auto stamp = [&](int it, int k) {
+        if (ws.trace && tid == 0 && it < TRACE_MAX_IT) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            ws.trace[((size_t)blockIdx.x * TRACE_MAX_IT + it) * 8 + k] = t;
+        }
+    };
+    int it = 0;
+    for (int64_t tile = blockIdx.x; tile < num_tiles; tile += G, it++) {
+        const int stage = it % STAGES;
+        const int64_t tile_base = tile * L::TILE_ITEMS;
+        const bool full = tile_base + L::TILE_ITEMS <= n;
+        stamp(it, 0);
+        mbar_wait(&full_bar[stage], (unsigned)((it / STAGES) & 1));
+        stamp(it, 1);
+        T v[VECS][IPV];
+        unsigned hf[VECS];
+        typename P::Aux aux[VECS];
+        if (full) {
+            const unsigned char *in[P::NIN];
+#pragma unroll
+            for (int s = 0; s < P::NIN; s++) in[s] = ring + (size_t)stage * L::STAGE_BYTES + L::stream_off(s);
+#pragma unroll
+            for (int i = 0; i < VECS; i++) {
+                const int vec = i * THREADS + tid;
+                p.load_smem(in, vec, L::TILE_VECS, tile_base + (int64_t)vec * IPV, n, v[i], hf[i], aux[i]);
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < VECS; i++) p.load(tile_base + ((int64_t)i * THREADS + tid) * IPV, n, false, v[i], hf[i], aux[i]);
+        }
+        T cst[VECS];
+        const int64_t wave = it, wave_first = wave * G;
+        const int64_t wave_cnt = num_tiles - wave_first < G ? num_tiles - wave_first : G;
+        tile_core<P, THREADS, VECS>(
+            core, v, hf, cst,
+            // after the core's first barrier every thread holds its inputs in registers: the stage is free
+            [&] { if (filler) fill(stage, tile + (int64_t)STAGES * G); },
+            [&](T tile_agg, bool tile_f) -> T {
+                stamp(it, 2);
+                if (lane == 0) Slot<T>::publish(ws.A, tile, tile_agg, tile_f);
+                stamp(it, 3);
+                if ((int64_t)blockIdx.x == wave % wave_cnt) {
+                    // this wave's scanner (the job rotates over the CTAs that have a tile in the wave): wait for the aggregates,
+                    // scan them for everybody.  One warp, coalesced reads, nobody else reads them.
+                    T a[DPL], e[DPL];
+                    unsigned hb = 0, before;
+                    bool pending;
+                    do {
+                        pending = false;
+#pragma unroll
+                        for (int q = 0; q < DPL; q++) {
+                            const int64_t j = (int64_t)lane * DPL + q;
+                            a[q] = T(0);
+                            if (j < wave_cnt) {
+                                unsigned f;
+                                pending |= !Slot<T>::read(ws.A, wave_first + j, a[q], f);
+                                if (SEG && f) hb |= 1u << q; else hb &= ~(1u << q);
+                            }
+                        }
+                    } while (__any_sync(0xFFFFFFFFu, pending));
+                    T c0 = T(0);  // running prefix (since the last head) at the end of the previous wave
+                    if (wave > 0) {
+                        unsigned f;
+                        while (!Slot<T>::read(ws.W, wave - 1, c0, f)) {}
+                    }
+                    T total;
+                    bool any;
+                    warp_array_scan<T, SEG, DPL>(a, hb, lane, e, before, total, any);
+#pragma unroll
+                    for (int q = 0; q < DPL; q++) {
+                        const int64_t j = (int64_t)lane * DPL + q;
+                        if (j < wave_cnt) Slot<T>::publish(ws.X, wave_first + j, ((before >> q) & 1u) ? e[q] : c0 + e[q], 0);
+                    }
+                    if (lane == 0) Slot<T>::publish(ws.W, wave, any ? total : c0 + total, 0);
+                    stamp(it, 4);
+                }
+                T carry;
+                unsigned f;
+                while (!Slot<T>::read(ws.X, tile, carry, f)) {}
+                stamp(it, 5);
+                return carry;
+            });
+        stamp(it, 6);
+        finish_and_store<P, VECS>(p, tile_base, THREADS, n, full, v, hf, cst, aux);
+        stamp(it, 7);
     }
 }
 #endif  // __CUDACC__
 
-template <class P> static inline int64_t tile_items() { return (int64_t)THREADS * VECS * P::IPV; }
+// Tile configuration (tuned on B200, see profiles/r01_notes.md).
+template <class P> struct Cfg {
+    static constexpr int THREADS = 1024;                       // bulk kernel: one CTA per SM
+    static constexpr int VEC_BYTES = BulkLayout<P, 1, 1>::STAGE_BYTES;            // staged bytes per 16-byte value vector
+    static constexpr int VECS = (96 * 1024) / (THREADS * VEC_BYTES);              // ~96 KiB per stage whatever is streamed
+    static constexpr int STAGES = 2;
+    static constexpr int DPL = 5;                               // a wave holds at most 32*DPL = 160 tiles
+    static constexpr int DIRECT_THREADS = 256, DIRECT_VECS = 4; // one-tile-per-CTA kernel
+};
 
-// Host launcher: clear + carve the scratch, launch one CTA per tile.  `scratch` must hold
-// scratch_bytes(tiles, sizeof(T)) bytes; launch() takes it from the context workspace.
-template <class P>
-int launch_with_scratch(cme213_ctx *ctx, const P &p, int64_t n, bool vec_ok, cudaStream_t st, const char *name,
-                        void *scratch_mem) {
+// ---- host launchers ----------------------------------------------------------------------------------
+// `scratch_mem` must hold scratch_bytes(tiles, sizeof(T)) bytes, or be null to use the context workspace.
+template <class P, int THREADS, int VECS, int MIN_BLOCKS>
+int launch_direct(cme213_ctx *ctx, const P &p, int64_t n, bool vec_ok, cudaStream_t st, const char *name,
+                  void *scratch_mem) {
     using T = typename P::T;
-    const int64_t tiles = div_up(n, tile_items<P>());
+    const int64_t tiles = div_up(n, (int64_t)THREADS * VECS * P::IPV);
     if (tiles > 0x7FFFFFFFLL) { set_error("%s: n too large", name); return CME213_ERR_UNSUPPORTED; }
-    const size_t bytes = scratch_bytes(tiles, sizeof(T));
-    CME213_CUDA(cudaMemsetAsync(scratch_mem, 0, bytes, st));
+    if (!scratch_mem) {
+        int rc = workspace(ctx, scratch_bytes(tiles, sizeof(T)), &scratch_mem);
+        if (rc) return rc;
+    }
+    CME213_CUDA(cudaMemsetAsync(scratch_mem, 0, scratch_bytes(tiles, sizeof(T)), st));
     Scratch s = scratch_carve(scratch_mem, tiles, sizeof(T));
 #ifdef __CUDACC__
-    lookback_scan_kernel<P><<<(unsigned)tiles, THREADS, 0, st>>>(p, n, s, vec_ok ? 1 : 0);
+    lookback_scan_kernel<P, THREADS, VECS, MIN_BLOCKS><<<(unsigned)tiles, THREADS, 0, st>>>(p, n, s, vec_ok ? 1 : 0);
 #endif
     CME213_LAUNCHED(ctx, name);
     return CME213_OK;
 }
 
+template <class P, int THREADS, int VECS, int STAGES, int DPL>
+int launch_bulk(cme213_ctx *ctx, const P &p, int64_t n, cudaStream_t st, const char *name, void *scratch_mem,
+                size_t scratch_avail) {
+    using T = typename P::T;
+    using L = BulkLayout<P, THREADS, VECS>;
+    int64_t tiles = div_up(n, (int64_t)L::TILE_ITEMS);
+    if (tiles > 0x7FFFFFFFLL) { set_error("%s: n too large", name); return CME213_ERR_UNSUPPORTED; }
+#ifdef __CUDACC__
+    auto kern = lookback_scan_bulk_kernel<P, THREADS, VECS, STAGES, DPL>;
+    const int smem = STAGES * L::STAGE_BYTES;
+    static int per_sm_dev[64] = {0};  // per instantiation and device: resident CTAs per SM
+    int &per_sm = per_sm_dev[ctx->device & 63];
+    if (per_sm == 0) {
+        CME213_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        CME213_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        CME213_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, THREADS, smem));
+        if (per_sm < 1) { set_error("%s: kernel does not fit on an SM", name); per_sm = 0; return CME213_ERR_UNSUPPORTED; }
+    }
+    int64_t grid = (int64_t)per_sm * ctx->sm_count;   // all co-resident (cooperative launch checks it)
+    if (grid > 32 * DPL) grid = 32 * DPL;              // one warp scans a whole wave
+    if (grid > tiles) grid = tiles;
+    const int64_t waves = div_up(tiles, grid);
+    const size_t bytes = wave_scratch_bytes(tiles, waves, sizeof(T));
+    if (!scratch_mem) {
+        int rc = workspace(ctx, bytes, &scratch_mem);
+        if (rc) return rc;
+    } else if (bytes > scratch_avail) {
+        set_error("%s: scratch too small (%zu > %zu)", name, bytes, scratch_avail);
+        return CME213_ERR_INVALID;
+    }
+    CME213_CUDA(cudaMemsetAsync(scratch_mem, 0, bytes, st));
+    WaveScratch ws = wave_scratch_carve(scratch_mem, tiles, waves, sizeof(T));
+    static unsigned long long *d_trace = nullptr;
+    const bool tracing = getenv("CME213_SCAN_TRACE") != nullptr;
+    const size_t trace_words = (size_t)grid * TRACE_MAX_IT * 8;
+    if (tracing) {
+        if (!d_trace) CME213_CUDA(cudaMalloc(&d_trace, (size_t)1024 * TRACE_MAX_IT * 8 * 8));
+        CME213_CUDA(cudaMemsetAsync(d_trace, 0, trace_words * 8, st));
+        ws.trace = d_trace;
+    }
+    P pp = p;
+    void *args[] = {(void *)&pp, (void *)&n, (void *)&tiles, (void *)&ws};
+    CME213_CUDA(cudaLaunchCooperativeKernel((const void *)kern, dim3((unsigned)grid), dim3(THREADS), args, (size_t)smem, st));
+    if (tracing) {
+        // debug aid: average time between the stamps of the kernel, over all CTAs and waves
+        unsigned long long *h = (unsigned long long *)malloc(trace_words * 8);
+        CME213_CUDA(cudaStreamSynchronize(st));
+        CME213_CUDA(cudaMemcpy(h, d_trace, trace_words * 8, cudaMemcpyDeviceToHost));
+        double sum[8] = {0}; long cnt[8] = {0}; double iter = 0; long iters = 0;
+        long nit = waves < TRACE_MAX_IT ? (long)waves : TRACE_MAX_IT;
+        for (long c = 0; c < grid; c++)
+            for (long i = 1; i + 1 < nit; i++) {
+                unsigned long long *r = h + ((size_t)c * TRACE_MAX_IT + i) * 8, *nx = r + 8;
+                if (!r[0] || !r[7] || !nx[0]) continue;
+                iter += (double)(nx[0] - r[0]); iters++;
+                int prev = 0;
+                for (int k = 1; k < 8; k++) { if (!r[k]) continue; sum[k] += (double)(r[k] - r[prev]); cnt[k]++; prev = k; }
+            }
+        fprintf(stderr, "[scan trace] per_sm %d grid %ld waves %ld  ns/iter %.0f |", per_sm, (long)grid, (long)waves, iters ? iter / iters : 0.0);
+        const char *nm[8] = {"", "wait_data", "local+S1", "pub+atomic", "scanner", "poll", "S2+cst", "store"};
+        for (int k = 1; k < 8; k++) fprintf(stderr, " %s %.0f(n=%ld)", nm[k], cnt[k] ? sum[k] / cnt[k] : 0.0, cnt[k]);
+        fprintf(stderr, "\n");
+        free(h);
+    }
+#endif
+    CME213_LAUNCHED(ctx, name);
+    return CME213_OK;
+}
+
+// Upper bound of the scratch either front end needs for n items (callers that carve it themselves).
+template <class P> static inline size_t scratch_bytes_for(int64_t n) {
+    using T = typename P::T;
+    const int64_t dt = div_up(n > 0 ? n : 1, (int64_t)Cfg<P>::DIRECT_THREADS * Cfg<P>::DIRECT_VECS * P::IPV);
+    const size_t direct = scratch_bytes(dt, sizeof(T));
+    const size_t wave = wave_scratch_bytes(dt, dt, sizeof(T));  // generous: fewer, larger tiles in reality
+    return direct > wave ? direct : wave;
+}
+
+// Default dispatch: bulk pipeline when every streamed array is 16-byte aligned and the input is large,
+// direct kernel otherwise.
+template <class P>
+int launch_with_scratch(cme213_ctx *ctx, const P &p, int64_t n, bool vec_ok, cudaStream_t st, const char *name,
+                        void *scratch_mem, size_t scratch_avail) {
+    if (vec_ok && n >= (int64_t)1 << 20)
+        return launch_bulk<P, Cfg<P>::THREADS, Cfg<P>::VECS, Cfg<P>::STAGES, Cfg<P>::DPL>(ctx, p, n, st, name, scratch_mem, scratch_avail);
+    return launch_direct<P, Cfg<P>::DIRECT_THREADS, Cfg<P>::DIRECT_VECS, 1>(ctx, p, n, vec_ok, st, name, scratch_mem);
+}
+
 template <class P>
 int launch(cme213_ctx *ctx, const P &p, int64_t n, bool vec_ok, cudaStream_t st, const char *name) {
-    const int64_t tiles = div_up(n, tile_items<P>());
-    if (tiles > 0x7FFFFFFFLL) { set_error("%s: n too large", name); return CME213_ERR_UNSUPPORTED; }
-    void *ws = nullptr;
-    int rc = workspace(ctx, scratch_bytes(tiles, sizeof(typename P::T)), &ws);
-    if (rc) return rc;
-    return launch_with_scratch<P>(ctx, p, n, vec_ok, st, name, ws);
+    return launch_with_scratch<P>(ctx, p, n, vec_ok, st, name, nullptr, 0);
 }
 
 }  // namespace scan

@@ -1,6 +1,8 @@
 // scan.cu -- entry points built on the look-back scan: exclusive uint32 scan, (fused) segmented
 // scans of the final project, COO segmented reduction.
 #include "lookback_scan.cuh"
+#include <stdlib.h>
+#include <stdio.h>
 
 namespace {
 using namespace cme213;
@@ -32,10 +34,21 @@ struct PlainPolicy {
     using Aux = NoAux;
     static constexpr int IPV = 16 / sizeof(T);
     static constexpr bool SEG = SEG_;
+    static constexpr int NIN = 1;
+    __host__ __device__ static constexpr int in_bytes(int) { return (int)sizeof(T); }
     const T *in;
     T *out;
     const uint32_t *flag_bits;
+    __host__ __device__ const void *in_ptr(int) const { return in; }
 
+    __device__ void load_smem(const unsigned char *const (&sin)[NIN], int vec, int, int64_t idx, int64_t, T (&v)[IPV],
+                              unsigned &head, Aux &) const {
+        typename V16<T>::type x = *reinterpret_cast<const typename V16<T>::type *>(sin[0] + (size_t)vec * 16);
+        const T *e = reinterpret_cast<const T *>(&x);
+#pragma unroll
+        for (int j = 0; j < IPV; j++) v[j] = e[j];
+        head = SEG ? head_bits<IPV>(flag_bits, idx) : 0u;
+    }
     __device__ void load(int64_t idx, int64_t n, bool fast, T (&v)[IPV], unsigned &head, Aux &) const {
         head = 0;
         if (fast) {
@@ -79,12 +92,28 @@ struct MulGatherPolicy {
     using Aux = NoAux;
     static constexpr int IPV = 16 / sizeof(T);
     static constexpr bool SEG = true;
+    static constexpr int NIN = 2;
+    __host__ __device__ static constexpr int in_bytes(int s) { return s == 0 ? (int)sizeof(T) : 4; }
     const T *a;
     const int32_t *k;
     const T *x;
     const uint32_t *flag_bits;
     T *b;
+    __host__ __device__ const void *in_ptr(int s) const { return s == 0 ? (const void *)a : (const void *)k; }
 
+    __device__ void load_smem(const unsigned char *const (&sin)[NIN], int vec, int, int64_t idx, int64_t, T (&v)[IPV],
+                              unsigned &head, Aux &) const {
+        typename V16<T>::type av = *reinterpret_cast<const typename V16<T>::type *>(sin[0] + (size_t)vec * 16);
+        typename IdxVec<IPV>::type kv = *reinterpret_cast<const typename IdxVec<IPV>::type *>(sin[1] + (size_t)vec * IPV * 4);
+        const T *ae = reinterpret_cast<const T *>(&av);
+        const int *ke = reinterpret_cast<const int *>(&kv);
+        T xv[IPV];
+#pragma unroll
+        for (int j = 0; j < IPV; j++) xv[j] = __ldg(x + ke[j]);
+#pragma unroll
+        for (int j = 0; j < IPV; j++) v[j] = mul_rn(ae[j], xv[j]);
+        head = head_bits<IPV>(flag_bits, idx);
+    }
     __device__ void load(int64_t idx, int64_t n, bool fast, T (&v)[IPV], unsigned &head, Aux &) const {
         head = 0;
         if (fast) {
@@ -132,12 +161,41 @@ struct CooPolicy {
     static constexpr int IPV = 16 / sizeof(T);
     static constexpr bool SEG = true;
     struct Aux { int row[IPV]; int next; };
+    static constexpr int NIN = 3;
+    __host__ __device__ static constexpr int in_bytes(int s) { return s == 2 ? (int)sizeof(T) : 4; }
     const int32_t *row;
     const int32_t *col;
     const T *val;
     const T *x;
     T *y;
+    __host__ __device__ const void *in_ptr(int s) const {
+        return s == 0 ? (const void *)row : s == 1 ? (const void *)col : (const void *)val;
+    }
 
+    __device__ void load_smem(const unsigned char *const (&sin)[NIN], int vec, int nvec, int64_t idx, int64_t n,
+                              T (&v)[IPV], unsigned &head, Aux &aux) const {
+        const int *srow = reinterpret_cast<const int *>(sin[0]);
+        typename IdxVec<IPV>::type rv = *reinterpret_cast<const typename IdxVec<IPV>::type *>(sin[0] + (size_t)vec * IPV * 4);
+        typename IdxVec<IPV>::type cv = *reinterpret_cast<const typename IdxVec<IPV>::type *>(sin[1] + (size_t)vec * IPV * 4);
+        typename V16<T>::type vv = *reinterpret_cast<const typename V16<T>::type *>(sin[2] + (size_t)vec * 16);
+        const int *re = reinterpret_cast<const int *>(&rv);
+        const int *ce = reinterpret_cast<const int *>(&cv);
+        const T *ve = reinterpret_cast<const T *>(&vv);
+        T xv[IPV];
+#pragma unroll
+        for (int j = 0; j < IPV; j++) xv[j] = __ldg(x + ce[j]);
+        // neighbours across vector boundaries come from the staged tile; only the tile's two ends touch global
+        int prev = vec > 0 ? srow[vec * IPV - 1] : (idx > 0 ? __ldg(row + idx - 1) : -1);
+        aux.next = vec + 1 < nvec ? srow[(vec + 1) * IPV] : (idx + IPV < n ? __ldg(row + idx + IPV) : -1);
+        head = 0;
+#pragma unroll
+        for (int j = 0; j < IPV; j++) {
+            aux.row[j] = re[j];
+            v[j] = mul_rn(ve[j], xv[j]);
+            if (re[j] != prev) head |= 1u << j;
+            prev = re[j];
+        }
+    }
     __device__ void load(int64_t idx, int64_t n, bool fast, T (&v)[IPV], unsigned &head, Aux &aux) const {
         head = 0;
         int prev = (idx > 0 && idx - 1 < n) ? __ldg(row + idx - 1) : -1;
@@ -227,7 +285,23 @@ CME213_API int cme213_exclusive_scan_u32(cme213_ctx *ctx, const uint32_t *d_in, 
     if (n < 0 || (n > 0 && (!d_in || !d_out))) { set_error("exclusive_scan_u32: bad arguments"); return CME213_ERR_INVALID; }
     if (n == 0) return CME213_OK;
     PlainPolicy<uint32_t, false, false> p{d_in, d_out, nullptr};
-    return run(ctx, p, n, aligned16(d_in) && aligned16(d_out), stream, "exclusive_scan_u32");
+    const bool ok = aligned16(d_in) && aligned16(d_out);
+    if (const char *cfg = getenv("CME213_SCAN_CFG")) {  // tuning hook: "threads,vecs,stages" (stages 0 = direct kernel)
+        using P = PlainPolicy<uint32_t, false, false>;
+        DeviceGuard g(ctx->device);
+        cudaStream_t st = (cudaStream_t)stream;
+        int T_ = 0, V_ = 0, S_ = 0;
+        sscanf(cfg, "%d,%d,%d", &T_, &V_, &S_);
+#define CME213_TRY_BULK(T, V, S) if (T_ == T && V_ == V && S_ == S) return scan::launch_bulk<P, T, V, S, (T == 1024 ? 5 : 10)>(ctx, p, n, st, "scan", nullptr, 0);
+#define CME213_TRY_DIRECT(T, V) if (T_ == T && V_ == V && S_ == 0) return scan::launch_direct<P, T, V, 1>(ctx, p, n, ok, st, "scan", nullptr);
+        CME213_TRY_DIRECT(256, 4) CME213_TRY_DIRECT(1024, 8)
+        CME213_TRY_BULK(512, 4, 2) CME213_TRY_BULK(512, 4, 3) CME213_TRY_BULK(512, 6, 2) CME213_TRY_BULK(512, 8, 2) CME213_TRY_BULK(512, 8, 3)
+        CME213_TRY_BULK(1024, 4, 2) CME213_TRY_BULK(1024, 4, 3) CME213_TRY_BULK(1024, 6, 2) CME213_TRY_BULK(1024, 8, 1) CME213_TRY_BULK(1024, 2, 4)
+        CME213_TRY_BULK(1024, 3, 4) CME213_TRY_BULK(1024, 5, 2) CME213_TRY_BULK(1024, 7, 1)
+#undef CME213_TRY_BULK
+#undef CME213_TRY_DIRECT
+    }
+    return run(ctx, p, n, ok, stream, "exclusive_scan_u32");
 }
 
 template <typename T, bool INCLUSIVE>
@@ -300,8 +374,7 @@ CME213_API int cme213_spmv_coo_accumulate_f64(cme213_ctx *ctx, int64_t nnz, cons
 // ---- internal: scan with caller-provided scratch (see internal.cuh) ----------------------------------
 #include "internal.cuh"
 size_t cme213_internal_scan_u32_scratch_bytes(int64_t n) {
-    using P = PlainPolicy<uint32_t, false, false>;
-    return scan::scratch_bytes(div_up(n > 0 ? n : 1, scan::tile_items<P>()), 4);
+    return scan::scratch_bytes_for<PlainPolicy<uint32_t, false, false>>(n);
 }
 int cme213_internal_exclusive_scan_u32(cme213_ctx *ctx, const uint32_t *d_in, uint32_t *d_out, int64_t n,
                                        void *scratch, void *stream) {
@@ -309,5 +382,5 @@ int cme213_internal_exclusive_scan_u32(cme213_ctx *ctx, const uint32_t *d_in, ui
     DeviceGuard g(ctx->device);
     PlainPolicy<uint32_t, false, false> p{d_in, d_out, nullptr};
     return scan::launch_with_scratch(ctx, p, n, aligned16(d_in) && aligned16(d_out), (cudaStream_t)stream,
-                                     "exclusive_scan_u32", scratch);
+                                     "exclusive_scan_u32", scratch, cme213_internal_scan_u32_scratch_bytes(n));
 }

@@ -124,3 +124,22 @@ def test_hyb_split_and_spmv(ctx, cme):
     d_y2 = dev_empty(rows, np.float32)
     ctx.call("cme213_spmv_csr_f32", 0, rows, d_ptr, d_col, d_val, dev(x), d_y2, 3)
     assert np.array_equal(host(d_y2), oracle.csr_spmv(lp, col, val, x))
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_coo_segmented_reduction_bulk_path(ctx, dtype):
+    # >= 2^20 entries: persistent bulk-copy kernel; long rows cross tile boundaries, some rows are empty
+    nnz, rows = 3 * (1 << 20) + 7, 90000
+    rng = np.random.default_rng(5)
+    r = np.sort(rng.integers(0, rows, nnz)).astype(np.int32)
+    r[500000:900000] = r[500000]
+    r = np.sort(r)
+    c = rng.integers(0, rows, nnz).astype(np.int32)
+    v = rng.integers(-3, 4, nnz).astype(dtype)          # small integers: sums are exact in any order
+    x = rng.integers(-3, 4, rows).astype(dtype)
+    y0 = rng.integers(-3, 4, rows).astype(dtype)
+    d_y = dev(y0)
+    ctx.call("cme213_spmv_coo_accumulate_" + sfx(dtype), nnz, dev(r), dev(c), dev(v), dev(x), d_y)
+    want = y0.astype(np.float64) + np.bincount(r, v.astype(np.float64) * x[c], rows)
+    assert np.array_equal(host(d_y).astype(np.float64), want)
+    assert np.array_equal(host(d_y), oracle.coo_spmv_accumulate(r, c, v, x, y0))

@@ -200,3 +200,51 @@ def test_segscan_full_size_properties(ctx):
         want = torch.where(fl, vals[idx], prev + vals[idx])
         assert torch.equal(want, out[idx])
         del idx, fl, prev, want
+
+
+# ---- sizes that take the persistent bulk-copy kernel (>= 2^20 items), every policy -----------------------
+BIG = [(1 << 20), 3 * (1 << 20) + 5, 5 * 32768 * 31 + 4096]
+
+
+@pytest.mark.parametrize("n", BIG)
+def test_bulk_path_segscan_f32_f64(ctx, n):
+    flags = seg_inputs(n, "mean64", n)
+    flags[n // 3: n // 3 + 200000] = False  # one segment spanning several 16K-item tiles
+    s = g.flags_to_offsets(flags)
+    d_bits = dev(np.concatenate([g.pack_flags(flags), [0]]).astype(np.uint32))
+    ints = np.random.default_rng(n).integers(-4, 5, n)
+    for dt, fn in [(np.float32, "cme213_segscan_inclusive_f32"), (np.float64, "cme213_segscan_inclusive_f64")]:
+        d_out = dev_empty(n, dt)
+        ctx.call(fn, dev(ints.astype(dt)), d_bits, d_out, n)
+        assert np.array_equal(host(d_out), oracle.segscan_inclusive(ints.astype(dt), s))  # exact: small integers
+    d_out = dev_empty(n, np.float32)
+    ctx.call("cme213_segscan_exclusive_f32", dev(ints.astype(np.float32)), d_bits, d_out, n)
+    assert np.array_equal(host(d_out), oracle.segscan_inclusive(ints.astype(np.float32), s) - ints.astype(np.float32))
+    vals = np.random.default_rng(n + 1).uniform(-1, 1, n).astype(np.float32)
+    ctx.call("cme213_segscan_inclusive_f32", dev(vals), d_bits, d_out, n)
+    k, S = fp_bound(vals.astype(np.float64), flags)
+    assert np.all(np.abs(host(d_out) - oracle.segscan_inclusive(vals.astype(np.float64), s)) <= (k + 1) * 2.0 ** -24 * S + 1e-37)
+
+
+@pytest.mark.parametrize("dtype,fn,u", [(np.float32, "cme213_mul_gather_segscan_f32", 2.0 ** -24),
+                                         (np.float64, "cme213_mul_gather_segscan_f64", 2.0 ** -53)])
+@pytest.mark.parametrize("n", BIG[:2])
+def test_bulk_path_fused_step(ctx, dtype, fn, u, n):
+    a, s, k, x = g.fp_inputs(n, n // 50, 70001, seed=n % 1000, dtype=dtype)
+    flags = g.offsets_to_flags(s, n)
+    d_bits = dev(np.concatenate([g.pack_flags(flags), [0]]).astype(np.uint32))
+    d_a = dev(a)
+    ctx.call(fn, d_a, dev(k), dev(x), d_bits, d_a, n)  # in place
+    prod64 = a.astype(np.float64) * x[k].astype(np.float64)
+    kk, S = fp_bound(prod64, flags)
+    assert np.all(np.abs(host(d_a) - oracle.segscan_inclusive(prod64, s)) <= (kk + 2) * u * S + 1e-300)
+    # and the reference's own (float) CPU path agrees at the reference's tolerance
+    if dtype == np.float32:
+        norms = oracle.error_norms(oracle.fp_cpu_iterate(a, s, k, x, 1).astype(np.float64), host(d_a).astype(np.float64))
+        assert norms[2] < 1e-5
+
+
+def test_bulk_path_exclusive_scan_in_place_and_sizes(ctx):
+    for n in BIG + [(1 << 20) + 1, (1 << 22) - 3]:
+        x = np.random.default_rng(n).integers(0, 2**32, n, dtype=np.uint64).astype(np.uint32)
+        assert np.array_equal(gpu_exclusive_scan(ctx, x, in_place=True), oracle.exclusive_scan_u32(x))

@@ -1,0 +1,93 @@
+"""CPU tests (gloo, world_size 2 and 3) of the row-sharded iterate: partition, halo/full exchange and
+ping-pong logic of 2012-04_stanford_cme213_b200/sharded.py.  The per-rank SpMV is injected (the oracle's
+CSR loop on numpy views), so no GPU is involved; on the GPU box the same class is bound to the CUDA
+kernel (bench.py, tests/test_sharded_gpu.py)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from conftest import pkg
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, grid, mode, iters, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import importlib
+        import oracle
+        from oracle import generators as g
+        sh = importlib.import_module("2012-04_stanford_cme213_b200.sharded")
+        nx, ny, nz = grid
+        rows = nx * ny * nz
+        lo, hi = sh.row_partition(rows, world)[rank]
+        ptr, col, val = g.laplace3d(nx, ny, nz, lo, hi)
+
+        def spmv(a, b, x_full, y_full):  # rows [a,b) global; shard arrays are local
+            if b <= a:
+                return
+            p = ptr[a - lo:b - lo + 1]
+            y = oracle.csr_spmv(p - p[0], col[p[0]:p[-1]], val[p[0]:p[-1]], x_full.numpy())
+            y_full.numpy()[a:b] = y
+
+        x0 = np.random.default_rng(1).uniform(0, 1, rows)
+        xa, xb = torch.from_numpy(x0.copy()), torch.zeros(rows, dtype=torch.float64)
+        it = sh.ShardedIterate(rows, world, rank, spmv, xa, xb, halo=nx * ny, mode=mode, dist=dist)
+        it.iterate(iters)
+        full = it.gather_result(0).numpy()
+        if rank == 0:
+            fp, fc, fv = g.laplace3d(nx, ny, nz)
+            want = oracle.csr_iterate(fp, fc, fv, x0, iters)
+            out.put((it.mode, bool(np.array_equal(full, want)), it.comm_bytes_per_step))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,grid,mode,expect_mode", [
+    (2, (6, 5, 8), "halo", "halo"),
+    (2, (6, 5, 8), "full", "full"),
+    (2, (4, 4, 3), "halo", "full"),    # rows not divisible by 2 planes each: ragged -> falls back... (48 rows / 2 ok, 1.5 planes)
+    (3, (5, 4, 9), "halo", "halo"),
+    (3, (5, 4, 6), "halo", "halo"),    # shards of exactly two planes: boundary rows cover the whole shard
+])
+def test_sharded_iterate_matches_single_process(world, grid, mode, expect_mode):
+    ctx = mp.get_context("spawn")
+    out = ctx.SimpleQueue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, grid, mode, 4, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    got_mode, equal, comm = out.get()
+    assert equal, "sharded result differs from the single-process oracle"
+    rows = grid[0] * grid[1] * grid[2]
+    if got_mode == "halo":
+        assert comm == (world - 1) * 2 * grid[0] * grid[1] * 8
+    else:
+        assert comm == (world - 1) * (rows // world) * 8
+
+
+def test_row_partition_and_bandwidth():
+    sh = __import__("importlib").import_module("2012-04_stanford_cme213_b200.sharded")
+    assert sh.row_partition(10, 3) == [(0, 4), (4, 8), (8, 10)]  # ceil(rows/P) each, last takes the rest (2dHeat.cpp:284-306)
+    assert sh.row_partition(8, 4) == [(0, 2), (2, 4), (4, 6), (6, 8)]
+    assert sh.row_partition(3, 5) == [(0, 1), (1, 2), (2, 3), (3, 3), (3, 3)]
+    from oracle import generators as g
+    ptr, col, _ = g.laplace3d(5, 4, 3)
+    assert sh.half_bandwidth(torch.from_numpy(ptr), torch.from_numpy(col)) == 20
+    p2, c2, _ = g.laplace3d(5, 4, 3, 20, 40)
+    assert sh.half_bandwidth(torch.from_numpy(p2), torch.from_numpy(c2), 20) == 20
