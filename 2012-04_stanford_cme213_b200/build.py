@@ -58,5 +58,28 @@ def build(force=False, verbose=False):
     return LIB
 
 
+DRIVERS = {"fp": ["fp_main.cpp", "matrix_io.cpp"], "pagerank": ["pagerank_main.cpp"],
+           "check_output": ["check_output_main.cpp", "matrix_io.cpp"]}
+
+
+def build_drivers(force=False):
+    """The C++ drop-in drivers (host/), linked against the in-tree shared library."""
+    host, bindir = os.path.join(HERE, "host"), os.path.join(HERE, "bin")
+    os.makedirs(bindir, exist_ok=True)
+    gxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    for name, srcs in DRIVERS.items():
+        out = os.path.join(bindir, name)
+        paths = [os.path.join(host, s) for s in srcs]
+        newest = max(os.path.getmtime(p) for p in paths + [os.path.join(host, "matrix_io.h"), LIB])
+        if not force and os.path.exists(out) and os.path.getmtime(out) >= newest:
+            continue
+        cmd = [gxx, "-O2", "-fopenmp", "-std=c++17", "-o", out] + paths + ["-L" + HERE, "-lcme213_b200", "-Wl,-rpath,$ORIGIN/.."]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            sys.stderr.write(" ".join(cmd) + "\n" + r.stdout + r.stderr)
+            raise RuntimeError("driver build failed: " + name)
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))
+    build_drivers(force="--force" in sys.argv)
