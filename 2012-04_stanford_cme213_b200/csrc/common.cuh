@@ -61,6 +61,24 @@ static inline bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t
 template <typename V> __device__ __forceinline__ V ld_stream(const V *p) { return __ldcs(p); }
 template <typename V> __device__ __forceinline__ void st_stream(V *p, const V &v) { __stcs(p, v); }
 
+// Gathered vector entries are re-used by neighbouring rows long after the streamed matrix data has gone by:
+// keep them in L2 with an evict-last policy while col/val/y use evict-first (streaming) accesses.
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ float ld_keep(const float *p, uint64_t pol) {
+    float v;
+    asm volatile("ld.global.nc.L2::cache_hint.f32 %0, [%1], %2;" : "=f"(v) : "l"(p), "l"(pol));
+    return v;
+}
+__device__ __forceinline__ double ld_keep(const double *p, uint64_t pol) {
+    double v;
+    asm volatile("ld.global.nc.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v) : "l"(p), "l"(pol));
+    return v;
+}
+
 __device__ __forceinline__ uint32_t hash32(uint32_t seed, uint64_t idx) {
     // counter-based hash (two rounds of a 32-bit finaliser over a 64-bit counter); restated in
     // numpy by oracle/generators.py so tests can rebuild any generated input bit for bit.

@@ -226,8 +226,10 @@ __device__ __forceinline__ T lookback(const Scratch &scratch, int64_t tile, int 
 // Policy concept:
 //   using T; using Aux (per-vector state carried from load to store, may be empty);
 //   static constexpr int IPV (items per 16-byte vector); static constexpr bool SEG;
+//   static constexpr bool BULK; whether large inputs take the persistent bulk-copy kernel (gather-heavy
+//       policies hide their L2 latency better with many small CTAs per SM, i.e. the direct kernel)
 //   static constexpr int NIN;  number of input arrays streamed through shared memory by the bulk kernel
-//   static constexpr int in_bytes(int s);  element size of input stream s
+//   static constexpr int tile_bytes(int s, int tile_items);  bytes of input stream s per tile (a multiple of 16)
 //   const void *in_ptr(int s) const;       its base pointer
 //   __device__ void load(int64_t idx, int64_t n, bool fast, T (&v)[IPV], unsigned &head, Aux &aux) const;
 //       from global memory; `fast` = whole tile in range and 16-byte vector accesses allowed
@@ -285,15 +287,17 @@ __device__ __forceinline__ void warp_array_scan(const T (&a)[PL], unsigned hb, i
     }
 }
 
-// Steps 2-3 of the header comment.  On return cst[i] is the value to add in front of vector i's first
-// item (already reset where a head precedes it).  `between` runs after the first barrier on every
-// thread (the bulk kernel refills its ring there).  `get_carry(tile_agg, tile_has_head)` is called by
-// warp 0 (all lanes) once the tile aggregate is known and returns the tile's exclusive prefix: the
-// two front ends differ only there (decoupled look-back vs. one scanner per wave).
-template <class P, int THREADS, int VECS, class Between, class GetCarry>
-__device__ __forceinline__ void tile_core(CoreSmem<P, THREADS, VECS> &sm, const typename P::T (&v)[VECS][P::IPV],
-                                          const unsigned (&hf)[VECS], typename P::T (&cst)[VECS], Between between,
-                                          GetCarry get_carry) {
+// Per-tile core, split in two so that a front end can put other work between the parts.
+//
+// tile_local: per-thread aggregates, warp scans (inclusive results in wv, head ballots in wm), first
+// barrier, `between()` on every thread (the bulk kernel refills its ring there), then warp 0 scans the
+// warp aggregates, leaves their exclusive prefixes in shared memory and calls
+// `after_agg(tile_aggregate, tile_has_head)` (all 32 lanes of warp 0): the front ends publish the
+// aggregate and obtain tile prefixes there.  No trailing barrier.
+template <class P, int THREADS, int VECS, class Between, class AfterAgg>
+__device__ __forceinline__ void tile_local(CoreSmem<P, THREADS, VECS> &sm, const typename P::T (&v)[VECS][P::IPV],
+                                           const unsigned (&hf)[VECS], typename P::T (&wv)[VECS], unsigned (&wm)[VECS],
+                                           Between between, AfterAgg after_agg) {
     using T = typename P::T;
     constexpr int IPV = P::IPV;
     constexpr bool SEG = P::SEG;
@@ -302,9 +306,6 @@ __device__ __forceinline__ void tile_core(CoreSmem<P, THREADS, VECS> &sm, const 
     constexpr int PL = NAGG / 32;
     static_assert(NAGG % 32 == 0, "warp aggregates must fill whole lanes of one warp");
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-
-    T wv[VECS];
-    unsigned wm[VECS];
 #pragma unroll
     for (int i = 0; i < VECS; i++) {
         T a = v[i][0];
@@ -332,28 +333,36 @@ __device__ __forceinline__ void tile_core(CoreSmem<P, THREADS, VECS> &sm, const 
         T tile_agg;
         bool tile_f;
         warp_array_scan<T, SEG, PL>(a, hb, lane, e, before, tile_agg, tile_f);
-        const T carry = get_carry(tile_agg, tile_f);  // publishes the aggregate first: successors wait for it
 #pragma unroll
         for (int k = 0; k < PL; k++) {
             sm.excl_v[lane * PL + k] = e[k];
             sm.excl_f[lane * PL + k] = (unsigned char)((before >> k) & 1u);
         }
-        if (lane == 0) sm.carry = carry;
+        after_agg(tile_agg, tile_f);
     }
-    __syncthreads();
-    const T carry_tile = sm.carry;
+}
+
+// tile_cst (after a barrier that follows tile_local): cst[i] = what precedes vector i's first item inside
+// the tile (since the last head); bit i of `apply` = no head precedes it in the tile, so the tile's
+// exclusive prefix still has to be added.
+template <class P, int THREADS, int VECS>
+__device__ __forceinline__ void tile_cst(const CoreSmem<P, THREADS, VECS> &sm, const typename P::T (&wv)[VECS],
+                                         const unsigned (&wm)[VECS], typename P::T (&cst)[VECS], unsigned &apply) {
+    using T = typename P::T;
+    constexpr bool SEG = P::SEG;
+    constexpr int WARPS = THREADS / 32;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    apply = 0;
 #pragma unroll
     for (int i = 0; i < VECS; i++) {
         const int g = i * WARPS + warp;
-        const T e = sm.excl_v[g];
-        const bool head_before_warp = SEG && sm.excl_f[g];
         T w = __shfl_up_sync(0xFFFFFFFFu, wv[i], 1);
         if (lane == 0) w = T(0);
         const bool head_before_lane = SEG && (wm[i] & ((1u << lane) - 1u)) != 0;
         T c = w;
         if (!head_before_lane) {
-            c = e + c;
-            if (!head_before_warp) c = carry_tile + c;
+            c = sm.excl_v[g] + c;
+            if (!(SEG && sm.excl_f[g])) apply |= 1u << i;
         }
         cst[i] = c;
     }
@@ -362,12 +371,13 @@ __device__ __forceinline__ void tile_core(CoreSmem<P, THREADS, VECS> &sm, const 
 template <class P, int VECS>
 __device__ __forceinline__ void finish_and_store(const P &p, int64_t tile_base, int threads, int64_t n, bool fast,
                                                  const typename P::T (&v)[VECS][P::IPV], const unsigned (&hf)[VECS],
-                                                 const typename P::T (&cst)[VECS], const typename P::Aux (&aux)[VECS]) {
+                                                 const typename P::T (&cst)[VECS], unsigned apply, typename P::T carry_tile,
+                                                 const typename P::Aux (&aux)[VECS]) {
     using T = typename P::T;
     constexpr int IPV = P::IPV;
 #pragma unroll
     for (int i = 0; i < VECS; i++) {
-        T c = cst[i];
+        T c = ((apply >> i) & 1u) ? carry_tile + cst[i] : cst[i];
         T incl[IPV], excl[IPV];
 #pragma unroll
         for (int j = 0; j < IPV; j++) {
@@ -402,15 +412,20 @@ lookback_scan_kernel(P p, int64_t n, Scratch scratch, int vec_ok) {
     typename P::Aux aux[VECS];
 #pragma unroll
     for (int i = 0; i < VECS; i++) p.load(tile_base + ((int64_t)i * THREADS + tid) * IPV, n, fast, v[i], hf[i], aux[i]);
-    T cst[VECS];
-    tile_core<P, THREADS, VECS>(core, v, hf, cst, [] {}, [&](T tile_agg, bool tile_f) -> T {
+    T wv[VECS], cst[VECS];
+    unsigned wm[VECS], apply;
+    tile_local<P, THREADS, VECS>(core, v, hf, wv, wm, [] {}, [&](T tile_agg, bool tile_f) {
         if (lane == 0) Desc<T>::publish(scratch, tile, tile == 0 ? ST_PREFIX : ST_AGG, tile_agg, tile_f);
-        if (tile == 0) return T(0);
-        const T carry = lookback<T, SEG, 1>(scratch, tile, lane);
-        if (lane == 0) Desc<T>::publish(scratch, tile, ST_PREFIX, (SEG && tile_f) ? tile_agg : carry + tile_agg, tile_f);
-        return carry;
+        T carry = T(0);
+        if (tile != 0) {
+            carry = lookback<T, SEG, 1>(scratch, tile, lane);
+            if (lane == 0) Desc<T>::publish(scratch, tile, ST_PREFIX, (SEG && tile_f) ? tile_agg : carry + tile_agg, tile_f);
+        }
+        if (lane == 0) core.carry = carry;
     });
-    finish_and_store<P, VECS>(p, tile_base, THREADS, n, fast, v, hf, cst, aux);
+    __syncthreads();
+    tile_cst<P, THREADS, VECS>(core, wv, wm, cst, apply);
+    finish_and_store<P, VECS>(p, tile_base, THREADS, n, fast, v, hf, cst, apply, core.carry, aux);
 }
 
 // ---- front end 2: persistent CTAs, ring of bulk-async-copied tiles, one scanner per wave ----------------
@@ -419,7 +434,7 @@ template <class P, int THREADS, int VECS> struct BulkLayout {
     static constexpr int TILE_ITEMS = TILE_VECS * P::IPV;
     __host__ __device__ static constexpr int stream_off(int s) {
         int o = 0;
-        for (int i = 0; i < s; i++) o += TILE_ITEMS * P::in_bytes(i);
+        for (int i = 0; i < s; i++) o += P::tile_bytes(i, TILE_ITEMS);
         return o;
     }
     static constexpr int STAGE_BYTES = stream_off(P::NIN);
@@ -490,10 +505,11 @@ template <typename T> struct Slot<T, 8> {
 
 // Tiles are dealt round-robin: CTA b handles tiles b, b+G, b+2G, ...  (G = gridDim.x <= 32*DPL), so
 // "wave" w = tiles [wG, (w+1)G) is worked on by all CTAs at the same time; they are co-resident
-// (cooperative launch).  Every CTA publishes its tile aggregate; one CTA per wave (the job rotates)
-// waits for the wave's G aggregates, scans them (one warp, coalesced reads, nobody else reads them),
-// adds the running prefix of the previous wave and hands every tile its exclusive prefix.  Each CTA
-// then polls only its own slot.  All cross-CTA words carry their own ready bit, so no fence or
+// (cooperative launch).  Every data CTA publishes its tile aggregate; one extra CTA that owns no tiles
+// waits for each wave's G aggregates, scans them (one warp, coalesced reads, nobody else reads them),
+// adds the running prefix of the previous waves and hands every tile its exclusive prefix.  Each data
+// CTA polls only its own slot, one iteration later (the finish of a tile is deferred), so neither the
+// scanner's round trips nor a late CTA of the wave stall the others.  All cross-CTA words carry their own ready bit, so no fence or
 // atomic is needed (a fence would stall on the CTA's data stores that are still in flight).  Compared with every tile walking back over its
 // predecessors' descriptors this keeps the L2 lines holding the descriptors from becoming a
 // hot spot: with all tiles of a wave arriving together, 148 warps re-reading the same few lines
@@ -510,7 +526,44 @@ lookback_scan_bulk_kernel(P p, int64_t n, int64_t num_tiles, WaveScratch ws) {
     __shared__ CoreSmem<P, THREADS, VECS> core;
     const int tid = threadIdx.x, lane = tid & 31;
     const bool filler = tid == THREADS - 32;                 // lane 0 of the last warp feeds the ring
-    const int64_t G = gridDim.x;
+    const int64_t G = gridDim.x - 1;                         // data CTAs; CTA number G only scans
+
+    if ((int64_t)blockIdx.x == G) {
+        // The scanner CTA: for every wave, wait for the wave's aggregates (one warp, coalesced reads, nobody
+        // else reads them), scan them on top of the running prefix and hand every tile its exclusive prefix.
+        // It owns no tiles, so a late wave never delays the data of the next one.
+        if (tid >= 32) return;
+        T c0 = T(0);  // running prefix (since the last head) at the end of the previous wave
+        for (int64_t wave_first = 0; wave_first < num_tiles; wave_first += G) {
+            const int64_t wave_cnt = num_tiles - wave_first < G ? num_tiles - wave_first : G;
+            T a[DPL], e[DPL];
+            unsigned hb = 0, before;
+            bool pending;
+            do {
+                pending = false;
+#pragma unroll
+                for (int q = 0; q < DPL; q++) {
+                    const int64_t j = (int64_t)lane * DPL + q;
+                    a[q] = T(0);
+                    if (j < wave_cnt) {
+                        unsigned f;
+                        pending |= !Slot<T>::read(ws.A, wave_first + j, a[q], f);
+                        if (SEG && f) hb |= 1u << q; else hb &= ~(1u << q);
+                    }
+                }
+            } while (__any_sync(0xFFFFFFFFu, pending));
+            T total;
+            bool any;
+            warp_array_scan<T, SEG, DPL>(a, hb, lane, e, before, total, any);
+#pragma unroll
+            for (int q = 0; q < DPL; q++) {
+                const int64_t j = (int64_t)lane * DPL + q;
+                if (j < wave_cnt) Slot<T>::publish(ws.X, wave_first + j, ((before >> q) & 1u) ? e[q] : c0 + e[q], 0);
+            }
+            c0 = any ? total : c0 + total;
+        }
+        return;
+    }
 
     // start the copies of tile t into `stage`
     auto fill = [&](int stage, int64_t t) {
@@ -521,8 +574,8 @@ lookback_scan_bulk_kernel(P p, int64_t n, int64_t num_tiles, WaveScratch ws) {
 #pragma unroll
             for (int s = 0; s < P::NIN; s++)
                 bulk_load(ring + (size_t)stage * L::STAGE_BYTES + L::stream_off(s),
-                          (const unsigned char *)p.in_ptr(s) + base * P::in_bytes(s), (unsigned)(L::TILE_ITEMS * P::in_bytes(s)),
-                          &full_bar[stage]);
+                          (const unsigned char *)p.in_ptr(s) + t * P::tile_bytes(s, L::TILE_ITEMS),
+                          (unsigned)P::tile_bytes(s, L::TILE_ITEMS), &full_bar[stage]);
         } else {
             mbar_arrive(&full_bar[stage]);  // ragged last tile: read straight from global with guards
         }
@@ -542,6 +595,15 @@ lookback_scan_bulk_kernel(P p, int64_t n, int64_t num_tiles, WaveScratch ws) {
             ws.trace[((size_t)blockIdx.x * TRACE_MAX_IT + it) * 8 + k] = t;
         }
     };
+    // The finish of a tile (add its exclusive prefix, store) is deferred by one iteration: the prefix of
+    // tile i is only polled after the local phase of tile i+1, so the wave scanner's round trips overlap
+    // with useful work instead of stalling every CTA of the wave.
+    T v_p[VECS][IPV], cst_p[VECS];
+    unsigned hf_p[VECS], apply_p = 0;
+    typename P::Aux aux_p[VECS];
+    int64_t tile_p = -1, base_p = 0;
+    bool full_p = false;
+
     int it = 0;
     for (int64_t tile = blockIdx.x; tile < num_tiles; tile += G, it++) {
         const int stage = it % STAGES;
@@ -566,61 +628,47 @@ lookback_scan_bulk_kernel(P p, int64_t n, int64_t num_tiles, WaveScratch ws) {
 #pragma unroll
             for (int i = 0; i < VECS; i++) p.load(tile_base + ((int64_t)i * THREADS + tid) * IPV, n, false, v[i], hf[i], aux[i]);
         }
-        T cst[VECS];
-        const int64_t wave = it, wave_first = wave * G;
-        const int64_t wave_cnt = num_tiles - wave_first < G ? num_tiles - wave_first : G;
-        tile_core<P, THREADS, VECS>(
-            core, v, hf, cst,
-            // after the core's first barrier every thread holds its inputs in registers: the stage is free
+        T wv[VECS], cst[VECS];
+        unsigned wm[VECS], apply;
+        tile_local<P, THREADS, VECS>(
+            core, v, hf, wv, wm,
+            // after the first barrier every thread holds its inputs in registers: the stage is free
             [&] { if (filler) fill(stage, tile + (int64_t)STAGES * G); },
-            [&](T tile_agg, bool tile_f) -> T {
+            [&](T tile_agg, bool tile_f) {
                 stamp(it, 2);
                 if (lane == 0) Slot<T>::publish(ws.A, tile, tile_agg, tile_f);
                 stamp(it, 3);
-                if ((int64_t)blockIdx.x == wave % wave_cnt) {
-                    // this wave's scanner (the job rotates over the CTAs that have a tile in the wave): wait for the aggregates,
-                    // scan them for everybody.  One warp, coalesced reads, nobody else reads them.
-                    T a[DPL], e[DPL];
-                    unsigned hb = 0, before;
-                    bool pending;
-                    do {
-                        pending = false;
-#pragma unroll
-                        for (int q = 0; q < DPL; q++) {
-                            const int64_t j = (int64_t)lane * DPL + q;
-                            a[q] = T(0);
-                            if (j < wave_cnt) {
-                                unsigned f;
-                                pending |= !Slot<T>::read(ws.A, wave_first + j, a[q], f);
-                                if (SEG && f) hb |= 1u << q; else hb &= ~(1u << q);
-                            }
-                        }
-                    } while (__any_sync(0xFFFFFFFFu, pending));
-                    T c0 = T(0);  // running prefix (since the last head) at the end of the previous wave
-                    if (wave > 0) {
-                        unsigned f;
-                        while (!Slot<T>::read(ws.W, wave - 1, c0, f)) {}
-                    }
-                    T total;
-                    bool any;
-                    warp_array_scan<T, SEG, DPL>(a, hb, lane, e, before, total, any);
-#pragma unroll
-                    for (int q = 0; q < DPL; q++) {
-                        const int64_t j = (int64_t)lane * DPL + q;
-                        if (j < wave_cnt) Slot<T>::publish(ws.X, wave_first + j, ((before >> q) & 1u) ? e[q] : c0 + e[q], 0);
-                    }
-                    if (lane == 0) Slot<T>::publish(ws.W, wave, any ? total : c0 + total, 0);
-                    stamp(it, 4);
+                if (tile_p >= 0) {  // prefix of the PREVIOUS tile: one iteration old, normally there already
+                    T carry;
+                    unsigned f;
+                    while (!Slot<T>::read(ws.X, tile_p, carry, f)) {}
+                    if (lane == 0) core.carry = carry;
                 }
-                T carry;
-                unsigned f;
-                while (!Slot<T>::read(ws.X, tile, carry, f)) {}
                 stamp(it, 5);
-                return carry;
             });
+        __syncthreads();
         stamp(it, 6);
-        finish_and_store<P, VECS>(p, tile_base, THREADS, n, full, v, hf, cst, aux);
+        tile_cst<P, THREADS, VECS>(core, wv, wm, cst, apply);
+        if (tile_p >= 0) finish_and_store<P, VECS>(p, base_p, THREADS, n, full_p, v_p, hf_p, cst_p, apply_p, core.carry, aux_p);
         stamp(it, 7);
+#pragma unroll
+        for (int i = 0; i < VECS; i++) {
+#pragma unroll
+            for (int j = 0; j < IPV; j++) v_p[i][j] = v[i][j];
+            hf_p[i] = hf[i]; cst_p[i] = cst[i]; aux_p[i] = aux[i];
+        }
+        apply_p = apply; tile_p = tile; base_p = tile_base; full_p = full;
+    }
+    if (tile_p >= 0) {  // drain: the last tile of this CTA
+        __syncthreads();  // everybody is done reading core.carry of the previous finish
+        if (tid < 32) {
+            T carry;
+            unsigned f;
+            while (!Slot<T>::read(ws.X, tile_p, carry, f)) {}
+            if (lane == 0) core.carry = carry;
+        }
+        __syncthreads();
+        finish_and_store<P, VECS>(p, base_p, THREADS, n, full_p, v_p, hf_p, cst_p, apply_p, core.carry, aux_p);
     }
 }
 #endif  // __CUDACC__
@@ -628,11 +676,13 @@ lookback_scan_bulk_kernel(P p, int64_t n, int64_t num_tiles, WaveScratch ws) {
 // Tile configuration (tuned on B200, see profiles/r01_notes.md).
 template <class P> struct Cfg {
     static constexpr int THREADS = 1024;                       // bulk kernel: one CTA per SM
-    static constexpr int VEC_BYTES = BulkLayout<P, 1, 1>::STAGE_BYTES;            // staged bytes per 16-byte value vector
-    static constexpr int VECS = (96 * 1024) / (THREADS * VEC_BYTES);              // ~96 KiB per stage whatever is streamed
-    static constexpr int STAGES = 2;
+    static constexpr int VEC_BYTES = BulkLayout<P, 32, 1>::STAGE_BYTES / 32;      // staged bytes per 16-byte value vector
+    static constexpr int STAGE_TARGET = (P::SEG ? 64 : 80) * 1024;    // segmented variants carry more state per vector: smaller tiles, no spills
+    static constexpr int VECS = STAGE_TARGET / (THREADS * VEC_BYTES) > 0 ? STAGE_TARGET / (THREADS * VEC_BYTES) : 1;
+    static constexpr int STAGES = 2;   // large tiles amortise the ~0.7 us prefix round trip better than deep rings (profiles/r01_notes.md)
     static constexpr int DPL = 5;                               // a wave holds at most 32*DPL = 160 tiles
     static constexpr int DIRECT_THREADS = 256, DIRECT_VECS = 4; // one-tile-per-CTA kernel
+    static constexpr int DIRECT_MIN_BLOCKS = (P::SEG || P::NIN > 1) ? 4 : 6;   // register caps: 64 / 40 per thread
 };
 
 // ---- host launchers ----------------------------------------------------------------------------------
@@ -674,9 +724,10 @@ int launch_bulk(cme213_ctx *ctx, const P &p, int64_t n, cudaStream_t st, const c
         CME213_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, THREADS, smem));
         if (per_sm < 1) { set_error("%s: kernel does not fit on an SM", name); per_sm = 0; return CME213_ERR_UNSUPPORTED; }
     }
-    int64_t grid = (int64_t)per_sm * ctx->sm_count;   // all co-resident (cooperative launch checks it)
-    if (grid > 32 * DPL) grid = 32 * DPL;              // one warp scans a whole wave
+    int64_t grid = (int64_t)per_sm * ctx->sm_count - 1;   // data CTAs; all co-resident with the scanner CTA (cooperative launch checks it)
+    if (grid > 32 * DPL) grid = 32 * DPL;                  // one warp scans a whole wave
     if (grid > tiles) grid = tiles;
+    if (grid < 1) grid = 1;
     const int64_t waves = div_up(tiles, grid);
     const size_t bytes = wave_scratch_bytes(tiles, waves, sizeof(T));
     if (!scratch_mem) {
@@ -698,7 +749,7 @@ int launch_bulk(cme213_ctx *ctx, const P &p, int64_t n, cudaStream_t st, const c
     }
     P pp = p;
     void *args[] = {(void *)&pp, (void *)&n, (void *)&tiles, (void *)&ws};
-    CME213_CUDA(cudaLaunchCooperativeKernel((const void *)kern, dim3((unsigned)grid), dim3(THREADS), args, (size_t)smem, st));
+    CME213_CUDA(cudaLaunchCooperativeKernel((const void *)kern, dim3((unsigned)grid + 1), dim3(THREADS), args, (size_t)smem, st));
     if (tracing) {
         // debug aid: average time between the stamps of the kernel, over all CTAs and waves
         unsigned long long *h = (unsigned long long *)malloc(trace_words * 8);
@@ -739,9 +790,9 @@ template <class P> static inline size_t scratch_bytes_for(int64_t n) {
 template <class P>
 int launch_with_scratch(cme213_ctx *ctx, const P &p, int64_t n, bool vec_ok, cudaStream_t st, const char *name,
                         void *scratch_mem, size_t scratch_avail) {
-    if (vec_ok && n >= (int64_t)1 << 20)
+    if (P::BULK && vec_ok && n >= (int64_t)1 << 20)
         return launch_bulk<P, Cfg<P>::THREADS, Cfg<P>::VECS, Cfg<P>::STAGES, Cfg<P>::DPL>(ctx, p, n, st, name, scratch_mem, scratch_avail);
-    return launch_direct<P, Cfg<P>::DIRECT_THREADS, Cfg<P>::DIRECT_VECS, 1>(ctx, p, n, vec_ok, st, name, scratch_mem);
+    return launch_direct<P, Cfg<P>::DIRECT_THREADS, Cfg<P>::DIRECT_VECS, Cfg<P>::DIRECT_MIN_BLOCKS>(ctx, p, n, vec_ok, st, name, scratch_mem);
 }
 
 template <class P>

@@ -34,20 +34,22 @@ struct PlainPolicy {
     using Aux = NoAux;
     static constexpr int IPV = 16 / sizeof(T);
     static constexpr bool SEG = SEG_;
-    static constexpr int NIN = 1;
-    __host__ __device__ static constexpr int in_bytes(int) { return (int)sizeof(T); }
+    static constexpr bool BULK = true;
+    static constexpr int NIN = SEG_ ? 2 : 1;   // values, and for segmented scans the head-flag words (1 bit per item)
+    __host__ __device__ static constexpr int tile_bytes(int s, int tile_items) { return s == 0 ? tile_items * (int)sizeof(T) : tile_items / 8; }
     const T *in;
     T *out;
     const uint32_t *flag_bits;
-    __host__ __device__ const void *in_ptr(int) const { return in; }
+    __host__ __device__ const void *in_ptr(int s) const { return s == 0 ? (const void *)in : (const void *)flag_bits; }
 
-    __device__ void load_smem(const unsigned char *const (&sin)[NIN], int vec, int, int64_t idx, int64_t, T (&v)[IPV],
+    __device__ void load_smem(const unsigned char *const (&sin)[NIN], int vec, int, int64_t, int64_t, T (&v)[IPV],
                               unsigned &head, Aux &) const {
         typename V16<T>::type x = *reinterpret_cast<const typename V16<T>::type *>(sin[0] + (size_t)vec * 16);
         const T *e = reinterpret_cast<const T *>(&x);
 #pragma unroll
         for (int j = 0; j < IPV; j++) v[j] = e[j];
-        head = SEG ? head_bits<IPV>(flag_bits, idx) : 0u;
+        head = 0;
+        if constexpr (SEG_) head = head_bits<IPV>(reinterpret_cast<const uint32_t *>(sin[NIN - 1]), (int64_t)vec * IPV);
     }
     __device__ void load(int64_t idx, int64_t n, bool fast, T (&v)[IPV], unsigned &head, Aux &) const {
         head = 0;
@@ -92,14 +94,19 @@ struct MulGatherPolicy {
     using Aux = NoAux;
     static constexpr int IPV = 16 / sizeof(T);
     static constexpr bool SEG = true;
-    static constexpr int NIN = 2;
-    __host__ __device__ static constexpr int in_bytes(int s) { return s == 0 ? (int)sizeof(T) : 4; }
+    static constexpr bool BULK = false;  // bound by L2 gather rate, not by the stream: many small CTAs per SM hide it better (profiles/r01_notes.md)
+    static constexpr int NIN = 3;   // a, k, head-flag words
+    __host__ __device__ static constexpr int tile_bytes(int s, int tile_items) {
+        return s == 0 ? tile_items * (int)sizeof(T) : s == 1 ? tile_items * 4 : tile_items / 8;
+    }
     const T *a;
     const int32_t *k;
     const T *x;
     const uint32_t *flag_bits;
     T *b;
-    __host__ __device__ const void *in_ptr(int s) const { return s == 0 ? (const void *)a : (const void *)k; }
+    __host__ __device__ const void *in_ptr(int s) const {
+        return s == 0 ? (const void *)a : s == 1 ? (const void *)k : (const void *)flag_bits;
+    }
 
     __device__ void load_smem(const unsigned char *const (&sin)[NIN], int vec, int, int64_t idx, int64_t, T (&v)[IPV],
                               unsigned &head, Aux &) const {
@@ -112,7 +119,7 @@ struct MulGatherPolicy {
         for (int j = 0; j < IPV; j++) xv[j] = __ldg(x + ke[j]);
 #pragma unroll
         for (int j = 0; j < IPV; j++) v[j] = mul_rn(ae[j], xv[j]);
-        head = head_bits<IPV>(flag_bits, idx);
+        head = head_bits<IPV>(reinterpret_cast<const uint32_t *>(sin[2]), (int64_t)vec * IPV);
     }
     __device__ void load(int64_t idx, int64_t n, bool fast, T (&v)[IPV], unsigned &head, Aux &) const {
         head = 0;
@@ -161,8 +168,9 @@ struct CooPolicy {
     static constexpr int IPV = 16 / sizeof(T);
     static constexpr bool SEG = true;
     struct Aux { int row[IPV]; int next; };
+    static constexpr bool BULK = false;  // gather-bound like the fused step
     static constexpr int NIN = 3;
-    __host__ __device__ static constexpr int in_bytes(int s) { return s == 2 ? (int)sizeof(T) : 4; }
+    __host__ __device__ static constexpr int tile_bytes(int s, int tile_items) { return tile_items * (s == 2 ? (int)sizeof(T) : 4); }
     const int32_t *row;
     const int32_t *col;
     const T *val;
@@ -295,9 +303,9 @@ CME213_API int cme213_exclusive_scan_u32(cme213_ctx *ctx, const uint32_t *d_in, 
 #define CME213_TRY_BULK(T, V, S) if (T_ == T && V_ == V && S_ == S) return scan::launch_bulk<P, T, V, S, (T == 1024 ? 5 : 10)>(ctx, p, n, st, "scan", nullptr, 0);
 #define CME213_TRY_DIRECT(T, V) if (T_ == T && V_ == V && S_ == 0) return scan::launch_direct<P, T, V, 1>(ctx, p, n, ok, st, "scan", nullptr);
         CME213_TRY_DIRECT(256, 4) CME213_TRY_DIRECT(1024, 8)
-        CME213_TRY_BULK(512, 4, 2) CME213_TRY_BULK(512, 4, 3) CME213_TRY_BULK(512, 6, 2) CME213_TRY_BULK(512, 8, 2) CME213_TRY_BULK(512, 8, 3)
-        CME213_TRY_BULK(1024, 4, 2) CME213_TRY_BULK(1024, 4, 3) CME213_TRY_BULK(1024, 6, 2) CME213_TRY_BULK(1024, 8, 1) CME213_TRY_BULK(1024, 2, 4)
-        CME213_TRY_BULK(1024, 3, 4) CME213_TRY_BULK(1024, 5, 2) CME213_TRY_BULK(1024, 7, 1)
+        CME213_TRY_BULK(512, 4, 3) CME213_TRY_BULK(512, 2, 4) CME213_TRY_BULK(512, 2, 6)
+        CME213_TRY_BULK(1024, 4, 3) CME213_TRY_BULK(1024, 3, 4) CME213_TRY_BULK(1024, 6, 2) CME213_TRY_BULK(1024, 2, 4) CME213_TRY_BULK(1024, 2, 6)
+        CME213_TRY_BULK(1024, 5, 2) CME213_TRY_BULK(1024, 4, 2) CME213_TRY_BULK(1024, 3, 3) CME213_TRY_BULK(1024, 7, 1) CME213_TRY_BULK(1024, 5, 1) CME213_TRY_BULK(1024, 6, 1)
 #undef CME213_TRY_BULK
 #undef CME213_TRY_DIRECT
     }
@@ -311,7 +319,7 @@ static int segscan_impl(cme213_ctx *ctx, const T *d_in, const uint32_t *d_flag_b
     if (n < 0 || (n > 0 && (!d_in || !d_out || !d_flag_bits))) { set_error("%s: bad arguments", name); return CME213_ERR_INVALID; }
     if (n == 0) return CME213_OK;
     PlainPolicy<T, true, INCLUSIVE> p{d_in, d_out, d_flag_bits};
-    return run(ctx, p, n, aligned16(d_in) && aligned16(d_out), stream, name);
+    return run(ctx, p, n, aligned16(d_in) && aligned16(d_out) && aligned16(d_flag_bits), stream, name);
 }
 CME213_API int cme213_segscan_inclusive_f32(cme213_ctx *ctx, const float *d_in, const uint32_t *d_flag_bits,
                                             float *d_out, int64_t n, void *stream) {
@@ -336,7 +344,7 @@ static int mul_gather_impl(cme213_ctx *ctx, const T *d_a, const int32_t *d_k, co
     }
     if (n == 0) return CME213_OK;
     MulGatherPolicy<T> p{d_a, d_k, d_x, d_flag_bits, d_b};
-    return run(ctx, p, n, aligned16(d_a) && aligned16(d_k) && aligned16(d_b), stream, name);
+    return run(ctx, p, n, aligned16(d_a) && aligned16(d_k) && aligned16(d_b) && aligned16(d_flag_bits), stream, name);
 }
 CME213_API int cme213_mul_gather_segscan_f32(cme213_ctx *ctx, const float *d_a, const int32_t *d_k, const float *d_x,
                                              const uint32_t *d_flag_bits, float *d_b, int64_t n, void *stream) {

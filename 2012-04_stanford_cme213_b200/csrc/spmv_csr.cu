@@ -48,10 +48,17 @@ __device__ __forceinline__ T product(const Args<T> &a, T v, int c) {
     if (MODE == MODE_PAGERANK) return mul_rn(__ldg(a.x + c), __ldg(a.inv + c));
     return __ldg(a.x + c);
 }
+// same, with the gathered entries marked evict-last in L2 (stream kernel)
+template <typename T, int MODE>
+__device__ __forceinline__ T product_keep(const Args<T> &a, T v, int c, uint64_t pol) {
+    if (MODE == MODE_CSR) return mul_rn(v, ld_keep(a.x + c, pol));
+    if (MODE == MODE_PAGERANK) return mul_rn(ld_keep(a.x + c, pol), ld_keep(a.inv + c, pol));
+    return ld_keep(a.x + c, pol);
+}
 template <typename T, int MODE>
 __device__ __forceinline__ void epilogue(const Args<T> &a, int64_t r, T sum) {
     if (MODE == MODE_CSR) {
-        a.y[r] = sum;
+        st_stream(a.y + r, sum);
     } else {
         // graph_nodes_out[i] = 0.5f/N + 0.5f*sum   (pagerank.cu:54)
         const T out = add_rn(a.base, mul_rn(T(0.5), sum));
@@ -125,6 +132,7 @@ csr_stream_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
         re = a.row_ptr[r + 1];
     }
     const int b0 = __ldg(a.row_ptr + r0), b1 = __ldg(a.row_ptr + rl);  // this CTA's nonzero range
+    const uint64_t keep = l2_policy_evict_last();
     T sum = T(0);
     for (int base = b0 & ~3; base < b1; base += TILE) {
 #pragma unroll
@@ -136,10 +144,10 @@ csr_stream_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
                 V4<T> w;
                 if (MODE == MODE_CSR) w = V4<T>::load(a.val + j);
                 else w = V4<T>{{T(0), T(0), T(0), T(0)}};
-                T p0 = product<T, MODE>(a, w.v[0], c.x);
-                T p1 = product<T, MODE>(a, w.v[1], c.y);
-                T p2 = product<T, MODE>(a, w.v[2], c.z);
-                T p3 = product<T, MODE>(a, w.v[3], c.w);
+                T p0 = product_keep<T, MODE>(a, w.v[0], c.x, keep);
+                T p1 = product_keep<T, MODE>(a, w.v[1], c.y, keep);
+                T p2 = product_keep<T, MODE>(a, w.v[2], c.z, keep);
+                T p3 = product_keep<T, MODE>(a, w.v[3], c.w, keep);
                 prod[o + 0] = p0; prod[o + 1] = p1; prod[o + 2] = p2; prod[o + 3] = p3;
             } else {
 #pragma unroll

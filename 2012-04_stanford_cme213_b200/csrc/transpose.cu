@@ -11,8 +11,9 @@
 //    of the slides, so both the write phase (lanes walk along input columns) and the read phase
 //    (lanes walk along input rows) hit 8 distinct 16-byte bank groups per quarter-warp: no
 //    bank conflicts and no padding, and LDS/STS are 128-bit as well;
-//  * tiles are 64x64 elements (16 KiB for fp32, 32 KiB for fp64), 256 threads, so that several
-//    CTAs per SM keep >100 KiB of loads in flight per SM, which HBM3e needs.
+//  * tiles are 64 rows x 256 bytes (64x64 fp32, 64x32 fp64: 16 KiB either way), 256 threads, so that
+//    8+ CTAs per SM keep >100 KiB of loads in flight per SM, which HBM3e needs (the first version used
+//    64x64 fp64 tiles = 32 KiB and was occupancy-limited to 85 % of copy speed, profiles/r01_notes.md).
 //
 // HBM traffic is the algorithmic minimum: each element is read once and written once, in full
 // 32-byte sectors on both sides.  Matrices whose shape or pointers do not allow 16-byte vectors
@@ -21,7 +22,8 @@
 
 namespace {
 
-constexpr int TILE = 64;
+constexpr int TILE_R = 64;      // input rows per tile
+constexpr int TILE_BYTES_C = 256;  // input row segment per tile: 64 fp32 or 32 fp64 columns (16 KiB tiles both ways)
 constexpr int TR_THREADS = 256;
 
 template <typename T> struct Vec16;
@@ -32,18 +34,20 @@ template <typename T>
 __global__ void __launch_bounds__(TR_THREADS)
 transpose_vec_kernel(const T *__restrict__ in, T *__restrict__ out, int64_t rows, int64_t cols, int64_t ld_in,
                      int64_t ld_out, int tiles_c) {
-    constexpr int V = 16 / sizeof(T);   // elements per 16-byte vector: 4 (b32) or 2 (b64)
-    constexpr int NB = TILE / V;        // micro-blocks per tile side: 16 or 32
-    constexpr int BLOCKS = NB * NB;     // micro-blocks per tile: 256 or 1024
+    constexpr int V = 16 / sizeof(T);             // elements per 16-byte vector: 4 (b32) or 2 (b64)
+    constexpr int TILE_C = TILE_BYTES_C / sizeof(T);  // input columns per tile: 64 or 32
+    constexpr int NBC = TILE_C / V;               // micro-block columns per tile: 16
+    constexpr int NBR = TILE_R / V;               // micro-block rows per tile: 16 or 32
+    constexpr int BLOCKS = NBC * NBR;             // micro-blocks per tile: 256 or 512
     constexpr int PER_THREAD = BLOCKS / TR_THREADS;
     using V16 = typename Vec16<T>::type;
-    // unit (o, R): o = output row inside the tile (0..TILE-1), R = micro-block row index.
-    __shared__ V16 smem[TILE * NB];
+    // unit (o, R): o = output row inside the tile (0..TILE_C-1), R = micro-block row index.
+    __shared__ V16 smem[TILE_C * NBR];
 
     // blockIdx.x walks tiles along the input row direction fastest.
     const int64_t tile_id = blockIdx.x;
     const int64_t tr = tile_id / tiles_c, tc = tile_id % tiles_c;
-    const int64_t r0 = tr * TILE, c0 = tc * TILE;
+    const int64_t r0 = tr * TILE_R, c0 = tc * TILE_C;
     const int tid = threadIdx.x;
 
     // ---- load phase: lanes walk along input columns (c fastest) ----
@@ -51,7 +55,7 @@ transpose_vec_kernel(const T *__restrict__ in, T *__restrict__ out, int64_t rows
 #pragma unroll
     for (int b = 0; b < PER_THREAD; b++) {
         const int id = b * TR_THREADS + tid;
-        const int c = id % NB, R = id / NB;
+        const int c = id % NBC, R = id / NBC;
         const int64_t gc = c0 + (int64_t)c * V;
 #pragma unroll
         for (int i = 0; i < V; i++) {
@@ -67,7 +71,7 @@ transpose_vec_kernel(const T *__restrict__ in, T *__restrict__ out, int64_t rows
 #pragma unroll
     for (int b = 0; b < PER_THREAD; b++) {
         const int id = b * TR_THREADS + tid;
-        const int c = id % NB, R = id / NB;
+        const int c = id % NBC, R = id / NBC;
 #pragma unroll
         for (int j = 0; j < V; j++) {
             V16 v;
@@ -75,7 +79,7 @@ transpose_vec_kernel(const T *__restrict__ in, T *__restrict__ out, int64_t rows
 #pragma unroll
             for (int i = 0; i < V; i++) e[i] = blk[b][i][j];
             const int o = c * V + j;
-            smem[o * NB + (R ^ (c & 7))] = v;
+            smem[o * NBR + (R ^ (c & 7))] = v;
         }
     }
     __syncthreads();
@@ -83,13 +87,13 @@ transpose_vec_kernel(const T *__restrict__ in, T *__restrict__ out, int64_t rows
 #pragma unroll
     for (int b = 0; b < PER_THREAD; b++) {
         const int id = b * TR_THREADS + tid;
-        const int R = id % NB, c = id / NB;
+        const int R = id % NBR, c = id / NBR;
         const int64_t orow_base = c0 + (int64_t)c * V;  // output row = input column
         const int64_t ocol = r0 + (int64_t)R * V;       // output column = input row
 #pragma unroll
         for (int j = 0; j < V; j++) {
             const int o = c * V + j;
-            V16 v = smem[o * NB + (R ^ (c & 7))];
+            V16 v = smem[o * NBR + (R ^ (c & 7))];
             const int64_t orow = orow_base + j;
             if (orow < cols && ocol < rows) cme213::st_stream(reinterpret_cast<V16 *>(out + orow * ld_out + ocol), v);
         }
@@ -138,7 +142,7 @@ int transpose_impl(cme213_ctx *ctx, const void *d_in, void *d_out, int64_t rows,
     const bool vec_ok = cme213::aligned16(d_in) && cme213::aligned16(d_out) && rows % V == 0 &&
                         (cols % V == 0 || ld_in >= ((cols + V - 1) / V) * V) && ld_in % V == 0 && ld_out % V == 0;
     if (vec_ok) {
-        const int64_t tiles_r = cme213::div_up(rows, TILE), tiles_c = cme213::div_up(cols, TILE);
+        const int64_t tiles_r = cme213::div_up(rows, TILE_R), tiles_c = cme213::div_up(cols, TILE_BYTES_C / (int)sizeof(T));
         if (tiles_r * tiles_c > 0x7FFFFFFFLL || tiles_c > 0x7FFFFFFFLL) {
             cme213::set_error("transpose: too many tiles");
             return CME213_ERR_UNSUPPORTED;

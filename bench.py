@@ -126,7 +126,7 @@ def make_c5(ctx, torch, args, rank, world, dist):
                 meta={"workload": "C5: CSR SpMV iteration, 3-D 7-point Laplacian %d^3, fp64, row-sharded over %d GPU(s)" % (g, world),
                       "rows": rows, "nnz": nnz_total, "exchange": it.mode, "comm_bytes_per_rank_per_step": it.comm_bytes_per_step,
                       "l2": "working set %.1f GB per pass >> 126 MB L2" % (alg / 1e9)},
-                keep=(d_ptr, d_col, d_val, xa, xb, it), iterate=it, shard=(lo, hi, d_ptr, d_col, d_val, nnz.value))
+                keep=(d_ptr, d_col, d_val, xa, xb, it), iterate=it, shard=(lo, hi, d_ptr, d_col, d_val, nnz.value), ctx=ctx)
 
 
 def make_c1(ctx, torch, args):
@@ -387,13 +387,15 @@ def run_reference(args):
     """--impl reference: the reference's CPU path for the same metric on the host cores.  For C5 the
     reference has no fp64 CSR code of its own (its CSR is the fp32 PageRank gather), so this is the
     oracle port of the slide-20 loop with OpenMP over rows (kind = "port")."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    # torchrun pins OMP_NUM_THREADS=1 for its children; the reference arm is meant to use every host core
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
     import numpy as np
     import oracle
     from oracle import generators as g
     oracle.build()
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
-        return
     grid = args.grid
     planes = 32 if grid >= 32 else grid
     rows = planes * grid * grid
@@ -432,9 +434,9 @@ def e2e_c5(torch, pkg, wl, args, rank, world, dist):
     # Single-GPU semantics need a square operator: at N=1 that is the whole matrix.  At N>1 every rank
     # times the upload + iteration of a square diagonal block (columns outside the block dropped by
     # pointing them at a zero entry would change the matrix), so e2e is reported at N=1 only.
-    if world > 1:
-        return None
     iters = 20
+    if world > 1:
+        return e2e_c5_sharded(torch, pkg, wl, args, rank, world, dist, iters)
     pin = lambda t: t.cpu().pin_memory()
     h_ptr, h_col, h_val = pin(d_ptr), pin(d_col), pin(d_val)
     h_x = torch.empty(rows_total, dtype=torch.float64).pin_memory()
@@ -459,6 +461,49 @@ def e2e_c5(torch, pkg, wl, args, rank, world, dist):
     return {"value": wl["alg_bytes"] * iters * calls / el / 1e9, "unit": "GB/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
             "call": "cme213_csr_iterate_host_f64(nr_iterations=%d): pinned host CSR in, result vector out" % iters,
             "calls_timed": calls, "ms_per_call": el / calls * 1e3, "kernel_ms_inside_call": float(kernel_ms.value)}
+
+
+def e2e_c5_sharded(torch, pkg, wl, args, rank, world, dist, iters):
+    """N > 1: every rank owns the pinned HOST copy of its row block.  Timed per call: H2D of the block and of
+    x, `iters` row-sharded steps (halo exchange over NCCL), D2H of the rank's slice of the result."""
+    sh = importlib.import_module(PKG + ".sharded")
+    lo, hi, d_ptr, d_col, d_val, nnz = wl["shard"]
+    g = args.grid
+    rows = g ** 3
+    ctx = wl["ctx"]
+    h_ptr, h_col, h_val = d_ptr.cpu().pin_memory(), d_col.cpu().pin_memory(), d_val.cpu().pin_memory()
+    h_x = (torch.rand(rows, dtype=torch.float64) * 1e-3).pin_memory()
+    h_y = torch.empty(hi - lo, dtype=torch.float64).pin_memory()
+    # device buffers of the call (allocated once: the host-pointer API keeps its workspace between calls)
+    e_ptr, e_col, e_val = torch.empty_like(d_ptr), torch.empty_like(d_col), torch.empty_like(d_val)
+    xa = torch.empty(rows, dtype=torch.float64, device="cuda")
+    xb = torch.empty_like(xa)
+    streams = (torch.cuda.current_stream(), torch.cuda.Stream())
+    it = sh.ShardedIterate(rows, world, rank, sh.cuda_spmv(ctx, lo, e_ptr, e_col, e_val, args.csr_kernel), xa, xb,
+                           halo=g * g, mode=args.exchange, dist=dist, streams=streams)
+
+    def call():
+        e_ptr.copy_(h_ptr, non_blocking=True); e_col.copy_(h_col, non_blocking=True); e_val.copy_(h_val, non_blocking=True)
+        xa.copy_(h_x, non_blocking=True)
+        it.iterate(iters)
+        h_y.copy_(xa[lo:hi], non_blocking=True)
+        torch.cuda.synchronize()
+
+    call()
+    calls = max(1, min(args.steps, 3))
+    dist.barrier(); torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(calls):
+        call()
+    dist.barrier()
+    el = time.perf_counter() - t0
+    t = torch.tensor([el], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    el = float(t.item())
+    h2d = h_ptr.numel() * 4 + h_col.numel() * 4 + h_val.numel() * 8 + rows * 8
+    return {"value": wl["alg_bytes"] * iters * calls / el / 1e9, "unit": "GB/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": (hi - lo) * 8,
+            "call": "per rank: pinned host row block + x -> device, %d row-sharded iterations (sharded.ShardedIterate), result slice -> host" % iters,
+            "calls_timed": calls, "ms_per_call": el / calls * 1e3, "bytes_are": "per rank"}
 
 
 def main():
