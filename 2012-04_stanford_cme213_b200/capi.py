@@ -41,6 +41,8 @@ PROTOTYPES = {
     "cme213_transpose_b32": (_i, [_p, _p, _p, _i64, _i64, _i64, _i64, _p]),
     "cme213_transpose_b64": (_i, [_p, _p, _p, _i64, _i64, _i64, _i64, _p]),
     "cme213_exclusive_scan_u32": (_i, [_p, _p, _p, _i64, _p]),
+    "cme213_exclusive_scan_u32_static_max_n": (_i64, []),
+    "cme213_exclusive_scan_u32_static": (_i, [_p, _p, _i64, _p]),
     "cme213_flag_words": (_i64, [_i64]),
     "cme213_segment_flags_from_offsets": (_i, [_p, _p, _i, _i64, _p, _p]),
     "cme213_segscan_inclusive_f32": (_i, [_p, _p, _p, _p, _i64, _p]),

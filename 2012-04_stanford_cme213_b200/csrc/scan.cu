@@ -392,3 +392,58 @@ int cme213_internal_exclusive_scan_u32(cme213_ctx *ctx, const uint32_t *d_in, ui
     return scan::launch_with_scratch(ctx, p, n, aligned16(d_in) && aligned16(d_out), (cudaStream_t)stream,
                                      "exclusive_scan_u32", scratch, cme213_internal_scan_u32_scratch_bytes(n));
 }
+
+// ---- exclusive scan that allocates nothing -------------------------------------------------------------
+// Some hosts of this library may not allocate device memory at the moment they need a scan: a solver that
+// handed every byte of the GPU to its own pool at start-up, a service whose steady-state loop must not hit
+// cudaMalloc because it synchronises the whole device and can fail late, or a plug-in that is only given
+// input and output buffers by its framework.  The regular entry point keeps its look-back descriptors in
+// the context workspace, which is cudaMalloc'ed on first use and again whenever a larger input arrives.
+// This variant keeps them in a fixed array inside the library image instead, so nothing is ever allocated;
+// the price is a hard size limit and ~0.5 MiB of device memory held by every GPU that loads the library.
+namespace {
+constexpr int64_t STATIC_SCAN_MAX_N = (int64_t)1 << 28;  // elements
+using StaticScanPolicy = PlainPolicy<uint32_t, false, false>;
+constexpr int STATIC_SCAN_THREADS = 256, STATIC_SCAN_VECS = 4;
+constexpr int64_t STATIC_SCAN_TILE = (int64_t)STATIC_SCAN_THREADS * STATIC_SCAN_VECS * StaticScanPolicy::IPV;
+constexpr int64_t STATIC_SCAN_MAX_TILES = (STATIC_SCAN_MAX_N + STATIC_SCAN_TILE - 1) / STATIC_SCAN_TILE;
+constexpr size_t STATIC_SCAN_BYTES = 256 + (size_t)STATIC_SCAN_MAX_TILES * 8;  // ticket + one 64-bit descriptor per tile
+
+// In host code this name is only a handle for the runtime; the address a kernel may use comes from
+// cudaGetSymbolAddress, asked once per device with that device current.
+static __device__ __align__(256) unsigned char g_static_scan_scratch[STATIC_SCAN_BYTES];
+static void *g_static_scan_ptr[64] = {nullptr};
+}  // namespace
+
+CME213_API int64_t cme213_exclusive_scan_u32_static_max_n(void) { return STATIC_SCAN_MAX_N; }
+
+CME213_API int cme213_exclusive_scan_u32_static(const uint32_t *d_in, uint32_t *d_out, int64_t n, void *stream) {
+    if (n < 0) { set_error("exclusive_scan_u32_static: negative size"); return CME213_ERR_INVALID; }
+    if (n > STATIC_SCAN_MAX_N) {
+        set_error("exclusive_scan_u32_static: n = %lld exceeds the built-in scratch (max %lld elements); use "
+                  "cme213_exclusive_scan_u32 for larger inputs", (long long)n, (long long)STATIC_SCAN_MAX_N);
+        return CME213_ERR_UNSUPPORTED;
+    }
+    if (n == 0) return CME213_OK;
+    if (!d_in || !d_out) { set_error("exclusive_scan_u32_static: null pointer"); return CME213_ERR_INVALID; }
+    int dev = -1;
+    CME213_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) { set_error("exclusive_scan_u32_static: device index %d not supported", dev); return CME213_ERR_UNSUPPORTED; }
+    if (!g_static_scan_ptr[dev]) {
+        // set-up, first call on this device: resolve the device address of the array
+        void *ptr = nullptr;
+        CME213_CUDA(cudaGetSymbolAddress(&ptr, g_static_scan_scratch));
+        g_static_scan_ptr[dev] = ptr;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t tiles = div_up(n, STATIC_SCAN_TILE);
+    // the array still holds the previous call's descriptors and ticket: everything this call reads must start at zero
+    CME213_CUDA(cudaMemsetAsync(g_static_scan_ptr[dev], 0, scan::scratch_bytes(tiles, 4), st));
+    scan::Scratch s = scan::scratch_carve(g_static_scan_ptr[dev], tiles, 4);
+    StaticScanPolicy p{d_in, d_out, nullptr};
+    scan::lookback_scan_kernel<StaticScanPolicy, STATIC_SCAN_THREADS, STATIC_SCAN_VECS, 6>
+        <<<(unsigned)tiles, STATIC_SCAN_THREADS, 0, st>>>(p, n, s, (aligned16(d_in) && aligned16(d_out)) ? 1 : 0);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "exclusive_scan_u32_static");
+    return CME213_OK;
+}

@@ -75,6 +75,24 @@ int cme213_transpose_b64(cme213_ctx *ctx, const void *d_in, void *d_out, int64_t
  * reference: hw/hw4/programming/radixsort.cpp:76-81 and :136-140; my-refs/scan.pdf p.4. */
 int cme213_exclusive_scan_u32(cme213_ctx *ctx, const uint32_t *d_in, uint32_t *d_out, int64_t n, void *stream);
 
+/* The same scan for callers that must not allocate device memory when they call it (a host that gave the
+ * whole GPU to its own pool, a steady-state loop that cannot afford cudaMalloc's device-wide synchronisation
+ * or a late out-of-memory error, a plug-in that only ever receives input and output buffers).  It takes no
+ * context: the look-back descriptors live in a fixed array inside the library (about 0.5 MiB of device
+ * memory on every GPU that loads the library, until the process exits), so the call performs no cudaMalloc,
+ * cudaFree or other allocating call.  Consequences:
+ *   - n is limited to cme213_exclusive_scan_u32_static_max_n() = 2^28 elements; larger n returns
+ *     CME213_ERR_UNSUPPORTED and touches nothing;
+ *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress); make that
+ *     first call during set-up, before any stream capture begins;
+ *   - all calls on a device share the one array (each call clears the part it uses first), so two calls whose
+ *     kernels may overlap on the GPU -- different streams without an ordering between them -- race; keep
+ *     calls on one device ordered.
+ * Results are bit-identical to cme213_exclusive_scan_u32.  In place (d_out == d_in) is allowed.
+ * This entry point has no counterpart in the reference. */
+int64_t cme213_exclusive_scan_u32_static_max_n(void);
+int cme213_exclusive_scan_u32_static(const uint32_t *d_in, uint32_t *d_out, int64_t n, void *stream);
+
 /* Segment descriptions.  The reference stores p segment START offsets s[0]=0 < ... < s[p-1]=n
  * (hw/hw_final/programming/aux/mp1-util.h:118-139).  The kernels read a head-flag bitmask instead
  * (bit i of word i/32 set = element i starts a segment); it depends on s only, so it is built
