@@ -40,6 +40,7 @@ template <typename T> struct Args {
     T *y;
     T *w_out;       // PAGERANK_W: y[r]*inv[r] for the next iteration (may be null)
     T base;         // PAGERANK: 0.5/N
+    const int32_t *order;  // stream kernel: CTA b works on row block order[b] (null = b); see cme213_spmv_csr_*_ordered
 };
 
 template <typename T, int MODE>
@@ -123,7 +124,8 @@ csr_stream_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
     static_assert(TILE % (4 * THREADS) == 0, "tile must be a whole number of 4-wide vectors per thread");
     __shared__ __align__(16) T prod[TILE];
     const int tid = threadIdx.x;
-    const int64_t r0 = row_begin + (int64_t)blockIdx.x * THREADS;
+    const int64_t blk = a.order ? (int64_t)__ldg(a.order + blockIdx.x) : (int64_t)blockIdx.x;
+    const int64_t r0 = row_begin + blk * THREADS;
     const int64_t r = r0 + tid;
     const int64_t rl = r0 + THREADS < row_end ? r0 + THREADS : row_end;
     int rs = 0, re = 0;
@@ -210,14 +212,15 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
 
 template <typename T>
 int spmv_csr_impl(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, const int32_t *d_row_ptr, const int32_t *d_col,
-                  const T *d_val, const T *d_x, T *d_y, int kernel, void *stream) {
+                  const T *d_val, const T *d_x, T *d_y, int kernel, void *stream, const int32_t *d_order = nullptr) {
     CME213_CHECK_CTX(ctx);
     if (row_begin < 0 || row_end < row_begin) { set_error("spmv_csr: bad row range"); return CME213_ERR_INVALID; }
     if (row_end == row_begin) return CME213_OK;
     if (!d_row_ptr || !d_col || !d_val || !d_x || !d_y) { set_error("spmv_csr: null pointer"); return CME213_ERR_INVALID; }
     DeviceGuard g(ctx->device);
-    Args<T> a{d_row_ptr, d_col, d_val, d_x, nullptr, d_y, nullptr, T(0)};
-    return launch_csr<T, MODE_CSR>(ctx, a, row_begin, row_end, kernel, (cudaStream_t)stream);
+    Args<T> a{d_row_ptr, d_col, d_val, d_x, nullptr, d_y, nullptr, T(0), d_order};
+    if (d_order && !(aligned16(d_col) && aligned16(d_val))) { set_error("spmv_csr ordered: col/val must be 16-byte aligned"); return CME213_ERR_INVALID; }
+    return launch_csr<T, MODE_CSR>(ctx, a, row_begin, row_end, d_order ? CME213_CSR_STREAM : kernel, (cudaStream_t)stream);
 }
 
 }  // namespace
@@ -231,6 +234,18 @@ CME213_API int cme213_spmv_csr_f64(cme213_ctx *ctx, int64_t row_begin, int64_t r
                                    const int32_t *d_col, const double *d_val, const double *d_x, double *d_y,
                                    int kernel, void *stream) {
     return spmv_csr_impl<double>(ctx, row_begin, row_end, d_row_ptr, d_col, d_val, d_x, d_y, kernel, stream);
+}
+
+CME213_API int cme213_spmv_csr_block_rows(void) { return 256; }
+CME213_API int cme213_spmv_csr_f32_ordered(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, const int32_t *d_row_ptr,
+                                           const int32_t *d_col, const float *d_val, const float *d_x, float *d_y,
+                                           const int32_t *d_block_order, void *stream) {
+    return spmv_csr_impl<float>(ctx, row_begin, row_end, d_row_ptr, d_col, d_val, d_x, d_y, CME213_CSR_STREAM, stream, d_block_order);
+}
+CME213_API int cme213_spmv_csr_f64_ordered(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, const int32_t *d_row_ptr,
+                                           const int32_t *d_col, const double *d_val, const double *d_x, double *d_y,
+                                           const int32_t *d_block_order, void *stream) {
+    return spmv_csr_impl<double>(ctx, row_begin, row_end, d_row_ptr, d_col, d_val, d_x, d_y, CME213_CSR_STREAM, stream, d_block_order);
 }
 
 CME213_API int cme213_pagerank_propagate(cme213_ctx *ctx, const uint32_t *d_graph_indices,
@@ -248,7 +263,7 @@ CME213_API int cme213_pagerank_propagate(cme213_ctx *ctx, const uint32_t *d_grap
     // 0.5f/(float)array_length, rounded once on the host exactly as pagerank.cu:54 rounds it.
     const float base = 0.5f / (float)array_length;
     Args<float> a{(const int32_t *)d_graph_indices, (const int32_t *)d_graph_edges, nullptr, d_nodes_in,
-                  d_inv_edges_per_node, d_nodes_out, nullptr, base};
+                  d_inv_edges_per_node, d_nodes_out, nullptr, base, nullptr};
     return launch_csr<float, MODE_PAGERANK>(ctx, a, 0, array_length, kernel, (cudaStream_t)stream);
 }
 
@@ -263,10 +278,10 @@ int cme213_internal_pagerank_propagate_w(cme213_ctx *ctx, const uint32_t *d_grap
     const float base = 0.5f / (float)array_length;
     if (d_nodes_in) {
         Args<float> a{(const int32_t *)d_graph_indices, (const int32_t *)d_graph_edges, nullptr, d_nodes_in, d_inv,
-                      d_nodes_out, d_w_out, base};
+                      d_nodes_out, d_w_out, base, nullptr};
         return launch_csr<float, MODE_PAGERANK>(ctx, a, 0, array_length, CME213_CSR_STREAM, (cudaStream_t)stream);
     }
     Args<float> a{(const int32_t *)d_graph_indices, (const int32_t *)d_graph_edges, nullptr, d_w_in, d_inv,
-                  d_nodes_out, d_w_out, base};
+                  d_nodes_out, d_w_out, base, nullptr};
     return launch_csr<float, MODE_PAGERANK_W>(ctx, a, 0, array_length, CME213_CSR_STREAM, (cudaStream_t)stream);
 }

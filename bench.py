@@ -110,11 +110,18 @@ def make_c5(ctx, torch, args, rank, world, dist):
     ctx.call("cme213_fill_uniform_f64", xa, rows, 9)
     xa.mul_(0.05)  # keeps 7-point growth (|lambda| <= 12) far from overflow over the run
     streams = (torch.cuda.current_stream(), torch.cuda.Stream()) if world > 1 else None
-    it = sh.ShardedIterate(rows, world, rank, sh.cuda_spmv(ctx, lo, d_ptr, d_col, d_val, args.csr_kernel), xa, xb,
+    order_fn = (lambda a, b: sh.grid3d_block_order(g, g, g, a, b, strip_lines=args.order_strip)) if args.order_strip > 0 else None
+    it = sh.ShardedIterate(rows, world, rank, sh.cuda_spmv(ctx, lo, d_ptr, d_col, d_val, args.csr_kernel, order_fn), xa, xb,
                            halo=g * g, mode=args.exchange, dist=dist, streams=streams)
     state = {"src": 0}
+    replay = it.capture_pair() if (world > 1 and args.graph) else None
 
     def step():
+        if replay is not None:
+            if state["src"] == 0:
+                replay()          # one graph launch = two passes (A->B, B->A); the odd call is already done
+            state["src"] = 1 - state["src"]
+            return
         it.step(state["src"], 1 - state["src"])
         state["src"] = 1 - state["src"]
 
@@ -125,6 +132,8 @@ def make_c5(ctx, torch, args, rank, world, dist):
                 launches_per_step=1 if it.mode != "halo" else 3,
                 meta={"workload": "C5: CSR SpMV iteration, 3-D 7-point Laplacian %d^3, fp64, row-sharded over %d GPU(s)" % (g, world),
                       "rows": rows, "nnz": nnz_total, "exchange": it.mode, "comm_bytes_per_rank_per_step": it.comm_bytes_per_step,
+                      "launch": "CUDA graph of two passes (kernels + NCCL all-gather)" if replay is not None else "eager",
+                      "cta_order": ("z fastest inside strips of %d grid lines" % args.order_strip) if args.order_strip > 0 else "row order",
                       "l2": "working set %.1f GB per pass >> 126 MB L2" % (alg / 1e9)},
                 keep=(d_ptr, d_col, d_val, xa, xb, it), iterate=it, shard=(lo, hi, d_ptr, d_col, d_val, nnz.value), ctx=ctx)
 
@@ -516,6 +525,8 @@ def main():
     ap.add_argument("--grid", type=int, default=512)
     ap.add_argument("--exchange", default="halo", choices=["halo", "full"])
     ap.add_argument("--csr-kernel", type=int, default=0)
+    ap.add_argument("--graph", type=int, default=1, help="N>1: replay a CUDA graph of two passes instead of launching eagerly")
+    ap.add_argument("--order-strip", type=int, default=0, help="C5: CTA order = z fastest inside strips of this many grid lines (0 = row order)")
     ap.add_argument("--powerlaw-rows", type=int, default=1 << 24)
     ap.add_argument("--window", type=int, default=0)
     ap.add_argument("--regular", type=int, default=0)
@@ -546,6 +557,9 @@ def main():
     peak, peak_kind = measured_peak()
 
     wl = build_workload(args.workload, ctx, torch, args, rank, world, dist)
+    if world > 1 and args.workload == "c5" and args.graph:
+        args.steps += args.steps % 2      # a graph replay is a pair of passes
+        args.warmup += args.warmup % 2
     torch.cuda.synchronize()
     sampler = ClockSampler(local)
     if rank == 0:
@@ -553,6 +567,8 @@ def main():
     l0 = ctx.launches
     ms = time_steps(torch, wl["step"], args.steps, args.warmup, dist)
     launches = (ctx.launches - l0) * args.steps // (args.steps + args.warmup)
+    if launches == 0:  # graph replay: the kernels were recorded once, each replayed pass still launches them
+        launches = wl["launches_per_step"] * args.steps
     clocks = sampler.stop() if rank == 0 else None
     ms_step = ms / args.steps
     value = wl["alg_bytes"] / (ms_step * 1e-3) / 1e9
@@ -611,7 +627,12 @@ def main():
         print(json.dumps(out), flush=True)
     if dist is not None:
         dist.barrier()
-        dist.destroy_process_group()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        # Tearing the NCCL communicator down while a captured graph still references it can block for
+        # minutes; every rank is past the barrier and has nothing left to do, so leave without the teardown.
+        os._exit(0)
 
 
 if __name__ == "__main__":

@@ -117,3 +117,27 @@ def test_pagerank_iterations_match_reference_golden(ctx):
         if it == 0:
             assert np.array_equal(host(A), f["out2"])
     assert np.array_equal(host(A), f["out20"])
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_csr_ordered_launch_is_bitwise_identical(ctx, cme, dtype):
+    # any permutation of the 256-row blocks gives the same bits; the 3-D strip order is one such permutation
+    import importlib
+    import torch
+    sh = importlib.import_module("2012-04_stanford_cme213_b200.sharded")
+    nx, ny, nz = 20, 17, 13
+    ptr, col, val = g.laplace3d(nx, ny, nz, dtype=dtype)
+    n = nx * ny * nz
+    x = np.random.default_rng(6).uniform(-1, 1, n).astype(dtype)
+    want = oracle.csr_spmv(ptr, col, val, x)
+    br = cme.load().cme213_spmv_csr_block_rows()
+    fn = "cme213_spmv_csr_f64_ordered" if dtype == np.float64 else "cme213_spmv_csr_f32_ordered"
+    for lo, hi in [(0, n), (nx * ny, n - nx * ny), (300, 301)]:
+        nblk = -(-(hi - lo) // br)
+        for order in (np.random.default_rng(7).permutation(nblk).astype(np.int32),
+                      sh.grid3d_block_order(nx, ny, nz, lo, hi, br, 4).cpu().numpy()):
+            assert sorted(order.tolist()) == list(range(nblk))
+            d_y = dev(np.full(n, -7.0, dtype=dtype))
+            ctx.call(fn, lo, hi, dev(ptr), dev(col), dev(val), dev(x), d_y, dev(order))
+            got = host(d_y)
+            assert np.array_equal(got[lo:hi], want[lo:hi]) and np.all(got[:lo] == -7.0) and np.all(got[hi:] == -7.0)
