@@ -53,8 +53,8 @@ PROTOTYPES = {
     "cme213_spmv_csr_f32": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _i, _p]),
     "cme213_spmv_csr_f64": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _i, _p]),
     "cme213_spmv_csr_block_rows": (_i, []),
-    "cme213_spmv_csr_f32_ordered": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _p, _p]),
-    "cme213_spmv_csr_f64_ordered": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _p, _p]),
+    "cme213_spmv_csr_f32_ordered": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _p, _i64, _p]),
+    "cme213_spmv_csr_f64_ordered": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _p, _i64, _p]),
     "cme213_pagerank_propagate": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _p]),
     "cme213_spmv_ell_f32": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _p, _p]),
     "cme213_spmv_ell_f64": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _p, _p]),

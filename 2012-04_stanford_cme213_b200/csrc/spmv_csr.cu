@@ -170,7 +170,8 @@ csr_stream_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
 }
 
 template <typename T, int MODE>
-int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row_end, int kernel, cudaStream_t st) {
+int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row_end, int kernel, cudaStream_t st,
+               int64_t num_blocks = -1) {
     const int64_t rows = row_end - row_begin;
     if (rows <= 0) return CME213_OK;
     int kind = kernel & 0xFF;
@@ -200,7 +201,8 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
         }
     } else if (kind == CME213_CSR_STREAM) {
         constexpr int THREADS = 256, TILE = 2048;
-        const int64_t blocks = div_up(rows, THREADS);
+        const int64_t blocks = num_blocks >= 0 ? num_blocks : div_up(rows, THREADS);
+        if (blocks == 0) return CME213_OK;
         csr_stream_kernel<T, MODE, THREADS, TILE><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end);
         CME213_LAUNCHED(ctx, "csr_stream_kernel");
     } else {
@@ -212,7 +214,8 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
 
 template <typename T>
 int spmv_csr_impl(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, const int32_t *d_row_ptr, const int32_t *d_col,
-                  const T *d_val, const T *d_x, T *d_y, int kernel, void *stream, const int32_t *d_order = nullptr) {
+                  const T *d_val, const T *d_x, T *d_y, int kernel, void *stream, const int32_t *d_order = nullptr,
+                  int64_t num_blocks = -1) {
     CME213_CHECK_CTX(ctx);
     if (row_begin < 0 || row_end < row_begin) { set_error("spmv_csr: bad row range"); return CME213_ERR_INVALID; }
     if (row_end == row_begin) return CME213_OK;
@@ -220,7 +223,9 @@ int spmv_csr_impl(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, const int
     DeviceGuard g(ctx->device);
     Args<T> a{d_row_ptr, d_col, d_val, d_x, nullptr, d_y, nullptr, T(0), d_order};
     if (d_order && !(aligned16(d_col) && aligned16(d_val))) { set_error("spmv_csr ordered: col/val must be 16-byte aligned"); return CME213_ERR_INVALID; }
-    return launch_csr<T, MODE_CSR>(ctx, a, row_begin, row_end, d_order ? CME213_CSR_STREAM : kernel, (cudaStream_t)stream);
+    if (d_order && (num_blocks < 0 || num_blocks > div_up(row_end - row_begin, 256))) { set_error("spmv_csr ordered: bad num_blocks"); return CME213_ERR_INVALID; }
+    return launch_csr<T, MODE_CSR>(ctx, a, row_begin, row_end, d_order ? CME213_CSR_STREAM : kernel, (cudaStream_t)stream,
+                                   d_order ? num_blocks : -1);
 }
 
 }  // namespace
@@ -239,13 +244,13 @@ CME213_API int cme213_spmv_csr_f64(cme213_ctx *ctx, int64_t row_begin, int64_t r
 CME213_API int cme213_spmv_csr_block_rows(void) { return 256; }
 CME213_API int cme213_spmv_csr_f32_ordered(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, const int32_t *d_row_ptr,
                                            const int32_t *d_col, const float *d_val, const float *d_x, float *d_y,
-                                           const int32_t *d_block_order, void *stream) {
-    return spmv_csr_impl<float>(ctx, row_begin, row_end, d_row_ptr, d_col, d_val, d_x, d_y, CME213_CSR_STREAM, stream, d_block_order);
+                                           const int32_t *d_block_order, int64_t num_blocks, void *stream) {
+    return spmv_csr_impl<float>(ctx, row_begin, row_end, d_row_ptr, d_col, d_val, d_x, d_y, CME213_CSR_STREAM, stream, d_block_order, num_blocks);
 }
 CME213_API int cme213_spmv_csr_f64_ordered(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, const int32_t *d_row_ptr,
                                            const int32_t *d_col, const double *d_val, const double *d_x, double *d_y,
-                                           const int32_t *d_block_order, void *stream) {
-    return spmv_csr_impl<double>(ctx, row_begin, row_end, d_row_ptr, d_col, d_val, d_x, d_y, CME213_CSR_STREAM, stream, d_block_order);
+                                           const int32_t *d_block_order, int64_t num_blocks, void *stream) {
+    return spmv_csr_impl<double>(ctx, row_begin, row_end, d_row_ptr, d_col, d_val, d_x, d_y, CME213_CSR_STREAM, stream, d_block_order, num_blocks);
 }
 
 CME213_API int cme213_pagerank_propagate(cme213_ctx *ctx, const uint32_t *d_graph_indices,

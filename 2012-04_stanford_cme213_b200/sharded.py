@@ -13,6 +13,8 @@ stream while the interior rows are computed.
 Exchange modes
   full : every rank all-gathers its whole y slice into everybody's x (N*8/P bytes sent per rank).
          Always correct; costs more than the SpMV itself beyond 2 GPUs for the 7-point stencil.
+  p2p  : same data as `halo`, moved by NCCL send/recv between neighbours straight out of / into the full-length
+         vector (no pack / unpack copies).
   halo : for a matrix of half-bandwidth `halo` (max |col - row|), rank r only needs the last `halo`
          entries of rank r-1 and the first `halo` of rank r+1.  Each rank contributes its first and
          last `halo` entries to ONE all-gather (2*halo values per rank) and copies the two pieces it
@@ -55,7 +57,7 @@ class ShardedIterate:
         self.lo, self.hi = self.parts[rank]
         self.mode = mode if world > 1 else "none"
         self.halo = int(halo) if halo is not None else None
-        if self.mode == "halo":
+        if self.mode in ("halo", "p2p"):
             smallest = min(e - b for b, e in self.parts)
             if self.halo is None or not equal_partition_ok(rows, world) or smallest < 2 * self.halo:
                 self.mode = "full"  # shards too thin (or ragged) for the two-piece halo layout
@@ -71,6 +73,8 @@ class ShardedIterate:
             self.comm_bytes_per_step = (world - 1) * (self.hi - self.lo) * x_a.element_size()
         elif self.mode == "halo":
             self.comm_bytes_per_step = (world - 1) * 2 * self.halo * x_a.element_size()
+        elif self.mode == "p2p":
+            self.comm_bytes_per_step = ((rank > 0) + (rank < world - 1)) * self.halo * x_a.element_size()
 
     # -- helpers ---------------------------------------------------------------------------------
     def _on(self, stream):
@@ -100,10 +104,40 @@ class ShardedIterate:
             return
         h = self.halo
         cs, ms = self.compute_stream, self.comm_stream
+        if self.mode == "p2p":
+            with self._on(cs):
+                # 1. boundary rows first (one launch when the kernel binding offers it): they are the neighbours' halo
+                if hasattr(self.spmv, "two_ranges"):
+                    self.spmv.two_ranges(lo, hi, h, xin, xout)
+                else:
+                    self.spmv(lo, lo + h, xin, xout)
+                    self.spmv(hi - h, hi, xin, xout)
+                ready = self._event(cs)
+            with self._on(ms):
+                # 2. neighbour exchange straight from / into the full-length vector: no pack, no unpack
+                if ready is not None:
+                    ms.wait_event(ready)
+                D = self.dist
+                ops = []
+                if self.rank > 0:
+                    ops += [D.P2POp(D.isend, xout[lo:lo + h], self.rank - 1), D.P2POp(D.irecv, xout[lo - h:lo], self.rank - 1)]
+                if self.rank < self.world - 1:
+                    ops += [D.P2POp(D.isend, xout[hi - h:hi], self.rank + 1), D.P2POp(D.irecv, xout[hi:hi + h], self.rank + 1)]
+                for w in D.batch_isend_irecv(ops):
+                    w.wait()
+                done = self._event(ms)
+            with self._on(cs):
+                self.spmv(lo + h, hi - h, xin, xout)
+                if done is not None:
+                    cs.wait_event(done)
+            return
         with self._on(cs):
             # 1. boundary rows first: they are the neighbours' halo
-            self.spmv(lo, lo + h, xin, xout)
-            self.spmv(hi - h, hi, xin, xout)
+            if hasattr(self.spmv, "two_ranges"):
+                self.spmv.two_ranges(lo, hi, h, xin, xout)
+            else:
+                self.spmv(lo, lo + h, xin, xout)
+                self.spmv(hi - h, hi, xin, xout)
             self.send[:h].copy_(xout[lo:lo + h])
             self.send[h:].copy_(xout[hi - h:hi])
             ready = self._event(cs)
@@ -214,11 +248,31 @@ def cuda_spmv(ctx, row_lo_global, d_row_ptr_local, d_col, d_val, kernel=0, order
             if (lo, hi) not in orders:
                 orders[(lo, hi)] = order_fn(lo, hi)
             ctx.call(fn + "_ordered", lo - row_lo_global, hi - row_lo_global, d_row_ptr_local, d_col, d_val, x_full,
-                     y_full.data_ptr() + row_lo_global * esize, orders[(lo, hi)], stream=torch.cuda.current_stream())
+                     y_full.data_ptr() + row_lo_global * esize, orders[(lo, hi)], orders[(lo, hi)].numel(),
+                     stream=torch.cuda.current_stream())
             return
         ctx.call(fn, lo - row_lo_global, hi - row_lo_global, d_row_ptr_local, d_col, d_val, x_full,
                  y_full.data_ptr() + row_lo_global * esize, kernel, stream=torch.cuda.current_stream())
 
+    def spmv_two_ranges(lo, hi, h, x_full, y_full):
+        """rows [lo, lo+h) and [hi-h, hi) of the shard in ONE launch (h a multiple of the kernel's block rows)."""
+        key = ("pair", lo, hi, h)
+        if key not in orders:
+            br = int(ctx.lib.cme213_spmv_csr_block_rows())
+            if h % br or (hi - lo) % br:
+                orders[key] = None
+            else:
+                nb, hb = (hi - lo) // br, h // br
+                orders[key] = torch.cat([torch.arange(hb, device="cuda"), torch.arange(nb - hb, nb, device="cuda")]).to(torch.int32)
+        o = orders[key]
+        if o is None:
+            spmv(lo, lo + h, x_full, y_full)
+            spmv(hi - h, hi, x_full, y_full)
+            return
+        ctx.call(fn + "_ordered", lo - row_lo_global, hi - row_lo_global, d_row_ptr_local, d_col, d_val, x_full,
+                 y_full.data_ptr() + row_lo_global * esize, o, o.numel(), stream=torch.cuda.current_stream())
+
+    spmv.two_ranges = spmv_two_ranges
     return spmv
 
 

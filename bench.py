@@ -129,7 +129,7 @@ def make_c5(ctx, torch, args, rank, world, dist):
     alg = nnz_total * 12 + (rows + 1) * 4 + rows * 8 * 2
     local_alg = nnz.value * 12 + (nloc + 1) * 4 + nloc * 8 * 2
     return dict(step=step, alg_bytes=alg, local_alg_bytes=local_alg, flops=2 * nnz_total, kernel="csr_stream_kernel<double>",
-                launches_per_step=1 if it.mode != "halo" else 3,
+                launches_per_step=1 if it.mode not in ("halo", "p2p") else 2,
                 meta={"workload": "C5: CSR SpMV iteration, 3-D 7-point Laplacian %d^3, fp64, row-sharded over %d GPU(s)" % (g, world),
                       "rows": rows, "nnz": nnz_total, "exchange": it.mode, "comm_bytes_per_rank_per_step": it.comm_bytes_per_step,
                       "launch": "CUDA graph of two passes (kernels + NCCL all-gather)" if replay is not None else "eager",
@@ -523,7 +523,8 @@ def main():
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--workload", default="c5")
     ap.add_argument("--grid", type=int, default=512)
-    ap.add_argument("--exchange", default="halo", choices=["halo", "full"])
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "halo", "full"],
+                    help="N>1: p2p = NCCL send/recv of the halo planes between neighbours; halo = one all-gather of every rank's boundary planes; full = all-gather of the whole vector")
     ap.add_argument("--csr-kernel", type=int, default=0)
     ap.add_argument("--graph", type=int, default=1, help="N>1: replay a CUDA graph of two passes instead of launching eagerly")
     ap.add_argument("--order-strip", type=int, default=0, help="C5: CTA order = z fastest inside strips of this many grid lines (0 = row order)")

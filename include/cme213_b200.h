@@ -134,19 +134,20 @@ int cme213_spmv_csr_f64(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, con
                         const int32_t *d_col, const double *d_val, const double *d_x, double *d_y, int kernel,
                         void *stream);
 
-/* Same result (bit for bit), with the caller choosing the order in which the stream kernel's CTAs walk the
- * matrix: CTA b computes the block of cme213_spmv_csr_block_rows() consecutive rows number d_block_order[b]
- * (counted from row_begin).  d_block_order must be a permutation of 0 .. ceil((row_end-row_begin)/block_rows)-1.
- * An order that keeps rows touching the same x entries close together in time (e.g. z fastest inside a strip of
- * grid lines for a 3-D stencil) lets the x gathers hit in L2 instead of re-reading HBM.  No reference counterpart:
- * the reference's kernels walk rows in index order (pagerank.cu:72). */
+/* Same result (bit for bit), with the caller choosing WHICH blocks of cme213_spmv_csr_block_rows() consecutive
+ * rows one launch computes and in what order: CTA b (b < num_blocks) computes block number d_block_order[b],
+ * counted from row_begin.  d_block_order holds distinct block numbers < ceil((row_end-row_begin)/block_rows);
+ * rows of blocks that are not listed are left untouched.  Uses: the multi-GPU iterate computes the blocks of
+ * its first and last halo rows in one launch before the exchange starts; an order that keeps rows touching
+ * the same x entries close in time was tried for the 3-D stencil and measured slower (profiles/r01_notes.md).
+ * No reference counterpart: the reference's kernels walk rows in index order (pagerank.cu:72). */
 int cme213_spmv_csr_block_rows(void);
 int cme213_spmv_csr_f32_ordered(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, const int32_t *d_row_ptr,
                                 const int32_t *d_col, const float *d_val, const float *d_x, float *d_y,
-                                const int32_t *d_block_order, void *stream);
+                                const int32_t *d_block_order, int64_t num_blocks, void *stream);
 int cme213_spmv_csr_f64_ordered(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, const int32_t *d_row_ptr,
                                 const int32_t *d_col, const double *d_val, const double *d_x, double *d_y,
-                                const int32_t *d_block_order, void *stream);
+                                const int32_t *d_block_order, int64_t num_blocks, void *stream);
 
 /* PageRank propagate: out[i] = 0.5f/N + 0.5f * sum_j in[e[j]] * inv[e[j]].
  * reference: hw/hw1/programming/pagerank.cu:45-56 (CPU), :70-83 (GPU). */

@@ -4,7 +4,7 @@
         scripts/verify_sharded.py [--grid 128] [--iters 6]
 
 Every rank builds its z-slab shard of the 7-point Laplacian on the device, runs the row-sharded iterate
-(halo and full exchange) through the C ABI, and rank 0 compares the gathered result BITWISE with the
+(neighbour send/recv, halo all-gather and full all-gather) through the C ABI, and rank 0 compares the gathered result BITWISE with the
 same iteration done on one GPU over the whole matrix, and with the CPU oracle at a size it finishes
 quickly.  Row sharding does not change the per-row summation order, so the results must be identical."""
 import argparse
@@ -50,7 +50,7 @@ def main():
     assert sh.half_bandwidth(d_ptr, d_col, lo) == g * g
     ok = True
     results = {}
-    for mode in ("halo", "full"):
+    for mode in ("p2p", "halo", "full"):
         xa = torch.empty(rows, dtype=torch.float64, device="cuda")
         ctx.call("cme213_fill_uniform_f64", xa, rows, 9)
         xb = torch.zeros_like(xa)

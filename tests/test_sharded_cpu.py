@@ -61,6 +61,8 @@ def _worker(rank, world, port, grid, mode, iters, out):
     (2, (4, 4, 3), "halo", "full"),    # rows not divisible by 2 planes each: ragged -> falls back... (48 rows / 2 ok, 1.5 planes)
     (3, (5, 4, 9), "halo", "halo"),
     (3, (5, 4, 6), "halo", "halo"),    # shards of exactly two planes: boundary rows cover the whole shard
+    (2, (6, 5, 8), "p2p", "p2p"),
+    (3, (5, 4, 9), "p2p", "p2p"),
 ])
 def test_sharded_iterate_matches_single_process(world, grid, mode, expect_mode):
     ctx = mp.get_context("spawn")
@@ -75,8 +77,11 @@ def test_sharded_iterate_matches_single_process(world, grid, mode, expect_mode):
     got_mode, equal, comm = out.get()
     assert equal, "sharded result differs from the single-process oracle"
     rows = grid[0] * grid[1] * grid[2]
+    assert got_mode == expect_mode
     if got_mode == "halo":
         assert comm == (world - 1) * 2 * grid[0] * grid[1] * 8
+    elif got_mode == "p2p":
+        assert comm == grid[0] * grid[1] * 8   # rank 0 has one neighbour
     else:
         assert comm == (world - 1) * (rows // world) * 8
 

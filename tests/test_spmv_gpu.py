@@ -138,6 +138,16 @@ def test_csr_ordered_launch_is_bitwise_identical(ctx, cme, dtype):
                       sh.grid3d_block_order(nx, ny, nz, lo, hi, br, 4).cpu().numpy()):
             assert sorted(order.tolist()) == list(range(nblk))
             d_y = dev(np.full(n, -7.0, dtype=dtype))
-            ctx.call(fn, lo, hi, dev(ptr), dev(col), dev(val), dev(x), d_y, dev(order))
+            ctx.call(fn, lo, hi, dev(ptr), dev(col), dev(val), dev(x), d_y, dev(order), nblk)
             got = host(d_y)
             assert np.array_equal(got[lo:hi], want[lo:hi]) and np.all(got[:lo] == -7.0) and np.all(got[hi:] == -7.0)
+    # a subset of the blocks: only those rows are written (the multi-GPU boundary launch)
+    nblk = -(-n // br)
+    sub = np.array([nblk - 1, 0, 3], np.int32)
+    d_y = dev(np.full(n, -7.0, dtype=dtype))
+    ctx.call(fn, 0, n, dev(ptr), dev(col), dev(val), dev(x), d_y, dev(sub), len(sub))
+    got = host(d_y)
+    mask = np.zeros(n, bool)
+    for b in sub:
+        mask[b * br:(b + 1) * br] = True
+    assert np.array_equal(got[mask], want[mask]) and np.all(got[~mask] == -7.0)
