@@ -438,6 +438,12 @@ template <class P, int THREADS, int VECS> struct BulkLayout {
         return o;
     }
     static constexpr int STAGE_BYTES = stream_off(P::NIN);
+    __host__ __device__ static constexpr bool aligned() {
+        for (int i = 0; i < P::NIN; i++)
+            if (P::tile_bytes(i, TILE_ITEMS) % 16 != 0) return false;
+        return true;
+    }
+    static_assert(aligned(), "every staged stream must be a whole number of 16-byte units per tile (bulk copy granularity)");
 };
 
 // Cross-CTA state of the wave protocol: slot arrays of {value, flag, ready}.
@@ -671,6 +677,305 @@ lookback_scan_bulk_kernel(P p, int64_t n, int64_t num_tiles, WaveScratch ws) {
         finish_and_store<P, VECS>(p, base_p, THREADS, n, full_p, v_p, hf_p, cst_p, apply_p, core.carry, aux_p);
     }
 }
+
+// ---- front end 3: as front end 2, but blocked per-thread layout and bulk-copy stores ---------------------
+// For policies whose output is one dense array of T (the plain scans).  Differences from front end 2:
+//   * a thread owns VECS *consecutive* vectors of the staged tile (odd VECS: its 128-bit shared loads and
+//     stores are bank-conflict free), scans them serially and takes part in ONE warp scan per tile instead of
+//     one per vector: about a third of the instructions per item;
+//   * results go back into the tile's ring slot and leave the SM as one cp.async.bulk store (smem -> global),
+//     so neither loads nor stores occupy the LSU or wait in the threads;
+//   * ring of STAGES >= 3 slots: [stored last iteration, being refilled] [finishing] [computing] [loading ...].
+__device__ __forceinline__ void bulk_store(void *gmem_dst, const void *smem_src, unsigned bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem_dst), "r"(smem_u32(smem_src)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_store_wait_read_all() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+template <class P, int THREADS, int VECS, int STAGES, int DPL, int DEFER>
+__global__ void __launch_bounds__(THREADS, 1)
+scan_bulk_blocked_kernel(P p, int64_t n, int64_t num_tiles, WaveScratch ws) {
+    using T = typename P::T;
+    using L = BulkLayout<P, THREADS, VECS>;
+    constexpr int IPV = P::IPV;
+    constexpr bool SEG = P::SEG;
+    constexpr int WARPS = THREADS / 32;
+    constexpr int ITEMS = VECS * IPV;  // per thread, consecutive
+    static_assert(WARPS <= 32 && ITEMS <= 32, "one warp scans the warp aggregates; head bits fit a word");
+    static_assert(STAGES >= DEFER + 2, "DEFER pending tiles + the one being computed + at least one slot in flight");
+    extern __shared__ __align__(128) unsigned char ring[];  // STAGES * STAGE_BYTES
+    __shared__ __align__(8) uint64_t full_bar[STAGES];
+    __shared__ T s_agg_v[32], s_excl_v[32], s_carry;
+    __shared__ unsigned char s_agg_f[32], s_excl_f[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const bool filler = tid == THREADS - 32;                 // lane 0 of the last warp feeds and drains the ring
+    const int64_t G = gridDim.x - 1;                         // data CTAs; CTA number G only scans
+
+    if ((int64_t)blockIdx.x == G) {  // the scanner CTA (see front end 2)
+        if (tid >= 32) return;
+        T c0 = T(0);
+        int wv_i = 0;
+        auto sstamp = [&](int k) {
+            if (ws.trace && tid == 0 && wv_i < TRACE_MAX_IT) {
+                unsigned long long t;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                ws.trace[((size_t)G * TRACE_MAX_IT + wv_i) * 8 + k] = t;
+            }
+        };
+        for (int64_t wave_first = 0; wave_first < num_tiles; wave_first += G, wv_i++) {
+            const int64_t wave_cnt = num_tiles - wave_first < G ? num_tiles - wave_first : G;
+            sstamp(0);
+            T a[DPL], e[DPL];
+            unsigned hb = 0, before;
+            bool pending;
+            do {
+                pending = false;
+#pragma unroll
+                for (int q = 0; q < DPL; q++) {
+                    const int64_t j = (int64_t)lane * DPL + q;
+                    a[q] = T(0);
+                    if (j < wave_cnt) {
+                        unsigned f;
+                        pending |= !Slot<T>::read(ws.A, wave_first + j, a[q], f);
+                        if (SEG && f) hb |= 1u << q; else hb &= ~(1u << q);
+                    }
+                }
+            } while (__any_sync(0xFFFFFFFFu, pending));
+            sstamp(1);
+            T total;
+            bool any;
+            warp_array_scan<T, SEG, DPL>(a, hb, lane, e, before, total, any);
+#pragma unroll
+            for (int q = 0; q < DPL; q++) {
+                const int64_t j = (int64_t)lane * DPL + q;
+                if (j < wave_cnt) Slot<T>::publish(ws.X, wave_first + j, ((before >> q) & 1u) ? e[q] : c0 + e[q], 0);
+            }
+            c0 = any ? total : c0 + total;
+            sstamp(2);
+        }
+        return;
+    }
+
+    auto stage_ptr = [&](int stage) { return ring + (size_t)stage * L::STAGE_BYTES; };
+    auto fill = [&](int stage, int64_t t) {
+        if (t >= num_tiles) return;
+        const int64_t base = t * L::TILE_ITEMS;
+        if (base + L::TILE_ITEMS <= n) {
+            mbar_expect_tx(&full_bar[stage], (unsigned)L::STAGE_BYTES);
+#pragma unroll
+            for (int s = 0; s < P::NIN; s++)
+                bulk_load(stage_ptr(stage) + L::stream_off(s), (const unsigned char *)p.in_ptr(s) + t * P::tile_bytes(s, L::TILE_ITEMS),
+                          (unsigned)P::tile_bytes(s, L::TILE_ITEMS), &full_bar[stage]);
+        } else {
+            mbar_arrive(&full_bar[stage]);  // ragged last tile: read and written straight from/to global with guards
+        }
+    };
+    auto stamp = [&](int it, int k) {
+        if (ws.trace && tid == 0 && it < TRACE_MAX_IT) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            ws.trace[((size_t)blockIdx.x * TRACE_MAX_IT + it) * 8 + k] = t;
+        }
+    };
+
+    if (filler) {
+        for (int s = 0; s < STAGES; s++) mbar_init(&full_bar[s], 1);
+        mbar_fence_init();
+        for (int s = 0; s < STAGES; s++) fill(s, (int64_t)s * G + blockIdx.x);
+    }
+    __syncthreads();
+
+    // Tiles whose finish is deferred: the finish of tile i (add its exclusive prefix, write back, store) runs
+    // DEFER iterations after its local phase, so the scanner's round trips and a late CTA of the wave are
+    // hidden behind useful work.  A pending tile keeps its inputs in its ring slot; only these few values stay
+    // in registers.  q[0] is the oldest pending tile.
+    struct Pending { T cst; int64_t tile, base; unsigned apply; int stage; };
+    Pending q[DEFER];
+#pragma unroll
+    for (int d = 0; d < DEFER; d++) q[d].tile = -1;
+
+    // re-reads the tile's inputs from its slot, adds the prefix in front of the thread's run, writes the results
+    // back to the slot; the caller then hands the slot to the copy engine
+    auto finish_slot = [&](const Pending &t, T carry_tile) {
+        const unsigned char *in[P::NIN];
+#pragma unroll
+        for (int s = 0; s < P::NIN; s++) in[s] = stage_ptr(t.stage) + L::stream_off(s);
+        T c = t.apply ? carry_tile + t.cst : t.cst;
+#pragma unroll
+        for (int i = 0; i < VECS; i++) {
+            const int vec = tid * VECS + i;
+            T v[IPV];
+            unsigned h;
+            typename P::Aux aux;
+            p.load_smem(in, vec, L::TILE_VECS, t.base + (int64_t)vec * IPV, n, v, h, aux);
+            typename P::V16T o;
+            T *e = reinterpret_cast<T *>(&o);
+#pragma unroll
+            for (int j = 0; j < IPV; j++) {
+                if (SEG && ((h >> j) & 1u)) c = T(0);
+                const T ex = c;
+                c = c + v[j];
+                e[j] = P::INCLUSIVE_OUT ? c : ex;
+            }
+            *reinterpret_cast<typename P::V16T *>(stage_ptr(t.stage) + (size_t)vec * 16) = o;
+        }
+        fence_proxy_async_smem();  // make the generic-proxy writes visible to the bulk-copy engine
+    };
+    auto store_slot = [&](const Pending &t) {
+        bulk_store(reinterpret_cast<unsigned char *>(p.out_ptr()) + t.base * (int64_t)sizeof(T), stage_ptr(t.stage),
+                   (unsigned)(L::TILE_ITEMS * sizeof(T)));
+    };
+    auto poll = [&](int64_t t) {  // warp 0: exclusive prefix of tile t into s_carry
+        T carry;
+        unsigned f;
+        while (!Slot<T>::read(ws.X, t, carry, f)) {}
+        if (lane == 0) s_carry = carry;
+    };
+
+    int it = 0;
+    for (int64_t tile = blockIdx.x; tile < num_tiles; tile += G, it++) {
+        const int stage = it % STAGES;
+        const int64_t tile_base = tile * L::TILE_ITEMS;
+        const bool full = tile_base + L::TILE_ITEMS <= n;
+        stamp(it, 0);
+        // first look at the oldest pending tile's prefix now, so that its L2 round trip overlaps the local phase
+        T early_carry = T(0);
+        bool early_ok = false;
+        if (warp == 0 && q[0].tile >= 0) {
+            unsigned f;
+            early_ok = Slot<T>::read(ws.X, q[0].tile, early_carry, f);
+        }
+        mbar_wait(&full_bar[stage], (unsigned)((it / STAGES) & 1));
+        stamp(it, 1);
+        T v[VECS][IPV];
+        unsigned hf = 0;
+        if (full) {
+            const unsigned char *in[P::NIN];
+#pragma unroll
+            for (int s = 0; s < P::NIN; s++) in[s] = stage_ptr(stage) + L::stream_off(s);
+#pragma unroll
+            for (int i = 0; i < VECS; i++) {
+                const int vec = tid * VECS + i;
+                unsigned h;
+                typename P::Aux aux;
+                p.load_smem(in, vec, L::TILE_VECS, tile_base + (int64_t)vec * IPV, n, v[i], h, aux);
+                hf |= h << (i * IPV);
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < VECS; i++) {
+                unsigned h;
+                typename P::Aux aux;
+                p.load(tile_base + ((int64_t)tid * VECS + i) * IPV, n, false, v[i], h, aux);
+                hf |= h << (i * IPV);
+            }
+        }
+        // thread-serial aggregate of the run, then ONE warp scan
+        T a = v[0][0];
+#pragma unroll
+        for (int k = 1; k < ITEMS; k++) a = (SEG && ((hf >> k) & 1u)) ? v[k / IPV][k % IPV] : a + v[k / IPV][k % IPV];
+        const unsigned m = SEG ? __ballot_sync(0xFFFFFFFFu, hf != 0) : 0u;
+        const int lo = SEG ? 31 - __clz(m & (0xFFFFFFFFu >> (31 - lane))) : -1;
+        const T wv = warp_scan_inclusive<T, SEG>(a, lane, lo);
+        if (lane == 31) { s_agg_v[warp] = wv; s_agg_f[warp] = (unsigned char)(m != 0); }
+        __syncthreads();  // S1: warp aggregates visible
+        if (filler && it >= DEFER + 1) {
+            // Slots in use right now: this tile's and the DEFER pending ones.  The tile before those was stored
+            // during the previous iteration; once the copy engine has read its slot, the slot takes the tile
+            // STAGES-DEFER-1 waves ahead.
+            bulk_store_wait_read_all();
+            fill((it - DEFER - 1) % STAGES, tile + (int64_t)(STAGES - DEFER - 1) * G);
+        }
+        if (warp == 0) {
+            T ag[1], ex[1];
+            ag[0] = lane < WARPS ? s_agg_v[lane] : T(0);
+            const unsigned hb = (SEG && lane < WARPS && s_agg_f[lane]) ? 1u : 0u;
+            unsigned before;
+            T tile_agg;
+            bool tile_f;
+            warp_array_scan<T, SEG, 1>(ag, hb, lane, ex, before, tile_agg, tile_f);
+            stamp(it, 2);
+            if (lane == 0) Slot<T>::publish(ws.A, tile, tile_agg, tile_f);
+            if (lane < WARPS) { s_excl_v[lane] = ex[0]; s_excl_f[lane] = (unsigned char)(before & 1u); }
+            stamp(it, 3);
+            if (q[0].tile >= 0) {  // DEFER iterations old: normally the early look already has it
+                if (early_ok) { if (lane == 0) s_carry = early_carry; }
+                else poll(q[0].tile);
+            }
+            stamp(it, 5);
+        }
+        __syncthreads();  // S2
+        stamp(it, 6);
+        T w = __shfl_up_sync(0xFFFFFFFFu, wv, 1);
+        if (lane == 0) w = T(0);
+        const bool head_before_lane = SEG && (m & ((1u << lane) - 1u)) != 0;
+        Pending cur;
+        cur.cst = w; cur.apply = 0; cur.tile = tile; cur.base = tile_base; cur.stage = stage;
+        if (!head_before_lane) {
+            cur.cst = s_excl_v[warp] + cur.cst;
+            cur.apply = !(SEG && s_excl_f[warp]);
+        }
+        if (!full) {
+            // The ragged last tile of the whole input is not in a slot.  It is this CTA's last tile: drain the
+            // pending tiles, then finish it straight from registers with guarded stores.
+            const T carry_oldest = s_carry;
+#pragma unroll
+            for (int d = 0; d < DEFER; d++) {
+                if (q[d].tile < 0) continue;
+                if (d > 0) {
+                    __syncthreads();
+                    if (warp == 0) poll(q[d].tile);
+                    __syncthreads();
+                }
+                finish_slot(q[d], d == 0 ? carry_oldest : s_carry);
+                __syncthreads();
+                if (filler) store_slot(q[d]);
+                q[d].tile = -1;
+            }
+            __syncthreads();
+            if (warp == 0) poll(tile);
+            __syncthreads();
+            T c = cur.apply ? s_carry + cur.cst : cur.cst;
+#pragma unroll
+            for (int i = 0; i < VECS; i++) {
+                T incl[IPV], excl[IPV];
+#pragma unroll
+                for (int j = 0; j < IPV; j++) {
+                    if (SEG && ((hf >> (i * IPV + j)) & 1u)) c = T(0);
+                    excl[j] = c;
+                    c = c + v[i][j];
+                    incl[j] = c;
+                }
+                typename P::Aux aux;
+                p.store(tile_base + ((int64_t)tid * VECS + i) * IPV, n, false, incl, excl, aux);
+            }
+            break;
+        }
+        if (q[0].tile >= 0) {
+            finish_slot(q[0], s_carry);
+            __syncthreads();  // S3: the whole tile is back in its slot
+            if (filler) store_slot(q[0]);
+        }
+        stamp(it, 7);
+#pragma unroll
+        for (int d = 0; d + 1 < DEFER; d++) q[d] = q[d + 1];
+        q[DEFER - 1] = cur;
+    }
+    // drain the pending tiles of this CTA, oldest first
+#pragma unroll
+    for (int d = 0; d < DEFER; d++) {
+        if (q[d].tile < 0) continue;
+        __syncthreads();
+        if (warp == 0) poll(q[d].tile);
+        __syncthreads();
+        finish_slot(q[d], s_carry);
+        __syncthreads();
+        if (filler) store_slot(q[d]);
+    }
+    if (filler) bulk_store_wait_read_all();  // shared memory must outlive the copy engine's reads
+}
+
 #endif  // __CUDACC__
 
 // Tile configuration (tuned on B200, see profiles/r01_notes.md).
@@ -681,6 +986,9 @@ template <class P> struct Cfg {
     static constexpr int VECS = STAGE_TARGET / (THREADS * VEC_BYTES) > 0 ? STAGE_TARGET / (THREADS * VEC_BYTES) : 1;
     static constexpr int STAGES = 2;   // large tiles amortise the ~0.7 us prefix round trip better than deep rings (profiles/r01_notes.md)
     static constexpr int DPL = 5;                               // a wave holds at most 32*DPL = 160 tiles
+    // blocked bulk kernel (dense-output policies): ~700 threads x 5 consecutive vectors = 55 KiB tiles, 4 ring slots,
+    // finish deferred by 2 iterations (sweep in profiles/r01_notes.md; segmented scans also stage their flag words)
+    static constexpr int B_THREADS = P::SEG ? 640 : 704, B_VECS = 5, B_STAGES = 4, B_DEFER = 2;
     static constexpr int DIRECT_THREADS = 256, DIRECT_VECS = 4; // one-tile-per-CTA kernel
     static constexpr int DIRECT_MIN_BLOCKS = (P::SEG || P::NIN > 1) ? 4 : 6;   // register caps: 64 / 40 per thread
 };
@@ -706,7 +1014,7 @@ int launch_direct(cme213_ctx *ctx, const P &p, int64_t n, bool vec_ok, cudaStrea
     return CME213_OK;
 }
 
-template <class P, int THREADS, int VECS, int STAGES, int DPL>
+template <class P, int THREADS, int VECS, int STAGES, int DPL, bool BLOCKED = false, int DEFER = 1>
 int launch_bulk(cme213_ctx *ctx, const P &p, int64_t n, cudaStream_t st, const char *name, void *scratch_mem,
                 size_t scratch_avail) {
     using T = typename P::T;
@@ -714,7 +1022,9 @@ int launch_bulk(cme213_ctx *ctx, const P &p, int64_t n, cudaStream_t st, const c
     int64_t tiles = div_up(n, (int64_t)L::TILE_ITEMS);
     if (tiles > 0x7FFFFFFFLL) { set_error("%s: n too large", name); return CME213_ERR_UNSUPPORTED; }
 #ifdef __CUDACC__
-    auto kern = lookback_scan_bulk_kernel<P, THREADS, VECS, STAGES, DPL>;
+    void (*kern)(P, int64_t, int64_t, WaveScratch);
+    if constexpr (BLOCKED) kern = scan_bulk_blocked_kernel<P, THREADS, VECS, STAGES, DPL, DEFER>;
+    else kern = lookback_scan_bulk_kernel<P, THREADS, VECS, STAGES, DPL>;
     const int smem = STAGES * L::STAGE_BYTES;
     static int per_sm_dev[64] = {0};  // per instantiation and device: resident CTAs per SM
     int &per_sm = per_sm_dev[ctx->device & 63];
@@ -741,7 +1051,7 @@ int launch_bulk(cme213_ctx *ctx, const P &p, int64_t n, cudaStream_t st, const c
     WaveScratch ws = wave_scratch_carve(scratch_mem, tiles, waves, sizeof(T));
     static unsigned long long *d_trace = nullptr;
     const bool tracing = getenv("CME213_SCAN_TRACE") != nullptr;
-    const size_t trace_words = (size_t)grid * TRACE_MAX_IT * 8;
+    const size_t trace_words = (size_t)(grid + 1) * TRACE_MAX_IT * 8;
     if (tracing) {
         if (!d_trace) CME213_CUDA(cudaMalloc(&d_trace, (size_t)1024 * TRACE_MAX_IT * 8 * 8));
         CME213_CUDA(cudaMemsetAsync(d_trace, 0, trace_words * 8, st));
@@ -769,6 +1079,15 @@ int launch_bulk(cme213_ctx *ctx, const P &p, int64_t n, cudaStream_t st, const c
         const char *nm[8] = {"", "wait_data", "local+S1", "pub+atomic", "scanner", "poll", "S2+cst", "store"};
         for (int k = 1; k < 8; k++) fprintf(stderr, " %s %.0f(n=%ld)", nm[k], cnt[k] ? sum[k] / cnt[k] : 0.0, cnt[k]);
         fprintf(stderr, "\n");
+        if (const char *path = getenv("CME213_SCAN_TRACE_FILE")) {
+            FILE *f = fopen(path, "wb");
+            if (f) {
+                long hdr[3] = {(long)grid + 1, (long)TRACE_MAX_IT, (long)waves};
+                fwrite(hdr, sizeof(long), 3, f);
+                fwrite(h, 8, trace_words, f);
+                fclose(f);
+            }
+        }
         free(h);
     }
 #endif
@@ -790,8 +1109,10 @@ template <class P> static inline size_t scratch_bytes_for(int64_t n) {
 template <class P>
 int launch_with_scratch(cme213_ctx *ctx, const P &p, int64_t n, bool vec_ok, cudaStream_t st, const char *name,
                         void *scratch_mem, size_t scratch_avail) {
-    if (P::BULK && vec_ok && n >= (int64_t)1 << 20)
-        return launch_bulk<P, Cfg<P>::THREADS, Cfg<P>::VECS, Cfg<P>::STAGES, Cfg<P>::DPL>(ctx, p, n, st, name, scratch_mem, scratch_avail);
+    if constexpr (P::BULK) {
+        if (vec_ok && n >= (int64_t)1 << 20)
+            return launch_bulk<P, Cfg<P>::B_THREADS, Cfg<P>::B_VECS, Cfg<P>::B_STAGES, Cfg<P>::DPL, true, Cfg<P>::B_DEFER>(ctx, p, n, st, name, scratch_mem, scratch_avail);
+    }
     return launch_direct<P, Cfg<P>::DIRECT_THREADS, Cfg<P>::DIRECT_VECS, Cfg<P>::DIRECT_MIN_BLOCKS>(ctx, p, n, vec_ok, st, name, scratch_mem);
 }
 

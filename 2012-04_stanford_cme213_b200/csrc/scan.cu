@@ -35,6 +35,9 @@ struct PlainPolicy {
     static constexpr int IPV = 16 / sizeof(T);
     static constexpr bool SEG = SEG_;
     static constexpr bool BULK = true;
+    static constexpr bool INCLUSIVE_OUT = INCLUSIVE;
+    using V16T = typename V16<T_>::type;
+    __host__ __device__ T *out_ptr() const { return out; }
     static constexpr int NIN = SEG_ ? 2 : 1;   // values, and for segmented scans the head-flag words (1 bit per item)
     __host__ __device__ static constexpr int tile_bytes(int s, int tile_items) { return s == 0 ? tile_items * (int)sizeof(T) : tile_items / 8; }
     const T *in;
@@ -262,6 +265,18 @@ __global__ void flags_from_offsets_kernel(const int32_t *__restrict__ s, int p, 
 template <class P>
 int run(cme213_ctx *ctx, const P &p, int64_t n, bool vec_ok, void *stream, const char *name) {
     DeviceGuard g(ctx->device);
+    if constexpr (P::BULK) {
+        if (const char *cfg = getenv("CME213_SCAN_CFG")) {  // tuning hook: "threads,vecs,-stages,defer" picks a blocked-kernel shape
+            int T_ = 0, V_ = 0, S_ = 0, D_ = 1;
+            sscanf(cfg, "%d,%d,%d,%d", &T_, &V_, &S_, &D_);
+            cudaStream_t st = (cudaStream_t)stream;
+            if (vec_ok && n >= ((int64_t)1 << 20)) {
+#define CME213_TRY_BLOCKED(T, V, S, D) if (T_ == T && V_ == V && S_ == -(S) && D_ == D) return scan::launch_bulk<P, T, V, S, 5, true, D>(ctx, p, n, st, name, nullptr, 0);
+                CME213_TRY_BLOCKED(1024, 3, 4, 2) CME213_TRY_BLOCKED(896, 5, 3, 1) CME213_TRY_BLOCKED(640, 5, 4, 2)
+#undef CME213_TRY_BLOCKED
+            }
+        }
+    }
     return scan::launch<P>(ctx, p, n, vec_ok, (cudaStream_t)stream, name);
 }
 
@@ -294,21 +309,6 @@ CME213_API int cme213_exclusive_scan_u32(cme213_ctx *ctx, const uint32_t *d_in, 
     if (n == 0) return CME213_OK;
     PlainPolicy<uint32_t, false, false> p{d_in, d_out, nullptr};
     const bool ok = aligned16(d_in) && aligned16(d_out);
-    if (const char *cfg = getenv("CME213_SCAN_CFG")) {  // tuning hook: "threads,vecs,stages" (stages 0 = direct kernel)
-        using P = PlainPolicy<uint32_t, false, false>;
-        DeviceGuard g(ctx->device);
-        cudaStream_t st = (cudaStream_t)stream;
-        int T_ = 0, V_ = 0, S_ = 0;
-        sscanf(cfg, "%d,%d,%d", &T_, &V_, &S_);
-#define CME213_TRY_BULK(T, V, S) if (T_ == T && V_ == V && S_ == S) return scan::launch_bulk<P, T, V, S, (T == 1024 ? 5 : 10)>(ctx, p, n, st, "scan", nullptr, 0);
-#define CME213_TRY_DIRECT(T, V) if (T_ == T && V_ == V && S_ == 0) return scan::launch_direct<P, T, V, 1>(ctx, p, n, ok, st, "scan", nullptr);
-        CME213_TRY_DIRECT(256, 4) CME213_TRY_DIRECT(1024, 8)
-        CME213_TRY_BULK(512, 4, 3) CME213_TRY_BULK(512, 2, 4) CME213_TRY_BULK(512, 2, 6)
-        CME213_TRY_BULK(1024, 4, 3) CME213_TRY_BULK(1024, 3, 4) CME213_TRY_BULK(1024, 6, 2) CME213_TRY_BULK(1024, 2, 4) CME213_TRY_BULK(1024, 2, 6)
-        CME213_TRY_BULK(1024, 5, 2) CME213_TRY_BULK(1024, 4, 2) CME213_TRY_BULK(1024, 3, 3) CME213_TRY_BULK(1024, 7, 1) CME213_TRY_BULK(1024, 5, 1) CME213_TRY_BULK(1024, 6, 1)
-#undef CME213_TRY_BULK
-#undef CME213_TRY_DIRECT
-    }
     return run(ctx, p, n, ok, stream, "exclusive_scan_u32");
 }
 
