@@ -11,7 +11,7 @@ LIB_PATH = os.path.join(HERE, "libcme213_b200.so")
 
 OK = 0
 ERR_INVALID, ERR_CUDA, ERR_ALLOC, ERR_UNSUPPORTED = -1, -2, -3, -4
-CSR_AUTO, CSR_SCALAR, CSR_VECTOR, CSR_STREAM = 0, 1, 2, 3
+CSR_AUTO, CSR_SCALAR, CSR_VECTOR, CSR_STREAM, CSR_STREAM_PADDED = 0, 1, 2, 3, 4
 
 
 def csr_vector(lanes):

@@ -14,6 +14,11 @@ struct cme213_ctx {
     void *ws;          // scratch workspace, grown on demand
     size_t ws_bytes;
     int64_t launches;  // kernels launched through this context
+    // CSR AUTO decisions (spmv_csr.cu), remembered per (row_ptr, row range)
+    static constexpr int CSR_CACHE = 16;
+    struct CsrChoice { const int32_t *row_ptr; int64_t row_begin, row_end; bool padded; };
+    CsrChoice csr_cache[CSR_CACHE];
+    unsigned csr_cache_next;
 };
 
 namespace cme213 {

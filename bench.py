@@ -26,6 +26,9 @@ sys.path.insert(0, ROOT)
 PKG = "2012-04_stanford_cme213_b200"
 
 
+NCU_TRAFFIC_C5_BYTES = 15008900000  # 13.96 GB read + 1.05 GB written per csr_stream_kernel<double> launch (profiles/r01_ncu_csr_stream_f64_final.txt)
+
+
 def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
@@ -334,6 +337,15 @@ def build_workload(name, ctx, torch, args, rank=0, world=1, dist=None):
         return make_powerlaw(ctx, torch, args, name)
     if name == "csr_powerlaw":
         return make_powerlaw(ctx, torch, args, "csr")
+    if name in ("ell_window", "hyb_window", "csr_window", "ell_regular_window", "csr_regular_window"):
+        # same row lengths, columns drawn inside a 4,096-wide band around the diagonal (the locality of the FEM
+        # matrices in the final project's benchmark set): the x gathers then hit in L1/L2 and the format kernels show
+        # their streaming rate instead of the random-gather ceiling
+        import copy
+        a2 = copy.copy(args)
+        a2.window = 1 << 12
+        a2.regular = 1 if "regular" in name else 0
+        return make_powerlaw(ctx, torch, a2, name.split("_")[0])
     if name == "pagerank":
         return make_pagerank(ctx, torch, args)
     raise SystemExit("unknown workload " + name)
@@ -586,7 +598,11 @@ def main():
     else:
         kms = ms_step
         ach = value
-    roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+    # dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel, from the committed
+    # `ncu --set full` capture of this same command (profiles/r01_ncu_csr_stream_f64_*.txt); only valid for the
+    # default single-GPU C5 workload
+    traffic = NCU_TRAFFIC_C5_BYTES if (args.workload == "c5" and world == 1 and args.grid == 512) else None
+    roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic,
             "kernel": wl["kernel"], "kernel_ms": kms, "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)" if peak_kind == "measured" else "fallback 6650 GB/s",
             "frac_of_8TBs_spec": ach / 8000.0, "gflops": wl["flops"] / max(world, 1) / (kms * 1e-3) / 1e9 if args.workload == "c5" else wl["flops"] / (kms * 1e-3) / 1e9}
 
@@ -608,7 +624,8 @@ def main():
         others = []
         del wl
         torch.cuda.empty_cache()
-        names = ["scan", "segscan", "fp", "transpose32", "transpose64", "c1", "ell", "hyb", "csr_powerlaw", "pagerank"]
+        names = ["scan", "segscan", "fp", "transpose32", "transpose64", "c1", "ell", "hyb", "csr_powerlaw",
+                 "ell_window", "hyb_window", "csr_window", "ell_regular_window", "csr_regular_window", "pagerank"]
         for name in names:
             try:
                 w = build_workload(name, ctx, torch, args)

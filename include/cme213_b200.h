@@ -43,6 +43,8 @@ extern "C" {
 #define CME213_CSR_SCALAR 1 /* one thread per row, sequential sum: bit-identical to the CPU loop */
 #define CME213_CSR_VECTOR 2 /* 2..32 lanes per row, warp-shuffle reduction */
 #define CME213_CSR_STREAM 3 /* block streams its nonzeros through shared memory, then one thread per row sums sequentially: bit-identical to the CPU loop */
+#define CME213_CSR_STREAM_PADDED 4 /* same, shared-memory products padded against bank conflicts: for matrices whose rows all have 8, 16, 32 ... entries.
+                                      AUTO picks between 3 and 4 from the mean row length (one small device read per new matrix). */
 
 typedef struct cme213_ctx cme213_ctx;
 

@@ -47,8 +47,24 @@ def test_csr_kernels_on_random_matrices(ctx, dtype, rows, cols, mean):
     want = oracle.csr_spmv(ptr, col, val, x)
     assert np.array_equal(gpu_csr(ctx, ptr, col, val, x, SCALAR), want)
     assert np.array_equal(gpu_csr(ctx, ptr, col, val, x, STREAM), want)
+    assert np.array_equal(gpu_csr(ctx, ptr, col, val, x, 4), want)   # CME213_CSR_STREAM_PADDED
+    assert np.array_equal(gpu_csr(ctx, ptr, col, val, x, AUTO), want)
     for lanes in (2, 4, 8, 16, 32):
         check_tol(gpu_csr(ctx, ptr, col, val, x, VECTOR | (lanes << 8)), ptr, col, val, x)
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_csr_regular_rows_take_the_padded_variant(ctx, dtype):
+    # every row has 16 entries: AUTO's inspector picks the padded stream kernel; results stay bit-exact
+    rows, cols = 5000, 7000
+    rng = np.random.default_rng(11)
+    ptr = (np.arange(rows + 1) * 16).astype(np.int32)
+    col = np.concatenate([np.sort(rng.choice(cols, 16, replace=False)) for _ in range(rows)]).astype(np.int32)
+    val = rng.uniform(-1, 1, rows * 16).astype(dtype)
+    x = rng.uniform(-1, 1, cols).astype(dtype)
+    want = oracle.csr_spmv(ptr, col, val, x)
+    for kernel in (AUTO, STREAM, 4):
+        assert np.array_equal(gpu_csr(ctx, ptr, col, val, x, kernel), want)
 
 
 def test_csr_stream_rows_longer_than_a_tile(ctx):
