@@ -135,7 +135,7 @@ def make_c5(ctx, torch, args, rank, world, dist):
                 launches_per_step=1 if it.mode not in ("halo", "p2p") else 2,
                 meta={"workload": "C5: CSR SpMV iteration, 3-D 7-point Laplacian %d^3, fp64, row-sharded over %d GPU(s)" % (g, world),
                       "rows": rows, "nnz": nnz_total, "exchange": it.mode, "comm_bytes_per_rank_per_step": it.comm_bytes_per_step,
-                      "launch": "CUDA graph of two passes (kernels + NCCL all-gather)" if replay is not None else "eager",
+                      "launch": ("CUDA graph of two passes (kernels + NCCL %s)" % ("send/recv" if it.mode == "p2p" else "all-gather")) if replay is not None else "eager",
                       "cta_order": ("z fastest inside strips of %d grid lines" % args.order_strip) if args.order_strip > 0 else "row order",
                       "l2": "working set %.1f GB per pass >> 126 MB L2" % (alg / 1e9)},
                 keep=(d_ptr, d_col, d_val, xa, xb, it), iterate=it, shard=(lo, hi, d_ptr, d_col, d_val, nnz.value), ctx=ctx)
