@@ -20,6 +20,7 @@
 // code is built without FMA (x86-64 baseline), and its 10-ULP check (pagerank.cu:216-239) then
 // holds with zero slack.
 #include "internal.cuh"
+#include <stdlib.h>
 
 namespace {
 using namespace cme213;
@@ -118,19 +119,18 @@ template <> struct V4<double> {
     }
 };
 
+// The plain fast path: rows in index order.  Deliberately minimal -- it compiles to 32 registers
+// (8 CTAs of 256 threads per SM); the feature-complete kernel below (block lists, padded products) needs 38-40
+// and measured 5-30 % slower on the same inputs, so it only runs when one of its features is asked for.
 template <typename T, int MODE, int THREADS, int TILE, bool PADDED>
 __global__ void __launch_bounds__(THREADS)
-csr_stream_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
+csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
     static_assert(TILE % (4 * THREADS) == 0, "tile must be a whole number of 4-wide vectors per thread");
-    // PADDED: one pad element per 128 bytes.  When every row has 8, 16, 32 ... entries the per-row sums walk shared
-    // memory with a power-of-two stride (16-way bank conflicts: 0.43 of peak on a 16-per-row matrix, 0.77 padded);
-    // for odd row lengths (the stencils) the padding only costs instructions (0.81 -> 0.72), so it is a variant.
-    constexpr int PAD = 128 / (int)sizeof(T);
+    constexpr int PAD = 128 / (int)sizeof(T);   // PADDED: one pad element per 128 bytes (see the kernel below)
     auto pidx = [](int j) { return PADDED ? j + j / PAD : j; };
     __shared__ __align__(16) T prod[PADDED ? TILE + TILE / PAD : TILE];
     const int tid = threadIdx.x;
-    const int64_t blk = a.order ? (int64_t)__ldg(a.order + blockIdx.x) : (int64_t)blockIdx.x;
-    const int64_t r0 = row_begin + blk * THREADS;
+    const int64_t r0 = row_begin + (int64_t)blockIdx.x * THREADS;
     const int64_t r = r0 + tid;
     const int64_t rl = r0 + THREADS < row_end ? r0 + THREADS : row_end;
     int rs = 0, re = 0;
@@ -139,7 +139,6 @@ csr_stream_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
         re = a.row_ptr[r + 1];
     }
     const int b0 = __ldg(a.row_ptr + r0), b1 = __ldg(a.row_ptr + rl);  // this CTA's nonzero range
-    const uint64_t keep = l2_policy_evict_last();
     T sum = T(0);
     for (int base = b0 & ~3; base < b1; base += TILE) {
 #pragma unroll
@@ -151,11 +150,11 @@ csr_stream_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
                 V4<T> w;
                 if (MODE == MODE_CSR) w = V4<T>::load(a.val + j);
                 else w = V4<T>{{T(0), T(0), T(0), T(0)}};
-                T p0 = product_keep<T, MODE>(a, w.v[0], c.x, keep);
-                T p1 = product_keep<T, MODE>(a, w.v[1], c.y, keep);
-                T p2 = product_keep<T, MODE>(a, w.v[2], c.z, keep);
-                T p3 = product_keep<T, MODE>(a, w.v[3], c.w, keep);
-                const int po = pidx(o);  // o is a multiple of 4 and PAD a multiple of 4: the four slots are contiguous
+                T p0 = product<T, MODE>(a, w.v[0], c.x);
+                T p1 = product<T, MODE>(a, w.v[1], c.y);
+                T p2 = product<T, MODE>(a, w.v[2], c.z);
+                T p3 = product<T, MODE>(a, w.v[3], c.w);
+                const int po = pidx(o);
                 prod[po + 0] = p0; prod[po + 1] = p1; prod[po + 2] = p2; prod[po + 3] = p3;
             } else {
 #pragma unroll
@@ -173,6 +172,81 @@ csr_stream_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
         __syncthreads();
     }
     if (r < row_end) epilogue<T, MODE>(a, r, sum);
+}
+
+template <typename T, int MODE, int THREADS, int RPT, int TILE, bool PADDED, bool ORDERED = true, bool KEEP = true>
+__global__ void __launch_bounds__(THREADS)
+csr_stream_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
+    static_assert(TILE % (4 * THREADS) == 0, "tile must be a whole number of 4-wide vectors per thread");
+    // A CTA owns THREADS*RPT consecutive rows (thread t: rows t, t+THREADS, ...), i.e. one contiguous nonzero range.
+    // PADDED: one pad element per 128 bytes.  When every row has 8, 16, 32 ... entries the per-row sums walk shared
+    // memory with a power-of-two stride (16-way bank conflicts: 0.43 of peak on a 16-per-row matrix, 0.77 padded);
+    // for odd row lengths (the stencils) the padding only costs instructions (0.81 -> 0.72), so it is a variant.
+    constexpr int PAD = 128 / (int)sizeof(T);
+    constexpr int ROWS = THREADS * RPT;
+    auto pidx = [](int j) { return PADDED ? j + j / PAD : j; };
+    __shared__ __align__(16) T prod[PADDED ? TILE + TILE / PAD : TILE];
+    const int tid = threadIdx.x;
+    const int64_t blk = (ORDERED && a.order) ? (int64_t)__ldg(a.order + blockIdx.x) : (int64_t)blockIdx.x;
+    const int64_t r0 = row_begin + blk * ROWS;
+    const int64_t rl = r0 + ROWS < row_end ? r0 + ROWS : row_end;
+    int rs[RPT], re[RPT];
+    T sum[RPT];
+#pragma unroll
+    for (int k = 0; k < RPT; k++) {
+        const int64_t r = r0 + k * THREADS + tid;
+        rs[k] = re[k] = 0;
+        sum[k] = T(0);
+        if (r < row_end) {
+            rs[k] = a.row_ptr[r];
+            re[k] = a.row_ptr[r + 1];
+        }
+    }
+    const int b0 = __ldg(a.row_ptr + r0), b1 = __ldg(a.row_ptr + rl);  // this CTA's nonzero range
+    const uint64_t keep = KEEP ? l2_policy_evict_last() : 0;
+    for (int base = b0 & ~3; base < b1; base += TILE) {
+#pragma unroll
+        for (int v = 0; v < TILE / (4 * THREADS); v++) {
+            const int o = (v * THREADS + tid) * 4;
+            const int j = base + o;
+            if (j + 4 <= b1) {
+                const int4 c = ld_stream(reinterpret_cast<const int4 *>(a.col + j));
+                V4<T> w;
+                if (MODE == MODE_CSR) w = V4<T>::load(a.val + j);
+                else w = V4<T>{{T(0), T(0), T(0), T(0)}};
+                T p0, p1, p2, p3;
+                if (KEEP) {
+                    p0 = product_keep<T, MODE>(a, w.v[0], c.x, keep); p1 = product_keep<T, MODE>(a, w.v[1], c.y, keep);
+                    p2 = product_keep<T, MODE>(a, w.v[2], c.z, keep); p3 = product_keep<T, MODE>(a, w.v[3], c.w, keep);
+                } else {
+                    p0 = product<T, MODE>(a, w.v[0], c.x); p1 = product<T, MODE>(a, w.v[1], c.y);
+                    p2 = product<T, MODE>(a, w.v[2], c.z); p3 = product<T, MODE>(a, w.v[3], c.w);
+                }
+                const int po = pidx(o);  // o is a multiple of 4 and PAD a multiple of 4: the four slots are contiguous
+                prod[po + 0] = p0; prod[po + 1] = p1; prod[po + 2] = p2; prod[po + 3] = p3;
+            } else {
+#pragma unroll
+                for (int t = 0; t < 4; t++)
+                    if (j + t < b1) {
+                        const T vv = MODE == MODE_CSR ? a.val[j + t] : T(0);
+                        prod[pidx(o + t)] = product<T, MODE>(a, vv, a.col[j + t]);
+                    }
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < RPT; k++) {
+            const int lo = rs[k] > base ? rs[k] : base;
+            const int hi = re[k] < base + TILE ? re[k] : base + TILE;
+            for (int j = lo; j < hi; j++) sum[k] = add_rn(sum[k], prod[pidx(j - base)]);
+        }
+        if (base + TILE < b1) __syncthreads();  // only when another pass will overwrite the products
+    }
+#pragma unroll
+    for (int k = 0; k < RPT; k++) {
+        const int64_t r = r0 + k * THREADS + tid;
+        if (r < row_end) epilogue<T, MODE>(a, r, sum[k]);
+    }
 }
 
 // AUTO: rows whose common length is a multiple of 8 make the per-row sums of the stream kernel collide on shared
@@ -235,11 +309,21 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
             CME213_LAUNCHED(ctx, "csr_vector_kernel");
         }
     } else if (kind == CME213_CSR_STREAM) {
-        constexpr int THREADS = 256, TILE = 2048;
-        const int64_t blocks = num_blocks >= 0 ? num_blocks : div_up(rows, THREADS);
-        if (blocks == 0) return CME213_OK;
-        if (padded) csr_stream_kernel<T, MODE, THREADS, TILE, true><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end);
-        else csr_stream_kernel<T, MODE, THREADS, TILE, false><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end);
+        // Launch shape (sweep in profiles/r01_notes.md): fp64 rows are twice as heavy per nonzero, 128-row CTAs keep
+        // more CTAs per SM in their load phase (C5: 0.82 of peak vs 0.78 with 256); fp32 keeps 256-row CTAs.  Launches
+        // with a block list use 256-row blocks for every type (cme213_spmv_csr_block_rows()).
+        constexpr int ORD_THREADS = 256, ORD_TILE = 2048;
+        constexpr int THREADS = sizeof(T) == 8 ? 128 : 256, TILE = THREADS * 8;
+        if (a.order) {
+            const int64_t blocks = num_blocks >= 0 ? num_blocks : div_up(rows, ORD_THREADS);
+            if (blocks == 0) return CME213_OK;
+            if (padded) csr_stream_kernel<T, MODE, ORD_THREADS, 1, ORD_TILE, true, true><<<(unsigned)blocks, ORD_THREADS, 0, st>>>(a, row_begin, row_end);
+            else csr_stream_kernel<T, MODE, ORD_THREADS, 1, ORD_TILE, false, true><<<(unsigned)blocks, ORD_THREADS, 0, st>>>(a, row_begin, row_end);
+        } else {
+            const int64_t blocks = div_up(rows, THREADS);
+            if (padded) csr_stream_lean_kernel<T, MODE, THREADS, TILE, true><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end);
+            else csr_stream_lean_kernel<T, MODE, THREADS, TILE, false><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end);
+        }
         CME213_LAUNCHED(ctx, "csr_stream_kernel");
     } else {
         set_error("unknown CSR kernel %d", kernel);
