@@ -26,7 +26,7 @@ sys.path.insert(0, ROOT)
 PKG = "2012-04_stanford_cme213_b200"
 
 
-NCU_TRAFFIC_C5_BYTES = 15008900000  # 13.96 GB read + 1.05 GB written per csr_stream_kernel<double> launch (profiles/r01_ncu_csr_stream_f64_final.txt)
+NCU_TRAFFIC_C5_BYTES = 15193800000  # 14.14 GB read + 1.05 GB written per csr_stream_lean_kernel<double> launch (profiles/r01_ncu_csr_stream_lean_f64_final.txt)
 
 
 def log(*a):
