@@ -61,11 +61,14 @@ PROTOTYPES = {
     "cme213_spmv_coo_accumulate_f32": (_i, [_p, _i64, _p, _p, _p, _p, _p, _p]),
     "cme213_spmv_coo_accumulate_f64": (_i, [_p, _i64, _p, _p, _p, _p, _p, _p]),
     "cme213_spmv_hyb_f32": (_i, [_p, _i64, _i64, _i, _p, _p, _i64, _p, _p, _p, _p, _p, _p]),
+    "cme213_spmv_hyb_f64": (_i, [_p, _i64, _i64, _i, _p, _p, _i64, _p, _p, _p, _p, _p, _p]),
     "cme213_hyb_pick_k": (_i, [_p, _i64, _p, _pi, _pi, _p]),
     "cme213_ell_pitch": (_i64, [_i64]),
     "cme213_csr_to_ell_f32": (_i, [_p, _i64, _i64, _p, _p, _p, _i, _i64, _p, _p, _p]),
     "cme213_csr_to_ell_f64": (_i, [_p, _i64, _i64, _p, _p, _p, _i, _i64, _p, _p, _p]),
     "cme213_csr_to_coo_tail_f32": (_i, [_p, _i64, _p, _p, _p, _i, _pi64, _p, _p, _p, _p]),
+    "cme213_csr_to_coo_tail_f64": (_i, [_p, _i64, _p, _p, _p, _i, _pi64, _p, _p, _p, _p]),
+    "cme213_block_offsets_u32": (_i, [_p, _p, _p, _p, _i64, _i64, _p]),
     "cme213_gen_laplace2d_f32": (_i, [_p, _i, _i, _p, _p, _p, _pi64, _p]),
     "cme213_gen_laplace3d_f64": (_i, [_p, _i, _i, _i, _i64, _i64, _p, _p, _p, _pi64, _p]),
     "cme213_gen_powerlaw_lengths": (_i, [_p, _i64, _i, _u32, _u32, _i, _u32, _p, _pi64, _p]),

@@ -88,6 +88,18 @@ __global__ void tail_fill_kernel(int64_t num_rows, const int32_t *__restrict__ r
     }
 }
 
+__global__ void row_head_flags_kernel(int64_t num_rows, int64_t row_len, uint32_t *bits) {
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < num_rows) {
+        const int64_t pos = r * row_len;
+        atomicOr(bits + (pos >> 5), 1u << (unsigned)(pos & 31));
+    }
+}
+__global__ void add_row_vector_kernel(uint32_t *m, const uint32_t *__restrict__ v, int64_t total, int64_t cols) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x)
+        m[i] += __ldg(v + i % cols);
+}
+
 template <typename T>
 int csr_to_ell_impl(cme213_ctx *ctx, int64_t num_rows, int64_t num_cols, const int32_t *d_row_ptr,
                     const int32_t *d_col, const T *d_val, int K, int64_t pitch, int32_t *d_ell_idx, T *d_ell_val,
@@ -180,9 +192,10 @@ CME213_API int cme213_csr_to_ell_f64(cme213_ctx *ctx, int64_t num_rows, int64_t 
     return csr_to_ell_impl<double>(ctx, num_rows, num_cols, d_row_ptr, d_col, d_val, K, pitch, d_ell_idx, d_ell_val, stream);
 }
 
-CME213_API int cme213_csr_to_coo_tail_f32(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr,
-                                          const int32_t *d_col, const float *d_val, int K, int64_t *tail_nnz_out,
-                                          int32_t *d_coo_row, int32_t *d_coo_col, float *d_coo_val, void *stream) {
+template <typename T>
+static int csr_to_coo_tail_impl(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr,
+                                const int32_t *d_col, const T *d_val, int K, int64_t *tail_nnz_out,
+                                int32_t *d_coo_row, int32_t *d_coo_col, T *d_coo_val, void *stream) {
     CME213_CHECK_CTX(ctx);
     if (num_rows < 0 || K < 0 || (num_rows > 0 && !d_row_ptr)) { set_error("csr_to_coo_tail: bad arguments"); return CME213_ERR_INVALID; }
     if (tail_nnz_out) *tail_nnz_out = 0;
@@ -208,9 +221,56 @@ CME213_API int cme213_csr_to_coo_tail_f32(cme213_ctx *ctx, int64_t num_rows, con
     }
     if (fill) {
         if (!d_col || !d_val) { set_error("csr_to_coo_tail: null pointer"); return CME213_ERR_INVALID; }
-        tail_fill_kernel<float><<<(unsigned)div_up(num_rows * 32, 256), 256, 0, st>>>(num_rows, d_row_ptr, d_col, d_val, K, d_count,
+        tail_fill_kernel<T><<<(unsigned)div_up(num_rows * 32, 256), 256, 0, st>>>(num_rows, d_row_ptr, d_col, d_val, K, d_count,
                                                                                      d_coo_row, d_coo_col, d_coo_val);
         CME213_LAUNCHED(ctx, "tail_fill_kernel");
     }
+    return CME213_OK;
+}
+
+CME213_API int cme213_csr_to_coo_tail_f32(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr,
+                                          const int32_t *d_col, const float *d_val, int K, int64_t *tail_nnz_out,
+                                          int32_t *d_coo_row, int32_t *d_coo_col, float *d_coo_val, void *stream) {
+    return csr_to_coo_tail_impl<float>(ctx, num_rows, d_row_ptr, d_col, d_val, K, tail_nnz_out, d_coo_row, d_coo_col, d_coo_val, stream);
+}
+CME213_API int cme213_csr_to_coo_tail_f64(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr,
+                                          const int32_t *d_col, const double *d_val, int K, int64_t *tail_nnz_out,
+                                          int32_t *d_coo_row, int32_t *d_coo_col, double *d_coo_val, void *stream) {
+    return csr_to_coo_tail_impl<double>(ctx, num_rows, d_row_ptr, d_col, d_val, K, tail_nnz_out, d_coo_row, d_coo_col, d_coo_val, stream);
+}
+
+// Scatter offsets of a blocked LSD radix pass: for every bucket an exclusive scan down the blocks, started at
+// the bucket's global offset.  Built from the two primitives exactly as the reference's loop nest suggests:
+// transpose [blocks x buckets] -> [buckets x blocks], ONE segmented exclusive scan whose segments are the rows,
+// transpose back, add the global offsets.   reference: hw/hw4/programming/radixsort.cpp:85-97.
+CME213_API int cme213_block_offsets_u32(cme213_ctx *ctx, const uint32_t *d_local_hist, const uint32_t *d_global_excl,
+                                        uint32_t *d_out, int64_t num_blocks, int64_t num_buckets, void *stream) {
+    CME213_CHECK_CTX(ctx);
+    if (num_blocks < 0 || num_buckets < 0) { set_error("block_offsets_u32: negative size"); return CME213_ERR_INVALID; }
+    const int64_t total = num_blocks * num_buckets;
+    if (total == 0) return CME213_OK;
+    if (!d_local_hist || !d_global_excl || !d_out || d_local_hist == d_out) { set_error("block_offsets_u32: bad pointers"); return CME213_ERR_INVALID; }
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t t_bytes = ((size_t)total * 4 + 255) & ~(size_t)255;
+    const size_t f_bytes = ((size_t)cme213_flag_words(total) * 4 + 255) & ~(size_t)255;
+    void *ws = nullptr;
+    int rc = workspace(ctx, t_bytes + f_bytes + cme213_internal_segscan_u32_scratch_bytes(total), &ws);
+    if (rc) return rc;
+    uint32_t *d_t = (uint32_t *)ws;
+    uint32_t *d_flags = (uint32_t *)((char *)ws + t_bytes);
+    void *scratch = (char *)ws + t_bytes + f_bytes;
+    rc = cme213_transpose_b32(ctx, d_local_hist, d_t, num_blocks, num_buckets, num_buckets, num_blocks, stream);
+    if (rc) return rc;
+    CME213_CUDA(cudaMemsetAsync(d_flags, 0, f_bytes, st));
+    row_head_flags_kernel<<<(unsigned)div_up(num_buckets, 256), 256, 0, st>>>(num_buckets, num_blocks, d_flags);
+    CME213_LAUNCHED(ctx, "row_head_flags_kernel");
+    rc = cme213_internal_segscan_exclusive_u32(ctx, d_t, d_flags, d_t, total, scratch, stream);
+    if (rc) return rc;
+    rc = cme213_transpose_b32(ctx, d_t, d_out, num_buckets, num_blocks, num_blocks, num_buckets, stream);
+    if (rc) return rc;
+    const int64_t want = div_up(total, 256), cap = (int64_t)ctx->sm_count * 16;
+    add_row_vector_kernel<<<(unsigned)(want < cap ? want : cap), 256, 0, st>>>(d_out, d_global_excl, total, num_buckets);
+    CME213_LAUNCHED(ctx, "add_row_vector_kernel");
     return CME213_OK;
 }

@@ -7,6 +7,9 @@
 size_t cme213_internal_scan_u32_scratch_bytes(int64_t n);
 int cme213_internal_exclusive_scan_u32(cme213_ctx *ctx, const uint32_t *d_in, uint32_t *d_out, int64_t n,
                                        void *scratch, void *stream);
+size_t cme213_internal_segscan_u32_scratch_bytes(int64_t n);
+int cme213_internal_segscan_exclusive_u32(cme213_ctx *ctx, const uint32_t *d_in, const uint32_t *d_flag_bits,
+                                          uint32_t *d_out, int64_t n, void *scratch, void *stream);
 // spmv_csr.cu
 int cme213_internal_pagerank_propagate_w(cme213_ctx *ctx, const uint32_t *d_graph_indices,
                                          const uint32_t *d_graph_edges, const float *d_nodes_in, const float *d_w_in,

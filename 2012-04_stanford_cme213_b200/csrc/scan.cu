@@ -447,3 +447,17 @@ CME213_API int cme213_exclusive_scan_u32_static(const uint32_t *d_in, uint32_t *
     if (e != cudaSuccess) return cuda_fail(e, "exclusive_scan_u32_static");
     return CME213_OK;
 }
+
+// ---- internal: exclusive segmented uint32 scan with caller-provided scratch (convert.cu: radix block offsets) ----
+size_t cme213_internal_segscan_u32_scratch_bytes(int64_t n) {
+    return scan::scratch_bytes_for<PlainPolicy<uint32_t, true, false>>(n);
+}
+int cme213_internal_segscan_exclusive_u32(cme213_ctx *ctx, const uint32_t *d_in, const uint32_t *d_flag_bits,
+                                          uint32_t *d_out, int64_t n, void *scratch, void *stream) {
+    if (n <= 0) return CME213_OK;
+    DeviceGuard g(ctx->device);
+    PlainPolicy<uint32_t, true, false> p{d_in, d_out, d_flag_bits};
+    return scan::launch_with_scratch(ctx, p, n, aligned16(d_in) && aligned16(d_out) && aligned16(d_flag_bits),
+                                     (cudaStream_t)stream, "segscan_exclusive_u32", scratch,
+                                     cme213_internal_segscan_u32_scratch_bytes(n));
+}

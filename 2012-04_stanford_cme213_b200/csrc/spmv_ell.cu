@@ -127,3 +127,12 @@ CME213_API int cme213_spmv_hyb_f32(cme213_ctx *ctx, int64_t num_rows, int64_t pi
     if (rc) return rc;
     return cme213_spmv_coo_accumulate_f32(ctx, coo_nnz, d_coo_row, d_coo_col, d_coo_val, d_x, d_y, stream);
 }
+
+CME213_API int cme213_spmv_hyb_f64(cme213_ctx *ctx, int64_t num_rows, int64_t pitch, int K, const int32_t *d_ell_idx,
+                                   const double *d_ell_val, int64_t coo_nnz, const int32_t *d_coo_row,
+                                   const int32_t *d_coo_col, const double *d_coo_val, const double *d_x, double *d_y,
+                                   void *stream) {
+    int rc = cme213_spmv_ell_f64(ctx, num_rows, pitch, K, d_ell_idx, d_ell_val, d_x, d_y, stream);
+    if (rc) return rc;
+    return cme213_spmv_coo_accumulate_f64(ctx, coo_nnz, d_coo_row, d_coo_col, d_coo_val, d_x, d_y, stream);
+}

@@ -425,6 +425,8 @@ def run_reference(args):
     import oracle
     from oracle import generators as g
     oracle.build()
+    if args.workload == "pagerank":
+        return run_reference_pagerank(args, np, oracle, g)
     grid = args.grid
     planes = 32 if grid >= 32 else grid
     rows = planes * grid * grid
@@ -446,6 +448,32 @@ def run_reference(args):
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": "C5: CSR SpMV iteration, 3-D 7-point Laplacian %d^3, fp64 (CPU, bounded sample)" % grid},
         "cpu_baseline": {"value": v, "unit": "GB/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}), flush=True)
+
+
+def run_reference_pagerank(args, np, oracle, g):
+    """--impl reference --workload pagerank: the reference's OWN host_graph_propagate (pagerank.cu:45-56, compiled
+    from the checkout into oracle/_ref) on the homework's problem (N = 2^21, avg_edges = 8); serial, as shipped.
+    Falls back to the oracle restatement (kind "port") when oracle/_ref was not built."""
+    n, avg = 1 << 21, 8
+    ind, edges, inv, nodes = g.pagerank_graph(n, avg, seed=21)
+    alg = len(edges) * 4 + (n + 1) * 4 + n * 12
+    have_ref = oracle.ref_lib("pagerank") is not None
+    run = (lambda it: oracle.ref_pagerank_iterate(ind, edges, nodes, inv, it)) if have_ref else \
+          (lambda it: oracle.pagerank_iterate(ind, edges, nodes, inv, it))
+    run(2 * max(args.warmup // 2, 1))
+    iters = 2 * max(args.steps // 2, 1)           # a step = one propagate; the reference iterates in pairs
+    t0 = time.perf_counter()
+    run(iters)
+    el = time.perf_counter() - t0
+    v = alg * iters / el / 1e9
+    print(json.dumps({
+        "impl": "reference", "metric": "spmv_algorithmic_gbs", "value": v, "unit": "GB/s", "n_gpus": args.gpus, "steps": iters,
+        "warmup": args.warmup, "ms_per_step": el / iters * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "C1': PageRank propagate (hw1), N=2^21, avg_edges=8 (CPU)"},
+        "cpu_baseline": {"value": v, "unit": "GB/s", "cores": 1, "kind": "reference" if have_ref else "port",
+                         "sample": "host_graph_propagate of pagerank.cu:45-56, whole graph, %d propagates, 1 thread" % iters},
         "e2e": {"value": v, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}), flush=True)
 
 

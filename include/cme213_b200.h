@@ -176,6 +176,9 @@ int cme213_spmv_coo_accumulate_f64(cme213_ctx *ctx, int64_t nnz, const int32_t *
 int cme213_spmv_hyb_f32(cme213_ctx *ctx, int64_t num_rows, int64_t pitch, int K, const int32_t *d_ell_idx,
                         const float *d_ell_val, int64_t coo_nnz, const int32_t *d_coo_row,
                         const int32_t *d_coo_col, const float *d_coo_val, const float *d_x, float *d_y, void *stream);
+int cme213_spmv_hyb_f64(cme213_ctx *ctx, int64_t num_rows, int64_t pitch, int K, const int32_t *d_ell_idx,
+                        const double *d_ell_val, int64_t coo_nnz, const int32_t *d_coo_row,
+                        const int32_t *d_coo_col, const double *d_coo_val, const double *d_x, double *d_y, void *stream);
 
 /* ---- format conversion on the device ----------------------------------- */
 /* HYB split width: largest K such that at least max(4096, num_rows/3) rows have >= K entries.
@@ -197,6 +200,15 @@ int cme213_csr_to_ell_f64(cme213_ctx *ctx, int64_t num_rows, int64_t num_cols, c
 int cme213_csr_to_coo_tail_f32(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr, const int32_t *d_col,
                                const float *d_val, int K, int64_t *tail_nnz_out, int32_t *d_coo_row,
                                int32_t *d_coo_col, float *d_coo_val, void *stream);
+int cme213_csr_to_coo_tail_f64(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr, const int32_t *d_col,
+                               const double *d_val, int K, int64_t *tail_nnz_out, int32_t *d_coo_row,
+                               int32_t *d_coo_col, double *d_coo_val, void *stream);
+
+/* Scatter offsets of a blocked LSD radix pass: out[i][j] = global_excl[j] + sum of local[i'][j] over blocks i' < i
+ * (arrays [num_blocks x num_buckets], row-major).  Transpose + one segmented exclusive scan + transpose.
+ * reference: hw/hw4/programming/radixsort.cpp:85-97 (local_histogram_final). */
+int cme213_block_offsets_u32(cme213_ctx *ctx, const uint32_t *d_local_hist, const uint32_t *d_global_excl,
+                             uint32_t *d_out, int64_t num_blocks, int64_t num_buckets, void *stream);
 
 /* ---- input generators (device side, deterministic) ---------------------- */
 /* The homework drivers generate their inputs in main(); the large configurations cannot be

@@ -298,6 +298,17 @@ ORACLE_API void oracle_exclusive_scan_u32_omp(const uint32_t *in, uint32_t *out,
     free(tot);
 }
 
+/* Per-block scatter offsets of the parallel radix pass, hw/hw4/programming/radixsort.cpp:85-97:
+ *   final[0][j] = global_exclusive[j];  final[i][j] = final[i-1][j] + local[i-1][j]
+ * i.e. for every bucket j an exclusive scan down the blocks, started at the bucket's global offset. */
+ORACLE_API void oracle_block_offsets_u32(const uint32_t *local, const uint32_t *global_excl, uint32_t *final,
+                                         int64_t num_blocks, int64_t num_buckets) {
+    for (int64_t j = 0; j < num_buckets; ++j) final[j] = global_excl[j];
+    for (int64_t i = 1; i < num_blocks; ++i)
+        for (int64_t j = 0; j < num_buckets; ++j)
+            final[i * num_buckets + j] = final[(i - 1) * num_buckets + j] + local[(i - 1) * num_buckets + j];
+}
+
 /* One LSD radix pass built on the scan (radixsort.cpp:123-153,
  * radixSortSerialPass): histogram, exclusive scan, stable scatter. */
 ORACLE_API void oracle_radix_pass_u32(const uint32_t *keys, uint32_t *out, int64_t n, uint32_t start_bit, uint32_t num_bits) {

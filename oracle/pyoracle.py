@@ -198,6 +198,15 @@ def exclusive_scan_u32(x, omp=False):
     return out
 
 
+def block_offsets_u32(local, global_excl):
+    local = _c(local, np.uint32)
+    blocks, buckets = local.shape
+    global_excl = _c(global_excl, np.uint32)
+    out = np.empty_like(local)
+    lib().oracle_block_offsets_u32(_p(local), _p(global_excl), _p(out), C.c_int64(blocks), C.c_int64(buckets))
+    return out
+
+
 def radix_pass_u32(keys, start_bit, num_bits):
     keys = _c(keys, np.uint32)
     out = np.empty_like(keys)

@@ -143,3 +143,26 @@ def test_coo_segmented_reduction_bulk_path(ctx, dtype):
     want = y0.astype(np.float64) + np.bincount(r, v.astype(np.float64) * x[c], rows)
     assert np.array_equal(host(d_y).astype(np.float64), want)
     assert np.array_equal(host(d_y), oracle.coo_spmv_accumulate(r, c, v, x, y0))
+
+
+def test_hyb_f64_matches_csr_oracle(ctx, cme):
+    rows = 6000
+    ptr, col, val = g.random_csr(rows, rows, 7.0, seed=9, dtype=np.float64)
+    x = np.random.default_rng(10).uniform(-1, 1, rows)
+    K = 6
+    pitch = int(cme.load().cme213_ell_pitch(rows))
+    d_ptr, d_col, d_val = dev(ptr), dev(col), dev(val)
+    d_eidx, d_eval = dev_empty(K * pitch, np.int32), dev_empty(K * pitch, np.float64)
+    ctx.call("cme213_csr_to_ell_f64", rows, rows, d_ptr, d_col, d_val, K, pitch, d_eidx, d_eval)
+    tail = C.c_int64()
+    ctx.call("cme213_csr_to_coo_tail_f64", rows, d_ptr, d_col, d_val, K, C.byref(tail), None, None, None)
+    tr, tc, tv = oracle.csr_to_coo_tail(ptr, col, val, K)
+    assert tail.value == len(tr) > 0
+    d_tr, d_tc, d_tv = dev_empty(tail.value, np.int32), dev_empty(tail.value, np.int32), dev_empty(tail.value, np.float64)
+    ctx.call("cme213_csr_to_coo_tail_f64", rows, d_ptr, d_col, d_val, K, None, d_tr, d_tc, d_tv)
+    assert np.array_equal(host(d_tr), tr) and np.array_equal(host(d_tc), tc) and np.array_equal(host(d_tv), tv)
+    d_y = dev_empty(rows, np.float64)
+    ctx.call("cme213_spmv_hyb_f64", rows, pitch, K, d_eidx, d_eval, tail.value, d_tr, d_tc, d_tv, dev(x), d_y)
+    want = oracle.csr_spmv(ptr, col, val, x)
+    bound = oracle.csr_abs_bound(ptr, col, val, x)
+    assert np.all(np.abs(host(d_y) - want) <= 2 * (np.diff(ptr) + 2) * 2.0 ** -53 * bound + 1e-300)

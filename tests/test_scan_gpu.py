@@ -248,3 +248,43 @@ def test_bulk_path_exclusive_scan_in_place_and_sizes(ctx):
     for n in BIG + [(1 << 20) + 1, (1 << 22) - 3]:
         x = np.random.default_rng(n).integers(0, 2**32, n, dtype=np.uint64).astype(np.uint32)
         assert np.array_equal(gpu_exclusive_scan(ctx, x, in_place=True), oracle.exclusive_scan_u32(x))
+
+
+@pytest.mark.parametrize("blocks,buckets", [(1, 16), (37, 256), (2048, 256), (5000, 256), (300, 65536)])
+def test_radix_block_offsets(ctx, blocks, buckets):
+    # hw/hw4/programming/radixsort.cpp:85-97 through transpose + segmented exclusive scan + transpose, bit-exact
+    rng = np.random.default_rng(blocks + buckets)
+    local = rng.integers(0, 2**32 if blocks < 100 else 9000, (blocks, buckets), dtype=np.uint64).astype(np.uint32)
+    glob = oracle.exclusive_scan_u32(local.sum(0, dtype=np.uint64).astype(np.uint32))
+    d_out = dev_empty(blocks * buckets, np.uint32)
+    ctx.call("cme213_block_offsets_u32", dev(local), dev(glob), d_out, blocks, buckets)
+    assert np.array_equal(host(d_out, np.uint32).reshape(blocks, buckets), oracle.block_offsets_u32(local, glob))
+
+
+def test_blocked_radix_pass_sorts(ctx):
+    # one full blocked LSD pass (radixSortParallelPass, radixsort.cpp:44-109): per-block histograms on the host here,
+    # global exclusive scan and per-block offsets on the GPU, stable scatter; four passes sort the keys
+    rng = np.random.default_rng(12)
+    keys = rng.integers(0, 2**32, 200000, dtype=np.uint64).astype(np.uint32)
+    bs, nb = 8192, 256
+    k = keys
+    for start in range(0, 32, 8):
+        digit = (k >> start) & 255
+        nblk = -(-len(k) // bs)
+        local = np.stack([np.bincount(digit[i * bs:(i + 1) * bs], minlength=nb) for i in range(nblk)]).astype(np.uint32)
+        tot = local.sum(0, dtype=np.uint64).astype(np.uint32)
+        d_tot = dev(tot)
+        ctx.call("cme213_exclusive_scan_u32", d_tot, d_tot, nb)
+        d_off = dev_empty(nblk * nb, np.uint32)
+        ctx.call("cme213_block_offsets_u32", dev(local), d_tot, d_off, nblk, nb)
+        off = host(d_off, np.uint32).reshape(nblk, nb).astype(np.int64)
+        out = np.empty_like(k)
+        for i in range(nblk):
+            blk, dg = k[i * bs:(i + 1) * bs], digit[i * bs:(i + 1) * bs]
+            order = np.argsort(dg, kind="stable")
+            rank = np.empty(len(blk), np.int64)
+            rank[order] = np.arange(len(blk)) - np.searchsorted(dg[order], dg[order], side="left")
+            out[off[i, dg] + rank] = blk
+        assert np.array_equal(out, oracle.radix_pass_u32(k, start, 8))
+        k = out
+    assert np.array_equal(k, np.sort(keys))
