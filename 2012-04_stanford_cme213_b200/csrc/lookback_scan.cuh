@@ -990,7 +990,7 @@ template <class P> struct Cfg {
     // finish deferred by 2 iterations (sweep in profiles/r01_notes.md; segmented scans also stage their flag words)
     static constexpr int B_THREADS = P::SEG ? 640 : 704, B_VECS = 5, B_STAGES = 4, B_DEFER = 2;
     static constexpr int DIRECT_THREADS = 256, DIRECT_VECS = 4; // one-tile-per-CTA kernel
-    static constexpr int DIRECT_MIN_BLOCKS = (P::SEG || P::NIN > 1) ? 4 : 6;   // register caps: 64 / 40 per thread
+    static constexpr int DIRECT_MIN_BLOCKS = 6;   // 40 registers per thread: the gather-heavy policies want occupancy more than registers (fused step 1.68 -> 1.41 ms)
 };
 
 // ---- host launchers ----------------------------------------------------------------------------------

@@ -277,6 +277,17 @@ int run(cme213_ctx *ctx, const P &p, int64_t n, bool vec_ok, void *stream, const
             }
         }
     }
+    if constexpr (!P::BULK) {
+        if (const char *cfg = getenv("CME213_DIRECT_CFG")) {  // tuning hook: "threads,vecs,min_blocks" for the one-CTA-per-tile kernel
+            int T_ = 0, V_ = 0, B_ = 0;
+            sscanf(cfg, "%d,%d,%d", &T_, &V_, &B_);
+            cudaStream_t st = (cudaStream_t)stream;
+#define CME213_TRY_DIRECT(T, V, B) if (T_ == T && V_ == V && B_ == B) return scan::launch_direct<P, T, V, B>(ctx, p, n, vec_ok, st, name, nullptr);
+            CME213_TRY_DIRECT(256, 4, 4) CME213_TRY_DIRECT(128, 8, 8)
+            CME213_TRY_DIRECT(256, 4, 6) CME213_TRY_DIRECT(256, 4, 8)
+#undef CME213_TRY_DIRECT
+        }
+    }
     return scan::launch<P>(ctx, p, n, vec_ok, (cudaStream_t)stream, name);
 }
 
