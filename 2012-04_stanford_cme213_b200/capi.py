@@ -55,6 +55,13 @@ PROTOTYPES = {
     "cme213_spmv_csr_block_rows": (_i, []),
     "cme213_spmv_csr_f32_ordered": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _p, _i64, _p]),
     "cme213_spmv_csr_f64_ordered": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _p, _i64, _p]),
+    "cme213_spmv_csr_f64_halo_push": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _p, _i64, _i64, _p, _p, _p]),
+    "cme213_device_malloc": (_i, [C.c_size_t, C.POINTER(_p)]),
+    "cme213_device_free": (_i, [_p]),
+    "cme213_ipc_handle_bytes": (_i, []),
+    "cme213_ipc_export": (_i, [_p, _p]),
+    "cme213_ipc_open": (_i, [_p, C.POINTER(_p)]),
+    "cme213_ipc_close": (_i, [_p]),
     "cme213_pagerank_propagate": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _p]),
     "cme213_spmv_ell_f32": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _p, _p]),
     "cme213_spmv_ell_f64": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _p, _p]),

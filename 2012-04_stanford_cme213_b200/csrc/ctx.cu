@@ -70,3 +70,35 @@ CME213_API int cme213_ctx_destroy(cme213_ctx *ctx) {
 CME213_API int cme213_ctx_device(const cme213_ctx *ctx) { return ctx ? ctx->device : -1; }
 CME213_API int cme213_ctx_sm_count(const cme213_ctx *ctx) { return ctx ? ctx->sm_count : -1; }
 CME213_API int64_t cme213_ctx_launch_count(const cme213_ctx *ctx) { return ctx ? ctx->launches : -1; }
+
+// ---- device memory that other processes of the same box can map (multi-GPU halo push) ----------------------
+// torch's caching allocator hands out pieces of large blocks, which cannot be exported one by one; vectors that a
+// neighbouring rank writes into are therefore allocated here, one cudaMalloc each, and exported whole.
+CME213_API int cme213_device_malloc(size_t bytes, void **d_out) {
+    if (!d_out) { cme213::set_error("device_malloc: null out pointer"); return CME213_ERR_INVALID; }
+    CME213_CUDA(cudaMalloc(d_out, bytes ? bytes : 16));
+    return CME213_OK;
+}
+CME213_API int cme213_device_free(void *d_ptr) {
+    if (d_ptr) CME213_CUDA(cudaFree(d_ptr));
+    return CME213_OK;
+}
+CME213_API int cme213_ipc_handle_bytes(void) { return (int)sizeof(cudaIpcMemHandle_t); }
+CME213_API int cme213_ipc_export(const void *d_ptr, void *handle_out) {
+    if (!d_ptr || !handle_out) { cme213::set_error("ipc_export: null pointer"); return CME213_ERR_INVALID; }
+    cudaIpcMemHandle_t h;
+    CME213_CUDA(cudaIpcGetMemHandle(&h, const_cast<void *>(d_ptr)));
+    memcpy(handle_out, &h, sizeof(h));
+    return CME213_OK;
+}
+CME213_API int cme213_ipc_open(const void *handle, void **d_out) {
+    if (!handle || !d_out) { cme213::set_error("ipc_open: null pointer"); return CME213_ERR_INVALID; }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    CME213_CUDA(cudaIpcOpenMemHandle(d_out, h, cudaIpcMemLazyEnablePeerAccess));
+    return CME213_OK;
+}
+CME213_API int cme213_ipc_close(void *d_ptr) {
+    if (d_ptr) CME213_CUDA(cudaIpcCloseMemHandle(d_ptr));
+    return CME213_OK;
+}

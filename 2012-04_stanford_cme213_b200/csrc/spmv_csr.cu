@@ -42,6 +42,10 @@ template <typename T> struct Args {
     T *w_out;       // PAGERANK_W: y[r]*inv[r] for the next iteration (may be null)
     T base;         // PAGERANK: 0.5/N
     const int32_t *order;  // stream kernel: CTA b works on row block order[b] (null = b); see cme213_spmv_csr_*_ordered
+    // halo push (multi-GPU, cme213_spmv_csr_f64_halo_push): rows below push_lo_end are also stored into peer_lo[r], rows
+    // from push_hi_begin on into peer_hi[r]; the peers are the neighbouring GPUs' vectors, mapped through CUDA IPC
+    T *peer_lo, *peer_hi;
+    int64_t push_lo_end, push_hi_begin;
 };
 
 template <typename T, int MODE>
@@ -61,6 +65,10 @@ template <typename T, int MODE>
 __device__ __forceinline__ void epilogue(const Args<T> &a, int64_t r, T sum) {
     if (MODE == MODE_CSR) {
         st_stream(a.y + r, sum);
+        // fused exchange: the halo rows go straight into the neighbours' memory over NVLink while the rest of the
+        // launch is still computing (plain stores: peer addresses bypass the local L2)
+        if (a.peer_lo && r < a.push_lo_end) a.peer_lo[r] = sum;
+        if (a.peer_hi && r >= a.push_hi_begin) a.peer_hi[r] = sum;
     } else {
         // graph_nodes_out[i] = 0.5f/N + 0.5f*sum   (pagerank.cu:54)
         const T out = add_rn(a.base, mul_rn(T(0.5), sum));
@@ -119,6 +127,17 @@ template <> struct V4<double> {
     }
 };
 
+template <typename T, int MODE>
+__device__ __forceinline__ void epilogue_lean(const Args<T> &a, int64_t r, T sum) {
+    if (MODE == MODE_CSR) {
+        st_stream(a.y + r, sum);
+    } else {
+        const T out = add_rn(a.base, mul_rn(T(0.5), sum));
+        a.y[r] = out;
+        if (a.w_out) a.w_out[r] = mul_rn(out, a.inv[r]);
+    }
+}
+
 // The plain fast path: rows in index order.  Deliberately minimal -- it compiles to 32 registers
 // (8 CTAs of 256 threads per SM); the feature-complete kernel below (block lists, padded products) needs 38-40
 // and measured 5-30 % slower on the same inputs, so it only runs when one of its features is asked for.
@@ -171,7 +190,7 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
         for (int j = lo; j < hi; j++) sum = add_rn(sum, prod[pidx(j - base)]);
         __syncthreads();
     }
-    if (r < row_end) epilogue<T, MODE>(a, r, sum);
+    if (r < row_end) epilogue_lean<T, MODE>(a, r, sum);
 }
 
 template <typename T, int MODE, int THREADS, int RPT, int TILE, bool PADDED, bool ORDERED = true, bool KEEP = true>
@@ -332,16 +351,18 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
     return CME213_OK;
 }
 
+template <typename T> struct Push { T *peer_lo = nullptr, *peer_hi = nullptr; int64_t lo_end = 0, hi_begin = 0; };
+
 template <typename T>
 int spmv_csr_impl(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, const int32_t *d_row_ptr, const int32_t *d_col,
                   const T *d_val, const T *d_x, T *d_y, int kernel, void *stream, const int32_t *d_order = nullptr,
-                  int64_t num_blocks = -1) {
+                  int64_t num_blocks = -1, Push<T> push = Push<T>()) {
     CME213_CHECK_CTX(ctx);
     if (row_begin < 0 || row_end < row_begin) { set_error("spmv_csr: bad row range"); return CME213_ERR_INVALID; }
     if (row_end == row_begin) return CME213_OK;
     if (!d_row_ptr || !d_col || !d_val || !d_x || !d_y) { set_error("spmv_csr: null pointer"); return CME213_ERR_INVALID; }
     DeviceGuard g(ctx->device);
-    Args<T> a{d_row_ptr, d_col, d_val, d_x, nullptr, d_y, nullptr, T(0), d_order};
+    Args<T> a{d_row_ptr, d_col, d_val, d_x, nullptr, d_y, nullptr, T(0), d_order, push.peer_lo, push.peer_hi, push.lo_end, push.hi_begin};
     if (d_order && !(aligned16(d_col) && aligned16(d_val))) { set_error("spmv_csr ordered: col/val must be 16-byte aligned"); return CME213_ERR_INVALID; }
     if (d_order && (num_blocks < 0 || num_blocks > div_up(row_end - row_begin, 256))) { set_error("spmv_csr ordered: bad num_blocks"); return CME213_ERR_INVALID; }
     return launch_csr<T, MODE_CSR>(ctx, a, row_begin, row_end, d_order ? CME213_CSR_STREAM : kernel, (cudaStream_t)stream,
@@ -373,6 +394,21 @@ CME213_API int cme213_spmv_csr_f64_ordered(cme213_ctx *ctx, int64_t row_begin, i
     return spmv_csr_impl<double>(ctx, row_begin, row_end, d_row_ptr, d_col, d_val, d_x, d_y, CME213_CSR_STREAM, stream, d_block_order, num_blocks);
 }
 
+// Boundary launch of the multi-GPU iterate with the exchange fused in: computes the listed row blocks like
+// cme213_spmv_csr_f64_ordered and additionally stores rows [row_begin, row_begin+halo_rows) into d_peer_prev_y[r] and
+// rows [row_end-halo_rows, row_end) into d_peer_next_y[r] (either may be NULL).  The peer pointers are the
+// neighbouring ranks' output vectors opened with cme213_ipc_open and shifted like d_y, so index r means the same row.
+CME213_API int cme213_spmv_csr_f64_halo_push(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, const int32_t *d_row_ptr,
+                                             const int32_t *d_col, const double *d_val, const double *d_x, double *d_y,
+                                             const int32_t *d_block_order, int64_t num_blocks, int64_t halo_rows,
+                                             double *d_peer_prev_y, double *d_peer_next_y, void *stream) {
+    if (!d_block_order || halo_rows < 0 || halo_rows > row_end - row_begin) { set_error("spmv_csr halo_push: bad arguments"); return CME213_ERR_INVALID; }
+    Push<double> push;
+    push.peer_lo = d_peer_prev_y; push.peer_hi = d_peer_next_y;
+    push.lo_end = row_begin + halo_rows; push.hi_begin = row_end - halo_rows;
+    return spmv_csr_impl<double>(ctx, row_begin, row_end, d_row_ptr, d_col, d_val, d_x, d_y, CME213_CSR_STREAM, stream, d_block_order, num_blocks, push);
+}
+
 CME213_API int cme213_pagerank_propagate(cme213_ctx *ctx, const uint32_t *d_graph_indices,
                                          const uint32_t *d_graph_edges, const float *d_nodes_in, float *d_nodes_out,
                                          const float *d_inv_edges_per_node, int array_length, int kernel,
@@ -388,7 +424,7 @@ CME213_API int cme213_pagerank_propagate(cme213_ctx *ctx, const uint32_t *d_grap
     // 0.5f/(float)array_length, rounded once on the host exactly as pagerank.cu:54 rounds it.
     const float base = 0.5f / (float)array_length;
     Args<float> a{(const int32_t *)d_graph_indices, (const int32_t *)d_graph_edges, nullptr, d_nodes_in,
-                  d_inv_edges_per_node, d_nodes_out, nullptr, base, nullptr};
+                  d_inv_edges_per_node, d_nodes_out, nullptr, base, nullptr, nullptr, nullptr, 0, 0};
     return launch_csr<float, MODE_PAGERANK>(ctx, a, 0, array_length, kernel, (cudaStream_t)stream);
 }
 
@@ -403,10 +439,10 @@ int cme213_internal_pagerank_propagate_w(cme213_ctx *ctx, const uint32_t *d_grap
     const float base = 0.5f / (float)array_length;
     if (d_nodes_in) {
         Args<float> a{(const int32_t *)d_graph_indices, (const int32_t *)d_graph_edges, nullptr, d_nodes_in, d_inv,
-                      d_nodes_out, d_w_out, base, nullptr};
+                      d_nodes_out, d_w_out, base, nullptr, nullptr, nullptr, 0, 0};
         return launch_csr<float, MODE_PAGERANK>(ctx, a, 0, array_length, CME213_CSR_STREAM, (cudaStream_t)stream);
     }
     Args<float> a{(const int32_t *)d_graph_indices, (const int32_t *)d_graph_edges, nullptr, d_w_in, d_inv,
-                  d_nodes_out, d_w_out, base, nullptr};
+                  d_nodes_out, d_w_out, base, nullptr, nullptr, nullptr, 0, 0};
     return launch_csr<float, MODE_PAGERANK_W>(ctx, a, 0, array_length, CME213_CSR_STREAM, (cudaStream_t)stream);
 }

@@ -13,6 +13,9 @@ stream while the interior rows are computed.
 Exchange modes
   full : every rank all-gathers its whole y slice into everybody's x (N*8/P bytes sent per rank).
          Always correct; costs more than the SpMV itself beyond 2 GPUs for the 7-point stencil.
+  fused: the boundary launch itself stores the halo planes into the neighbours' vectors (peer memory over NVLink,
+         mapped with CUDA IPC: cme213_spmv_csr_f64_halo_push); NCCL only orders the ranks afterwards (a one-element
+         all-reduce on the second stream, hidden behind the interior rows).  Needs vectors from `shared_vector`.
   p2p  : same data as `halo`, moved by NCCL send/recv between neighbours straight out of / into the full-length
          vector (no pack / unpack copies).
   halo : for a matrix of half-bandwidth `halo` (max |col - row|), rank r only needs the last `halo`
@@ -48,7 +51,7 @@ class ShardedIterate:
     logic over gloo.
     """
 
-    def __init__(self, rows, world, rank, spmv, x_a, x_b, halo=None, mode="halo", dist=None, streams=None):
+    def __init__(self, rows, world, rank, spmv, x_a, x_b, halo=None, mode="halo", dist=None, streams=None, peers=None):
         self.rows, self.world, self.rank = rows, world, rank
         self.spmv = spmv
         self.x = [x_a, x_b]  # full-length ping-pong vectors
@@ -57,7 +60,10 @@ class ShardedIterate:
         self.lo, self.hi = self.parts[rank]
         self.mode = mode if world > 1 else "none"
         self.halo = int(halo) if halo is not None else None
-        if self.mode in ("halo", "p2p"):
+        self.peers = peers  # fused mode: PeerVectors of x_a / x_b
+        if self.mode == "fused" and (peers is None or not hasattr(spmv, "push")):
+            raise ValueError("fused exchange needs peer-mapped vectors (shared_vector / PeerVectors) and a CUDA spmv binding")
+        if self.mode in ("halo", "p2p", "fused"):
             smallest = min(e - b for b, e in self.parts)
             if self.halo is None or not equal_partition_ok(rows, world) or smallest < 2 * self.halo:
                 self.mode = "full"  # shards too thin (or ragged) for the two-piece halo layout
@@ -73,8 +79,10 @@ class ShardedIterate:
             self.comm_bytes_per_step = (world - 1) * (self.hi - self.lo) * x_a.element_size()
         elif self.mode == "halo":
             self.comm_bytes_per_step = (world - 1) * 2 * self.halo * x_a.element_size()
-        elif self.mode == "p2p":
+        elif self.mode in ("p2p", "fused"):
             self.comm_bytes_per_step = ((rank > 0) + (rank < world - 1)) * self.halo * x_a.element_size()
+        if self.mode == "fused":
+            self.token = x_a.new_zeros(1)
 
     # -- helpers ---------------------------------------------------------------------------------
     def _on(self, stream):
@@ -104,6 +112,23 @@ class ShardedIterate:
             return
         h = self.halo
         cs, ms = self.compute_stream, self.comm_stream
+        if self.mode == "fused":
+            with self._on(cs):
+                # 1. boundary rows, pushed into the neighbours' xout by the kernel's own stores
+                self.spmv.push(lo, hi, h, xin, xout, self.peers.prev(dst), self.peers.next(dst))
+                ready = self._event(cs)
+            with self._on(ms):
+                # 2. order the ranks: after this collective every neighbour's boundary launch has completed, so what
+                #    it pushed into this rank's xout is there
+                if ready is not None:
+                    ms.wait_event(ready)
+                self.dist.all_reduce(self.token)
+                done = self._event(ms)
+            with self._on(cs):
+                self.spmv(lo + h, hi - h, xin, xout)
+                if done is not None:
+                    cs.wait_event(done)
+            return
         if self.mode == "p2p":
             with self._on(cs):
                 # 1. boundary rows first (one launch when the kernel binding offers it): they are the neighbours' halo
@@ -272,8 +297,79 @@ def cuda_spmv(ctx, row_lo_global, d_row_ptr_local, d_col, d_val, kernel=0, order
         ctx.call(fn + "_ordered", lo - row_lo_global, hi - row_lo_global, d_row_ptr_local, d_col, d_val, x_full,
                  y_full.data_ptr() + row_lo_global * esize, o, o.numel(), stream=torch.cuda.current_stream())
 
+    def spmv_push(lo, hi, h, x_full, y_full, peer_prev, peer_next):
+        """boundary launch with the halo exchange fused in; peer_prev / peer_next are the base addresses of the
+        neighbours' output vectors (0 = no neighbour on that side)."""
+        key = ("pair", lo, hi, h)
+        if key not in orders:
+            br = int(ctx.lib.cme213_spmv_csr_block_rows())
+            if h % br or (hi - lo) % br:
+                raise ValueError("fused exchange needs halo and shard sizes that are multiples of %d rows" % br)
+            nb, hb = (hi - lo) // br, h // br
+            orders[key] = torch.cat([torch.arange(hb, device="cuda"), torch.arange(nb - hb, nb, device="cuda")]).to(torch.int32)
+        o = orders[key]
+        if o is None:
+            raise ValueError("fused exchange needs halo and shard sizes that are multiples of the kernel's block rows")
+        shift = row_lo_global * esize
+        ctx.call("cme213_spmv_csr_f64_halo_push", lo - row_lo_global, hi - row_lo_global, d_row_ptr_local, d_col, d_val, x_full,
+                 y_full.data_ptr() + shift, o, o.numel(), h, (peer_prev + shift) if peer_prev else None,
+                 (peer_next + shift) if peer_next else None, stream=torch.cuda.current_stream())
+
     spmv.two_ranges = spmv_two_ranges
+    if d_val.dtype == torch.float64:
+        spmv.push = spmv_push
     return spmv
+
+
+class _RawCuda:
+    def __init__(self, ptr, n, typestr):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 3}
+
+
+def shared_vector(lib, n, dtype="f8"):
+    """A device vector from one cudaMalloc of its own (exportable to the other ranks), as (torch tensor, address)."""
+    import ctypes as C
+    import torch
+    p = C.c_void_p()
+    rc = lib.cme213_device_malloc(n * int(dtype[1:]), C.byref(p))
+    if rc:
+        raise RuntimeError(lib.cme213_last_error().decode())
+    return torch.as_tensor(_RawCuda(p.value, n, "<" + dtype), device="cuda"), p.value
+
+
+class PeerVectors:
+    """The two ping-pong vectors of the neighbouring ranks, mapped into this process through CUDA IPC."""
+
+    def __init__(self, lib, dist, rank, world, addrs):
+        import ctypes as C
+        nbytes = lib.cme213_ipc_handle_bytes()
+        mine = []
+        for a in addrs:
+            buf = C.create_string_buffer(nbytes)
+            if lib.cme213_ipc_export(C.c_void_p(a), buf):
+                raise RuntimeError(lib.cme213_last_error().decode())
+            mine.append(buf.raw)
+        everyone = [None] * world
+        dist.all_gather_object(everyone, mine)
+        self.lib = lib
+        self._prev, self._next = [0, 0], [0, 0]
+
+        def open_(raw):
+            p = C.c_void_p()
+            if lib.cme213_ipc_open(C.create_string_buffer(raw, nbytes), C.byref(p)):
+                raise RuntimeError(lib.cme213_last_error().decode())
+            return p.value
+
+        if rank > 0:
+            self._prev = [open_(h) for h in everyone[rank - 1]]
+        if rank < world - 1:
+            self._next = [open_(h) for h in everyone[rank + 1]]
+
+    def prev(self, which):
+        return self._prev[which]
+
+    def next(self, which):
+        return self._next[which]
 
 
 def half_bandwidth(row_ptr, col, row_offset=0):

@@ -151,6 +151,25 @@ int cme213_spmv_csr_f64_ordered(cme213_ctx *ctx, int64_t row_begin, int64_t row_
                                 const int32_t *d_col, const double *d_val, const double *d_x, double *d_y,
                                 const int32_t *d_block_order, int64_t num_blocks, void *stream);
 
+/* Multi-GPU boundary launch with the exchange fused into the kernel: like cme213_spmv_csr_f64_ordered, and rows
+ * [row_begin, row_begin+halo_rows) are also stored into d_peer_prev_y[r], rows [row_end-halo_rows, row_end) into
+ * d_peer_next_y[r] (either may be NULL): the neighbouring GPUs' vectors, mapped with cme213_ipc_open and shifted
+ * like d_y, so the halo planes travel over NVLink as the rows are produced.  The caller still has to order the
+ * ranks (any collective after the launch) before the neighbours read what was pushed.
+ * reference: none (the reference's only exchange is the CPU MPI halo of hw/hw5/programming/2dHeat.cpp:503-547). */
+int cme213_spmv_csr_f64_halo_push(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, const int32_t *d_row_ptr,
+                                  const int32_t *d_col, const double *d_val, const double *d_x, double *d_y,
+                                  const int32_t *d_block_order, int64_t num_blocks, int64_t halo_rows,
+                                  double *d_peer_prev_y, double *d_peer_next_y, void *stream);
+/* Device vectors another process of the same box can map: one cudaMalloc each (exportable as a whole), an opaque
+ * handle of cme213_ipc_handle_bytes() bytes to send to the peer, and open/close on the peer's side. */
+int cme213_device_malloc(size_t bytes, void **d_out);
+int cme213_device_free(void *d_ptr);
+int cme213_ipc_handle_bytes(void);
+int cme213_ipc_export(const void *d_ptr, void *handle_out);
+int cme213_ipc_open(const void *handle, void **d_out);
+int cme213_ipc_close(void *d_ptr);
+
 /* PageRank propagate: out[i] = 0.5f/N + 0.5f * sum_j in[e[j]] * inv[e[j]].
  * reference: hw/hw1/programming/pagerank.cu:45-56 (CPU), :70-83 (GPU). */
 int cme213_pagerank_propagate(cme213_ctx *ctx, const uint32_t *d_graph_indices, const uint32_t *d_graph_edges,

@@ -50,13 +50,20 @@ def main():
     assert sh.half_bandwidth(d_ptr, d_col, lo) == g * g
     ok = True
     results = {}
-    for mode in ("p2p", "halo", "full"):
-        xa = torch.empty(rows, dtype=torch.float64, device="cuda")
+    for mode in ("fused", "p2p", "halo", "full"):
+        peers = None
+        if mode == "fused":
+            xa, pa = sh.shared_vector(ctx.lib, rows)
+            xb, pb = sh.shared_vector(ctx.lib, rows)
+            xb.zero_()
+            peers = sh.PeerVectors(ctx.lib, dist, rank, world, [pa, pb])
+        else:
+            xa = torch.empty(rows, dtype=torch.float64, device="cuda")
+            xb = torch.zeros_like(xa)
         ctx.call("cme213_fill_uniform_f64", xa, rows, 9)
-        xb = torch.zeros_like(xa)
         streams = (torch.cuda.current_stream(), torch.cuda.Stream())
         it = sh.ShardedIterate(rows, world, rank, sh.cuda_spmv(ctx, lo, d_ptr, d_col, d_val), xa, xb, halo=g * g, mode=mode,
-                               dist=dist, streams=streams)
+                               dist=dist, streams=streams, peers=peers)
         it.iterate(a.iters)
         torch.cuda.synchronize()
         results[mode] = (it.mode, it.gather_result(0))
