@@ -343,14 +343,16 @@ class PeerVectors:
     def __init__(self, lib, dist, rank, world, addrs):
         import ctypes as C
         nbytes = lib.cme213_ipc_handle_bytes()
-        mine = []
+        mine, failed = [], None
         for a in addrs:
             buf = C.create_string_buffer(nbytes)
             if lib.cme213_ipc_export(C.c_void_p(a), buf):
-                raise RuntimeError(lib.cme213_last_error().decode())
+                failed = lib.cme213_last_error().decode()
             mine.append(buf.raw)
         everyone = [None] * world
-        dist.all_gather_object(everyone, mine)
+        dist.all_gather_object(everyone, None if failed else mine)   # always reached: no rank is left waiting
+        if failed or any(e is None for e in everyone):
+            raise RuntimeError(failed or "a peer could not export its vectors")
         self.lib = lib
         self._prev, self._next = [0, 0], [0, 0]
 

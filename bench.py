@@ -94,6 +94,41 @@ def i32(n, torch):
     return torch.empty(int(n), dtype=torch.int32, device="cuda")
 
 
+def make_vectors(sh, ctx, torch, dist, rank, world, rows, halo, exchange):
+    """The two full-length ping-pong vectors.  `fused` needs vectors the neighbours can map (one cudaMalloc each,
+    exported through CUDA IPC) and shard / halo sizes that are whole 256-row blocks; if any rank cannot set that
+    up, every rank falls back to `p2p` (NCCL send/recv)."""
+    if world > 1 and exchange == "fused":
+        ok, xa = 1, None
+        try:
+            per = rows // world
+            if rows % world or per % 256 or halo % 256 or per < 2 * halo:
+                raise ValueError("shape not suited to the fused exchange")
+            xa, pa = sh.shared_vector(ctx.lib, rows)
+            xb, pb = sh.shared_vector(ctx.lib, rows)
+            xb.zero_()
+        except Exception as e:  # noqa: BLE001
+            log("[bench] fused exchange unavailable on rank %d (%r)" % (rank, e))
+            ok = 0
+        flag = torch.tensor([ok], device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 1:
+            peers = None
+            try:
+                peers = sh.PeerVectors(ctx.lib, dist, rank, world, [pa, pb])
+            except Exception as e:  # noqa: BLE001 -- IPC refused by the driver / container
+                log("[bench] CUDA IPC unavailable on rank %d (%r)" % (rank, e))
+                ok = 0
+            flag = torch.tensor([ok], device="cuda")
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)    # every rank reaches the same conclusion
+            if int(flag.item()) == 1:
+                return xa, xb, peers, "fused"
+        exchange = "p2p"
+    xa = torch.empty(rows, dtype=torch.float64, device="cuda")
+    xb = torch.zeros(rows, dtype=torch.float64, device="cuda")
+    return xa, xb, None, exchange
+
+
 def make_c5(ctx, torch, args, rank, world, dist):
     import ctypes as C
     pkg = importlib.import_module(PKG)
@@ -108,21 +143,13 @@ def make_c5(ctx, torch, args, rank, world, dist):
     d_col = i32(nnz.value, torch)
     d_val = torch.empty(nnz.value, dtype=torch.float64, device="cuda")
     ctx.call("cme213_gen_laplace3d_f64", g, g, g, lo, hi, d_ptr, d_col, d_val, C.byref(nnz))
-    peers = None
-    if world > 1 and args.exchange == "fused":
-        xa, pa = sh.shared_vector(ctx.lib, rows)
-        xb, pb = sh.shared_vector(ctx.lib, rows)
-        xb.zero_()
-        peers = sh.PeerVectors(ctx.lib, dist, rank, world, [pa, pb])
-    else:
-        xa = torch.empty(rows, dtype=torch.float64, device="cuda")
-        xb = torch.zeros(rows, dtype=torch.float64, device="cuda")
+    xa, xb, peers, exchange = make_vectors(sh, ctx, torch, dist, rank, world, rows, g * g, args.exchange)
     ctx.call("cme213_fill_uniform_f64", xa, rows, 9)
     xa.mul_(0.05)  # keeps 7-point growth (|lambda| <= 12) far from overflow over the run
     streams = (torch.cuda.current_stream(), torch.cuda.Stream()) if world > 1 else None
     order_fn = (lambda a, b: sh.grid3d_block_order(g, g, g, a, b, strip_lines=args.order_strip)) if args.order_strip > 0 else None
     it = sh.ShardedIterate(rows, world, rank, sh.cuda_spmv(ctx, lo, d_ptr, d_col, d_val, args.csr_kernel, order_fn), xa, xb,
-                           halo=g * g, mode=args.exchange, dist=dist, streams=streams, peers=peers)
+                           halo=g * g, mode=exchange, dist=dist, streams=streams, peers=peers)
     state = {"src": 0}
     replay = it.capture_pair() if (world > 1 and args.graph) else None
 
@@ -540,11 +567,10 @@ def e2e_c5_sharded(torch, pkg, wl, args, rank, world, dist, iters):
     h_y = torch.empty(hi - lo, dtype=torch.float64).pin_memory()
     # device buffers of the call (allocated once: the host-pointer API keeps its workspace between calls)
     e_ptr, e_col, e_val = torch.empty_like(d_ptr), torch.empty_like(d_col), torch.empty_like(d_val)
-    xa = torch.empty(rows, dtype=torch.float64, device="cuda")
-    xb = torch.empty_like(xa)
+    xa, xb, peers, exchange = make_vectors(sh, ctx, torch, dist, rank, world, rows, g * g, args.exchange)
     streams = (torch.cuda.current_stream(), torch.cuda.Stream())
     it = sh.ShardedIterate(rows, world, rank, sh.cuda_spmv(ctx, lo, e_ptr, e_col, e_val, args.csr_kernel), xa, xb,
-                           halo=g * g, mode=args.exchange, dist=dist, streams=streams)
+                           halo=g * g, mode=exchange, dist=dist, streams=streams, peers=peers)
 
     def call():
         e_ptr.copy_(h_ptr, non_blocking=True); e_col.copy_(h_col, non_blocking=True); e_val.copy_(h_val, non_blocking=True)
@@ -578,8 +604,8 @@ def main():
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--workload", default="c5")
     ap.add_argument("--grid", type=int, default=512)
-    ap.add_argument("--exchange", default="p2p", choices=["fused", "p2p", "halo", "full"],
-                    help="N>1: p2p = NCCL send/recv of the halo planes between neighbours; halo = one all-gather of every rank's boundary planes; full = all-gather of the whole vector")
+    ap.add_argument("--exchange", default="fused", choices=["fused", "p2p", "halo", "full"],
+                    help="N>1: fused = the boundary launch stores the halo planes into the neighbours' vectors over peer memory (falls back to p2p when CUDA IPC or the shape does not allow it); p2p = NCCL send/recv of the halo planes between neighbours; halo = one all-gather of every rank's boundary planes; full = all-gather of the whole vector")
     ap.add_argument("--csr-kernel", type=int, default=0)
     ap.add_argument("--graph", type=int, default=1, help="N>1: replay a CUDA graph of two passes instead of launching eagerly")
     ap.add_argument("--order-strip", type=int, default=0, help="C5: CTA order = z fastest inside strips of this many grid lines (0 = row order)")
