@@ -76,6 +76,8 @@ PROTOTYPES = {
     "cme213_csr_to_coo_tail_f32": (_i, [_p, _i64, _p, _p, _p, _i, _pi64, _p, _p, _p, _p]),
     "cme213_csr_to_coo_tail_f64": (_i, [_p, _i64, _p, _p, _p, _i, _pi64, _p, _p, _p, _p]),
     "cme213_block_offsets_u32": (_i, [_p, _p, _p, _p, _i64, _i64, _p]),
+    "cme213_radix_sort_pass_u32": (_i, [_p, _p, _p, _i64, _i, _i, _p]),
+    "cme213_radix_sort_u32": (_i, [_p, _p, _p, _i64, _i, _p]),
     "cme213_gen_laplace2d_f32": (_i, [_p, _i, _i, _p, _p, _p, _pi64, _p]),
     "cme213_gen_laplace3d_f64": (_i, [_p, _i, _i, _i, _i64, _i64, _p, _p, _p, _pi64, _p]),
     "cme213_gen_powerlaw_lengths": (_i, [_p, _i64, _i, _u32, _u32, _i, _u32, _p, _pi64, _p]),
@@ -92,6 +94,7 @@ PROTOTYPES = {
     "cme213_fp_iterate_host_f32": (_i, [_i, _i, _i, _i, _p, _p, _p, _p, _p, _pf]),
     "cme213_fp_iterate_host_f64": (_i, [_i, _i, _i, _i, _p, _p, _p, _p, _p, _pf]),
     "cme213_exclusive_scan_u32_host": (_i, [_p, _p, _i64]),
+    "cme213_radix_sort_u32_host": (_i, [_p, _i64, _i, _pf]),
     "cme213_transpose_host_b32": (_i, [_p, _p, _i64, _i64]),
     "cme213_transpose_host_b64": (_i, [_p, _p, _i64, _i64]),
 }

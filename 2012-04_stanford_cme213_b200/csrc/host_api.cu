@@ -257,6 +257,26 @@ CME213_API int cme213_exclusive_scan_u32_host(const uint32_t *h_in, uint32_t *h_
     CME213_CUDA(cudaMemcpy(h_out, d, (size_t)n * 4, cudaMemcpyDeviceToHost));
     return CME213_OK;
 }
+CME213_API int cme213_radix_sort_u32_host(uint32_t *h_keys, int64_t n, int num_bits, float *kernel_ms_out) {
+    if (kernel_ms_out) *kernel_ms_out = 0.f;
+    if (n < 0) { set_error("radix_sort_u32_host: negative size"); return CME213_ERR_INVALID; }
+    if (num_bits < 1 || num_bits > 16) { set_error("radix_sort_u32_host: num_bits must be 1..16"); return CME213_ERR_INVALID; }
+    if (n == 0) return CME213_OK;
+    if (!h_keys) { set_error("radix_sort_u32_host: null pointer"); return CME213_ERR_INVALID; }
+    CtxHolder c;
+    TRY(c.init());
+    DeviceBuffers buf;
+    uint32_t *d_keys, *d_tmp;
+    TRY(buf.alloc(&d_keys, (size_t)n));
+    TRY(buf.alloc(&d_tmp, (size_t)n));
+    CME213_CUDA(cudaMemcpy(d_keys, h_keys, (size_t)n * 4, cudaMemcpyHostToDevice));
+    Timer t;
+    TRY(t.start());
+    TRY(cme213_radix_sort_u32(c.ctx, d_keys, d_tmp, n, num_bits, nullptr));
+    TRY(t.stop(kernel_ms_out));
+    CME213_CUDA(cudaMemcpy(h_keys, d_keys, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    return CME213_OK;
+}
 CME213_API int cme213_transpose_host_b32(const void *h_in, void *h_out, int64_t rows, int64_t cols) {
     return transpose_host<uint32_t>(h_in, h_out, rows, cols);
 }

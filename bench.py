@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- measures the hot path on B200 (see DESIGN.md "Measurement").
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c5|c1|scan|segscan|fp|transpose32|
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c5|c1|scan|segscan|radixsort|fp|transpose32|
                      transpose64|ell|hyb|csr_powerlaw|pagerank] [--impl ours|reference] [--extras 0|1]
 
 Default workload = BASELINE.json config C5: row-sharded CSR SpMV iteration on the 3-D 7-point
@@ -226,6 +226,28 @@ def make_scan(ctx, torch, args):
                       "l2": "2.1 GB per pass >> L2"}, keep=(x, out))
 
 
+def make_radixsort(ctx, torch, args):
+    # 8f.4: LSD radix sort of 2^28 uint32 keys, 8-bit digits (the reference's default numBits, radixsort.cpp:165;
+    # its default size is 40 M keys).  The four passes run out of place from a pristine buffer so that every
+    # timed step sorts the same unsorted keys.
+    n = 1 << 28
+    x = i32(n, torch)
+    ctx.call("cme213_fill_hash_u32", x, n, 5, 0)
+    a, b = torch.empty_like(x), torch.empty_like(x)
+
+    def step():
+        st = torch.cuda.current_stream()
+        ctx.call("cme213_radix_sort_pass_u32", x, a, n, 0, 8, stream=st)
+        ctx.call("cme213_radix_sort_pass_u32", a, b, n, 8, 8, stream=st)
+        ctx.call("cme213_radix_sort_pass_u32", b, a, n, 16, 8, stream=st)
+        ctx.call("cme213_radix_sort_pass_u32", a, b, n, 24, 8, stream=st)
+
+    return dict(step=step, alg_bytes=4 * 12 * n, flops=0, kernel="radix_scatter_kernel", launches_per_step=12,
+                meta={"workload": "8f.4: LSD radix sort of 2^28 uint32 keys, 4 passes of 8 bits (12 B per key per pass: "
+                                  "histogram read, scatter read + write)", "n": n,
+                      "l2": "1.07 GB of keys >> L2"}, keep=(x, a, b))
+
+
 def make_segscan(ctx, torch, args):
     n = 1 << 28
     v = torch.empty(n, dtype=torch.float32, device="cuda")
@@ -369,6 +391,8 @@ def build_workload(name, ctx, torch, args, rank=0, world=1, dist=None):
         return make_scan(ctx, torch, args)
     if name == "segscan":
         return make_segscan(ctx, torch, args)
+    if name == "radixsort":
+        return make_radixsort(ctx, torch, args)
     if name == "fp":
         return make_fp(ctx, torch, args)
     if name == "transpose32":
@@ -693,7 +717,7 @@ def main():
         others = []
         del wl
         torch.cuda.empty_cache()
-        names = ["scan", "segscan", "fp", "transpose32", "transpose64", "c1", "ell", "hyb", "csr_powerlaw",
+        names = ["scan", "segscan", "radixsort", "fp", "transpose32", "transpose64", "c1", "ell", "hyb", "csr_powerlaw",
                  "ell_window", "hyb_window", "csr_window", "ell_regular_window", "csr_regular_window", "pagerank"]
         for name in names:
             try:

@@ -229,6 +229,20 @@ int cme213_csr_to_coo_tail_f64(cme213_ctx *ctx, int64_t num_rows, const int32_t 
 int cme213_block_offsets_u32(cme213_ctx *ctx, const uint32_t *d_local_hist, const uint32_t *d_global_excl,
                              uint32_t *d_out, int64_t num_blocks, int64_t num_buckets, void *stream);
 
+/* ---- LSD radix sort on the scan ---------------------------- */
+/* One stable counting pass on the digit (key >> start_bit) & ((1 << num_bits) - 1), num_bits 1..8:
+ * per-8192-key-block histograms, ONE exclusive scan of the digit-major histogram table, stable scatter.
+ * reference: hw/hw4/programming/radixsort.cpp:44-109 (radixSortParallelPass; its blockSize is 8192 too, :115).
+ * d_keys_in and d_keys_out must not overlap; n <= 2^31-1. */
+int cme213_radix_sort_pass_u32(cme213_ctx *ctx, const uint32_t *d_keys_in, uint32_t *d_keys_out, int64_t n,
+                               int start_bit, int num_bits, void *stream);
+/* Sorts d_keys ascending in place, using d_keys_tmp (n words) as the other half of the ping-pong.
+ * reference: radixsort.cpp:111-121 (radixSortParallel(keys, keys_tmp, numBits)); num_bits 1..16 as there
+ * (the assert at :113).  The device digit is min(num_bits, 8) bits wide -- the sorted result does not depend
+ * on it -- and the result always ends in d_keys, as the reference's paired passes guarantee. */
+int cme213_radix_sort_u32(cme213_ctx *ctx, uint32_t *d_keys, uint32_t *d_keys_tmp, int64_t n, int num_bits,
+                          void *stream);
+
 /* ---- input generators (device side, deterministic) ---------------------- */
 /* The homework drivers generate their inputs in main(); the large configurations cannot be
  * generated on the host in reasonable time, so the same recipes run on the device.  Row pointers
@@ -291,6 +305,9 @@ int cme213_fp_iterate_host_f64(int n, int p, int q, int iters, const double *h_a
                                const int32_t *h_k, const double *h_x, double *h_b, float *kernel_ms_out);
 /* Host-pointer twins of the primitives. */
 int cme213_exclusive_scan_u32_host(const uint32_t *h_in, uint32_t *h_out, int64_t n);
+/* radixSortParallel on host memory (radixsort.cpp:111-121): h_keys sorted in place; kernel_ms_out (may be NULL)
+ * gets the device time of the passes, the figure the reference's main() prints (radixsort.cpp:191-196). */
+int cme213_radix_sort_u32_host(uint32_t *h_keys, int64_t n, int num_bits, float *kernel_ms_out);
 int cme213_transpose_host_b32(const void *h_in, void *h_out, int64_t rows, int64_t cols);
 int cme213_transpose_host_b64(const void *h_in, void *h_out, int64_t rows, int64_t cols);
 

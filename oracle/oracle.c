@@ -322,6 +322,55 @@ ORACLE_API void oracle_radix_pass_u32(const uint32_t *keys, uint32_t *out, int64
     free(ex);
 }
 
+/* The blocked pass, hw/hw4/programming/radixsort.cpp:44-109 (radixSortParallelPass): per-block histograms
+ * (UPSWEEP 1, :50-57), summed over the blocks (:63-70), scanned (:75-81), pushed back down to per-block
+ * offsets (:85-97), then each block scatters with its own offsets (:103-108).  OpenMP over the blocks as
+ * in the reference; the result equals the serial pass whatever block_size is. */
+ORACLE_API void oracle_radix_pass_blocked_u32(const uint32_t *keys, uint32_t *out, int64_t n, uint32_t start_bit,
+                                              uint32_t num_bits, int64_t block_size) {
+    const uint32_t nb = 1u << num_bits, mask = nb - 1;
+    const int64_t blocks = (n + block_size - 1) / block_size;
+    if (blocks == 0) return;
+    uint32_t *local = (uint32_t *)calloc((size_t)blocks * nb, sizeof(uint32_t));
+    uint32_t *final = (uint32_t *)calloc((size_t)blocks * nb, sizeof(uint32_t));
+    uint32_t *glob = (uint32_t *)calloc(nb, sizeof(uint32_t));
+#pragma omp parallel for schedule(static)
+    for (int64_t b = 0; b < blocks; ++b) {
+        const int64_t lo = b * block_size, hi = (b == blocks - 1) ? n : lo + block_size;
+        uint32_t *h = local + b * nb;
+        for (int64_t i = lo; i < hi; ++i) h[(keys[i] >> start_bit) & mask]++;
+    }
+    for (int64_t b = 0; b < blocks; ++b)
+        for (uint32_t j = 0; j < nb; ++j) glob[j] += local[b * nb + j];
+    uint32_t sum = 0;
+    for (uint32_t j = 0; j < nb; ++j) { uint32_t x = glob[j]; glob[j] = sum; sum += x; }
+    oracle_block_offsets_u32(local, glob, final, blocks, nb);
+#pragma omp parallel for schedule(static)
+    for (int64_t b = 0; b < blocks; ++b) {
+        const int64_t lo = b * block_size, hi = (b == blocks - 1) ? n : lo + block_size;
+        uint32_t *o = final + b * nb;
+        for (int64_t i = lo; i < hi; ++i) out[o[(keys[i] >> start_bit) & mask]++] = keys[i];
+    }
+    free(local); free(final); free(glob);
+}
+
+/* radixSortParallel / radixSortSerial, radixsort.cpp:111-121 and :155-161: passes in pairs over
+ * startBit = 0, numBits, 2 numBits ... while the pair's first start bit is below 32; the result is in keys.
+ * block_size 0 = the serial pass, otherwise the blocked pass (the reference uses 8192, :115).
+ * A start bit of 32 or more is undefined in the reference (shift by >= width); here such a pass sees digit 0
+ * for every key, i.e. it copies. */
+ORACLE_API void oracle_radix_sort_u32(uint32_t *keys, uint32_t *tmp, int64_t n, uint32_t num_bits, int64_t block_size) {
+    for (uint32_t start = 0; start < 32; start += 2 * num_bits) {
+        for (int half = 0; half < 2; ++half) {
+            const uint32_t sb = start + (half ? num_bits : 0);
+            uint32_t *src = half ? tmp : keys, *dst = half ? keys : tmp;
+            if (sb >= 32) { memcpy(dst, src, (size_t)n * sizeof(uint32_t)); continue; }
+            if (block_size > 0) oracle_radix_pass_blocked_u32(src, dst, n, sb, num_bits, block_size);
+            else oracle_radix_pass_u32(src, dst, n, sb, num_bits);
+        }
+    }
+}
+
 /* ------------------------------------------------------------------------
  * Out-of-place transpose, M rows x N cols row-major -> N x M row-major.
  * Follows slides/Lecture06.pdf slide 9/20 line 10

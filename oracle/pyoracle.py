@@ -214,6 +214,45 @@ def radix_pass_u32(keys, start_bit, num_bits):
     return out
 
 
+def radix_pass_blocked_u32(keys, start_bit, num_bits, block_size=8192):
+    """radixSortParallelPass restated (radixsort.cpp:44-109)."""
+    keys = _c(keys, np.uint32)
+    out = np.empty_like(keys)
+    lib().oracle_radix_pass_blocked_u32(_p(keys), _p(out), C.c_int64(len(keys)), C.c_uint32(start_bit),
+                                        C.c_uint32(num_bits), C.c_int64(block_size))
+    return out
+
+
+def radix_sort_u32(keys, num_bits=8, block_size=8192):
+    """radixSortParallel (block_size > 0) / radixSortSerial (block_size 0) restated (radixsort.cpp:111-121, :155-161)."""
+    keys = _c(keys, np.uint32).copy()
+    tmp = np.empty_like(keys)
+    lib().oracle_radix_sort_u32(_p(keys), _p(tmp), C.c_int64(len(keys)), C.c_uint32(num_bits), C.c_int64(block_size))
+    return keys
+
+
+def ref_radix_pass(keys, start_bit, num_bits, block_size=8192):
+    """The reference's own radixSortParallelPass (block_size > 0) or radixSortSerialPass (0) from oracle/_ref."""
+    r = ref_lib("radixsort")
+    keys = _c(keys, np.uint32)
+    out = np.empty_like(keys)
+    if block_size:
+        r.ref_radix_pass_parallel(_p(keys), _p(out), C.c_long(len(keys)), C.c_uint(num_bits), C.c_uint(start_bit),
+                                  C.c_uint(block_size))
+    else:
+        r.ref_radix_pass_serial(_p(keys), _p(out), C.c_long(len(keys)), C.c_uint(num_bits), C.c_uint(start_bit))
+    return out
+
+
+def ref_radix_sort(keys, num_bits=8):
+    """The reference's parallel sort loop (radixsort.cpp:116-120) from oracle/_ref; returns (sorted, seconds)."""
+    r = ref_lib("radixsort")
+    r.ref_radix_sort_parallel.restype = C.c_double
+    keys = _c(keys, np.uint32).copy()
+    secs = r.ref_radix_sort_parallel(_p(keys), C.c_long(len(keys)), C.c_uint(num_bits))
+    return keys, secs
+
+
 def transpose(a, omp=False):
     a = np.ascontiguousarray(a)
     M, N = a.shape

@@ -56,6 +56,19 @@ def main():
              ell_val_colmajor=np.array([1, 2, 5, 6, 7, 8, 3, 4, 0, 0, 9, 0], np.float32),
              ell_idx_rows=np.array([[0, 1, -1], [1, 2, -1], [0, 2, 3], [1, 3, -1]], np.int32),
              coo_row=np.array([0, 0, 1, 1, 2, 2, 2, 3, 3], np.int32))
+    # 5. the reference's radix sort passes (hw/hw4/programming/radixsort.cpp) on 12 000 seeded keys: 31-bit values
+    #    like its rand() input (:172) with a low-entropy stretch so that stability matters
+    assert oracle.ref_lib("radixsort") is not None
+    rng = np.random.default_rng(2012)
+    keys = rng.integers(0, 2**31, 12000, dtype=np.int64).astype(np.uint32)
+    keys[3000:6000] = (keys[3000:6000] & 0x00030003) | 0x5A000000
+    p0 = oracle.ref_radix_pass(keys, 0, 8)
+    p1 = oracle.ref_radix_pass(p0, 8, 4, block_size=1000)
+    p2 = oracle.ref_radix_pass(keys, 13, 5, block_size=0)
+    s8, _ = oracle.ref_radix_sort(keys, 8)
+    s4, _ = oracle.ref_radix_sort(keys, 4)
+    np.savez_compressed(os.path.join(HERE, "radixsort_ref_n12000.npz"), keys=keys, pass_0_8=p0, pass_8_4_of_pass_0_8=p1,
+                        serial_pass_13_5=p2, sorted_bits8=s8, sorted_bits4=s4)
     print("golden vectors written to", HERE)
 
 
