@@ -12,6 +12,7 @@
 //                        in shared memory, then written out in runs (DOWNSWEEP 1, radixsort.cpp:99-109)
 // Algorithmic bytes per pass: 12 n (keys read twice, written once) + 8 * radix * n / 8192 for the table.
 #include "internal.cuh"
+#include <stdlib.h>
 
 using namespace cme213;
 
@@ -78,7 +79,23 @@ radix_hist_kernel(const uint32_t *__restrict__ keys, int64_t n, int start_bit, u
 constexpr int RS_START_PAD = 260;
 constexpr size_t RS_SCATTER_SMEM = (size_t)(RS_TILE + RS_WARPS * RS_BINS + RS_START_PAD + RS_MAX_RADIX) * 4;
 
-__global__ void __launch_bounds__(RS_THREADS, 3)
+// Lanes of the warp holding the same digit as this lane.  __match_any_sync would do it in one instruction, but
+// MATCH.ANY runs on the address-divergence unit at about one warp instruction per 64 cycles per SM and made the
+// kernel ADU-bound (91 % busy, 1.97 ms per pass, profiles/r01_ncu_radix_scatter_v1_match.txt); eight ballots and
+// sixteen logic operations are an order of magnitude cheaper.
+__device__ __forceinline__ uint32_t same_digit_lanes(uint32_t d) {
+    uint32_t peers = 0xFFFFFFFFu;
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+        const bool bit = (d >> b) & 1u;
+        const uint32_t vote = __ballot_sync(0xFFFFFFFFu, bit);
+        peers &= bit ? vote : ~vote;
+    }
+    return peers;
+}
+
+template <int MINB>
+__global__ void __launch_bounds__(RS_THREADS, MINB)
 radix_scatter_kernel(const uint32_t *__restrict__ keys_in, uint32_t *__restrict__ keys_out, int64_t n, int start_bit,
                      uint32_t mask, int radix, const uint32_t *__restrict__ table, int64_t pitch) {
     extern __shared__ __align__(16) uint32_t rs_smem[];
@@ -89,6 +106,7 @@ radix_scatter_kernel(const uint32_t *__restrict__ keys_in, uint32_t *__restrict_
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t base = (int64_t)blockIdx.x * RS_TILE;
     const int cnt = (int)((n - base) < RS_TILE ? (n - base) : RS_TILE);
+    const bool full = cnt == RS_TILE;
     const uint32_t tofs = tid < radix ? table[(int64_t)tid * pitch + blockIdx.x] : 0u;
 
     const int wbase = warp * 32 * RS_ITEMS + lane;
@@ -106,9 +124,13 @@ radix_scatter_kernel(const uint32_t *__restrict__ keys_in, uint32_t *__restrict_
     uint32_t rank2[RS_ITEMS / 2];   // two 16-bit ranks per register (a warp holds 512 keys)
 #pragma unroll
     for (int i = 0; i < RS_ITEMS; ++i) {
-        const int li = wbase + i * 32;
-        const uint32_t d = li < cnt ? ((key[i] >> start_bit) & mask) : (uint32_t)radix;
-        const uint32_t peers = __match_any_sync(0xFFFFFFFFu, d);
+        const bool valid = full || (wbase + i * 32 < cnt);
+        const uint32_t d = valid ? ((key[i] >> start_bit) & mask) : (uint32_t)radix;   // slots past the end: bin `radix`
+        uint32_t peers = same_digit_lanes(d);
+        if (!full) {   // uniform branch; keeps bin 256 apart from digit 0 (bit 8 is not among the ballots)
+            const uint32_t v = __ballot_sync(0xFFFFFFFFu, valid);
+            peers &= valid ? v : ~v;
+        }
         const int leader = __ffs(peers) - 1;
         uint32_t old = 0;
         if (lane == leader) { old = wh[d]; wh[d] = old + __popc(peers); }
@@ -119,14 +141,10 @@ radix_scatter_kernel(const uint32_t *__restrict__ keys_in, uint32_t *__restrict_
     }
     __syncthreads();
 
-    if (tid < RS_BINS) {            // counters -> exclusive over the warps; the total is the block's count
+    if (tid < RS_BINS) {            // the block's count of each digit
         uint32_t sum = 0;
 #pragma unroll
-        for (int w = 0; w < RS_WARPS; ++w) {
-            const uint32_t c = s_wh[w * RS_BINS + tid];
-            s_wh[w * RS_BINS + tid] = sum;
-            sum += c;
-        }
+        for (int w = 0; w < RS_WARPS; ++w) sum += s_wh[w * RS_BINS + tid];
         s_start[tid] = sum;
     }
     __syncthreads();
@@ -154,13 +172,23 @@ radix_scatter_kernel(const uint32_t *__restrict__ keys_in, uint32_t *__restrict_
         }
     }
     __syncthreads();
-    if (tid < radix) s_gofs[tid] = tofs - s_start[tid];
+    if (tid < RS_BINS) {            // counters -> first slot of (warp, digit) inside the regrouped block
+        uint32_t run = s_start[tid];
+        if (tid < radix) s_gofs[tid] = tofs - run;
+#pragma unroll
+        for (int w = 0; w < RS_WARPS; ++w) {
+            const uint32_t c = s_wh[w * RS_BINS + tid];
+            s_wh[w * RS_BINS + tid] = run;
+            run += c;
+        }
+    }
+    __syncthreads();
 #pragma unroll
     for (int i = 0; i < RS_ITEMS; ++i) {
-        const int li = wbase + i * 32;
-        const uint32_t d = li < cnt ? ((key[i] >> start_bit) & mask) : (uint32_t)radix;
+        const bool valid = full || (wbase + i * 32 < cnt);
+        const uint32_t d = valid ? ((key[i] >> start_bit) & mask) : (uint32_t)radix;
         const uint32_t r = (i & 1) ? (rank2[i >> 1] >> 16) : (rank2[i >> 1] & 0xFFFFu);
-        s_keys[s_start[d] + wh[d] + r] = key[i];
+        s_keys[wh[d] + r] = key[i];
     }
     __syncthreads();
 #pragma unroll 4
@@ -190,9 +218,6 @@ PassPlan plan_pass(int64_t n) {
 // One pass with the workspace already in hand.
 int run_pass(cme213_ctx *ctx, const uint32_t *d_in, uint32_t *d_out, int64_t n, int start_bit, int num_bits,
              const PassPlan &p, void *ws, cudaStream_t st) {
-    // per device and cheap: set on every call rather than tracked
-    CME213_CUDA(cudaFuncSetAttribute(radix_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)RS_SCATTER_SMEM));
     const int radix = 1 << num_bits;
     const uint32_t mask = (uint32_t)radix - 1u;
     uint32_t *table = (uint32_t *)ws;
@@ -202,8 +227,11 @@ int run_pass(cme213_ctx *ctx, const uint32_t *d_in, uint32_t *d_out, int64_t n, 
     CME213_LAUNCHED(ctx, "radix_hist_kernel");
     int rc = cme213_internal_exclusive_scan_u32(ctx, table, table, p.pitch * radix, scratch, st);
     if (rc) return rc;
-    radix_scatter_kernel<<<(unsigned)p.blocks, RS_THREADS, RS_SCATTER_SMEM, st>>>(d_in, d_out, n, start_bit, mask, radix,
-                                                                                table, p.pitch);
+    static const int minb = [] { const char *e = getenv("CME213_RS_MINB"); return e ? atoi(e) : 3; }();   // tuning hook
+    auto kern = minb == 2 ? radix_scatter_kernel<2> : radix_scatter_kernel<3>;
+    // per device and cheap: set on every call rather than tracked
+    CME213_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RS_SCATTER_SMEM));
+    kern<<<(unsigned)p.blocks, RS_THREADS, RS_SCATTER_SMEM, st>>>(d_in, d_out, n, start_bit, mask, radix, table, p.pitch);
     CME213_LAUNCHED(ctx, "radix_scatter_kernel");
     return CME213_OK;
 }
