@@ -79,21 +79,11 @@ radix_hist_kernel(const uint32_t *__restrict__ keys, int64_t n, int start_bit, u
 constexpr int RS_START_PAD = 260;
 constexpr size_t RS_SCATTER_SMEM = (size_t)(RS_TILE + RS_WARPS * RS_BINS + RS_START_PAD + RS_MAX_RADIX) * 4;
 
-// Lanes of the warp holding the same digit as this lane.  __match_any_sync would do it in one instruction, but
-// MATCH.ANY runs on the address-divergence unit at about one warp instruction per 64 cycles per SM and made the
-// kernel ADU-bound (91 % busy, 1.97 ms per pass, profiles/r01_ncu_radix_scatter_v1_match.txt); eight ballots and
-// sixteen logic operations are an order of magnitude cheaper.
-__device__ __forceinline__ uint32_t same_digit_lanes(uint32_t d) {
-    uint32_t peers = 0xFFFFFFFFu;
-#pragma unroll
-    for (int b = 0; b < 8; ++b) {
-        const bool bit = (d >> b) & 1u;
-        const uint32_t vote = __ballot_sync(0xFFFFFFFFu, bit);
-        peers &= bit ? vote : ~vote;
-    }
-    return peers;
-}
-
+// Finding the lanes of the warp that hold the same digit: __match_any_sync is one instruction, but MATCH.ANY runs
+// on the address-divergence unit at about one warp instruction per 64 cycles per SM (kernel 91 % ADU-bound,
+// 1.97 ms per pass, profiles/r01_ncu_radix_scatter_v1_match.txt); eight ballots + selects made it ALU-bound
+// (85 %, 1.27 ms, profiles/r01_ncu_radix_scatter_v2_ballot.txt).  Here every lane ORs its bit into a per-warp,
+// per-digit word in shared memory and reads the word back: two LSU instructions.
 template <int MINB>
 __global__ void __launch_bounds__(RS_THREADS, MINB)
 radix_scatter_kernel(const uint32_t *__restrict__ keys_in, uint32_t *__restrict__ keys_out, int64_t n, int start_bit,
@@ -116,24 +106,24 @@ radix_scatter_kernel(const uint32_t *__restrict__ keys_in, uint32_t *__restrict_
         const int li = wbase + i * 32;
         key[i] = li < cnt ? ld_stream(keys_in + base + li) : 0xFFFFFFFFu;
     }
-    for (int i = tid; i < RS_WARPS * RS_BINS; i += RS_THREADS) s_wh[i] = 0;
+    for (int i = tid; i < RS_WARPS * RS_BINS; i += RS_THREADS) { s_wh[i] = 0; s_keys[i] = 0; }
     __syncthreads();
 
     uint32_t *wh = s_wh + warp * RS_BINS;
-    const uint32_t lt = (1u << lane) - 1u;
+    uint32_t *mm = s_keys + warp * RS_BINS;   // match words; s_keys is not needed as key storage until the regroup
+    const uint32_t me = 1u << lane, lt = me - 1u;
     uint32_t rank2[RS_ITEMS / 2];   // two 16-bit ranks per register (a warp holds 512 keys)
 #pragma unroll
     for (int i = 0; i < RS_ITEMS; ++i) {
         const bool valid = full || (wbase + i * 32 < cnt);
         const uint32_t d = valid ? ((key[i] >> start_bit) & mask) : (uint32_t)radix;   // slots past the end: bin `radix`
-        uint32_t peers = same_digit_lanes(d);
-        if (!full) {   // uniform branch; keeps bin 256 apart from digit 0 (bit 8 is not among the ballots)
-            const uint32_t v = __ballot_sync(0xFFFFFFFFu, valid);
-            peers &= valid ? v : ~v;
-        }
-        const int leader = __ffs(peers) - 1;
+        atomicOr(&mm[d], me);
+        __syncwarp();
+        const uint32_t peers = mm[d];
+        __syncwarp();
+        const int leader = 31 - __clz(peers);
         uint32_t old = 0;
-        if (lane == leader) { old = wh[d]; wh[d] = old + __popc(peers); }
+        if (lane == leader) { mm[d] = 0; old = wh[d]; wh[d] = old + __popc(peers); }
         old = __shfl_sync(0xFFFFFFFFu, old, leader);
         const uint32_t r = old + __popc(peers & lt);
         if (i & 1) rank2[i >> 1] |= r << 16; else rank2[i >> 1] = r;
@@ -227,7 +217,7 @@ int run_pass(cme213_ctx *ctx, const uint32_t *d_in, uint32_t *d_out, int64_t n, 
     CME213_LAUNCHED(ctx, "radix_hist_kernel");
     int rc = cme213_internal_exclusive_scan_u32(ctx, table, table, p.pitch * radix, scratch, st);
     if (rc) return rc;
-    static const int minb = [] { const char *e = getenv("CME213_RS_MINB"); return e ? atoi(e) : 3; }();   // tuning hook
+    static const int minb = [] { const char *e = getenv("CME213_RS_MINB"); return e ? atoi(e) : 2; }();   // tuning hook
     auto kern = minb == 2 ? radix_scatter_kernel<2> : radix_scatter_kernel<3>;
     // per device and cheap: set on every call rather than tracked
     CME213_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RS_SCATTER_SMEM));
