@@ -75,6 +75,11 @@ PROTOTYPES = {
     "cme213_csr_to_ell_f64": (_i, [_p, _i64, _i64, _p, _p, _p, _i, _i64, _p, _p, _p]),
     "cme213_csr_to_coo_tail_f32": (_i, [_p, _i64, _p, _p, _p, _i, _pi64, _p, _p, _p, _p]),
     "cme213_csr_to_coo_tail_f64": (_i, [_p, _i64, _p, _p, _p, _i, _pi64, _p, _p, _p, _p]),
+    "cme213_spmv_dia_f32": (_i, [_p, _i64, _i64, _i64, _i, _p, _p, _p, _p, _p]),
+    "cme213_spmv_dia_f64": (_i, [_p, _i64, _i64, _i64, _i, _p, _p, _p, _p, _p]),
+    "cme213_csr_diagonals": (_i, [_p, _i64, _i64, _p, _p, _i, _p, _pi, _p]),
+    "cme213_csr_to_dia_f32": (_i, [_p, _i64, _p, _p, _p, _i, _p, _i64, _p, _pi64, _p]),
+    "cme213_csr_to_dia_f64": (_i, [_p, _i64, _p, _p, _p, _i, _p, _i64, _p, _pi64, _p]),
     "cme213_block_offsets_u32": (_i, [_p, _p, _p, _p, _i64, _i64, _p]),
     "cme213_radix_sort_pass_u32": (_i, [_p, _p, _p, _i64, _i, _i, _p]),
     "cme213_radix_sort_u32": (_i, [_p, _p, _p, _i64, _i, _p]),

@@ -1,0 +1,273 @@
+// spmv_dia.cu -- DIA (diagonal) sparse matrix-vector multiply and the CSR -> DIA conversion.
+//
+// Format and kernel semantics: refs/Bell SC 2009.pdf p.3 Fig. 1/3 and section 3.1; Bell TR 2008 Fig. 15
+// (spmv_dia_kernel: data[pitch*n + row], col = row + offsets[n], in-range test); slides/Lecture22.pdf slide 29.
+// The operator of configs C1 / C5 is a stencil (hw/hw2/programming/2dHeat.cu:361-366 is its 2-D order-2 form), so
+// DIA is the format bound for them: 8 (fp64) or 4 (fp32) bytes per stored entry against 12 / 8 for CSR
+// (SC09 Table 1).
+//
+// B200 shape: as in the ELL kernel a thread owns FOUR consecutive rows, so its loads from the diagonal-major
+// array are 128-bit and a warp covers 512 contiguous bytes (fp32) per diagonal; x is read with 128-bit loads
+// when the diagonal's offset keeps the four elements 16-byte aligned (every diagonal of a grid whose line length
+// is a multiple of 4 except the +-1 ones), scalar loads otherwise.  Zero entries (padding outside the matrix and
+// missing stencil legs at the grid boundary) are skipped, and the sum runs in diagonal order with rounded multiply
+// and add: for a CSR matrix with ascending columns that is the CSR row loop's order, hence bit-identical results.
+#include "internal.cuh"
+
+namespace {
+using namespace cme213;
+
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ double add_rn(double a, double b) { return __dadd_rn(a, b); }
+
+__device__ __forceinline__ void load4_stream(const float *p, float (&v)[4]) {
+    const float4 t = ld_stream(reinterpret_cast<const float4 *>(p));
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+}
+__device__ __forceinline__ void load4_stream(const double *p, double (&v)[4]) {
+    const double2 t0 = ld_stream(reinterpret_cast<const double2 *>(p));
+    const double2 t1 = ld_stream(reinterpret_cast<const double2 *>(p) + 1);
+    v[0] = t0.x; v[1] = t0.y; v[2] = t1.x; v[3] = t1.y;
+}
+__device__ __forceinline__ void load4_cached(const float *p, float (&v)[4]) {
+    const float4 t = __ldg(reinterpret_cast<const float4 *>(p));
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+}
+__device__ __forceinline__ void load4_cached(const double *p, double (&v)[4]) {
+    const double2 t0 = __ldg(reinterpret_cast<const double2 *>(p));
+    const double2 t1 = __ldg(reinterpret_cast<const double2 *>(p) + 1);
+    v[0] = t0.x; v[1] = t0.y; v[2] = t1.x; v[3] = t1.y;
+}
+
+// One diagonal's contribution to the four rows r4 .. r4+3.
+template <typename T>
+__device__ __forceinline__ void dia_accumulate(const T (&v)[4], int64_t c0, int64_t num_cols, const T *__restrict__ x,
+                                               bool x_vec_ok, T (&s)[4]) {
+    // four elements of 4 bytes (or two pairs of 8 bytes) at a multiple of 4 elements from an aligned base
+    constexpr int64_t AL = sizeof(T) == 4 ? 3 : 1;   // 16-byte alignment of x + c0 in elements
+    if (x_vec_ok && (c0 & AL) == 0 && c0 >= 0 && c0 + 3 < num_cols) {
+        T xv[4];
+        load4_cached(x + c0, xv);
+#pragma unroll
+        for (int t = 0; t < 4; ++t)
+            if (v[t] != T(0)) s[t] = add_rn(s[t], mul_rn(v[t], xv[t]));
+    } else {
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const int64_t c = c0 + t;
+            if (v[t] != T(0) && c >= 0 && c < num_cols) s[t] = add_rn(s[t], mul_rn(v[t], __ldg(x + c)));
+        }
+    }
+}
+
+template <typename T, int UNROLL>
+__global__ void __launch_bounds__(256)
+dia_v4_kernel(int64_t num_rows, int64_t num_cols, int64_t pitch, int num_diags, const int32_t *__restrict__ offsets,
+              const T *__restrict__ data, const T *__restrict__ x, T *__restrict__ y, int x_vec_ok, int y_vec_ok) {
+    const int64_t r4 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (r4 >= num_rows) return;
+    T s[4] = {T(0), T(0), T(0), T(0)};
+    const T *dp = data + r4;
+    int n = 0;
+    for (; n + UNROLL <= num_diags; n += UNROLL) {
+        T v[UNROLL][4];
+        int32_t off[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+            load4_stream(dp + (int64_t)(n + u) * pitch, v[u]);
+            off[u] = __ldg(offsets + n + u);
+        }
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) dia_accumulate(v[u], r4 + off[u], num_cols, x, x_vec_ok != 0, s);
+    }
+    for (; n < num_diags; ++n) {
+        T v[4];
+        load4_stream(dp + (int64_t)n * pitch, v);
+        dia_accumulate(v, r4 + __ldg(offsets + n), num_cols, x, x_vec_ok != 0, s);
+    }
+    if (r4 + 3 < num_rows && y_vec_ok) {
+        if (sizeof(T) == 4) {
+            st_stream(reinterpret_cast<float4 *>(y + r4), make_float4((float)s[0], (float)s[1], (float)s[2], (float)s[3]));
+        } else {
+            st_stream(reinterpret_cast<double2 *>(y + r4), make_double2((double)s[0], (double)s[1]));
+            st_stream(reinterpret_cast<double2 *>(y + r4) + 1, make_double2((double)s[2], (double)s[3]));
+        }
+    } else {
+#pragma unroll
+        for (int t = 0; t < 4; ++t)
+            if (r4 + t < num_rows) y[r4 + t] = s[t];
+    }
+}
+
+// Any pitch / alignment: one row per thread (Bell TR Fig. 15 as written, plus the zero skip).
+template <typename T>
+__global__ void __launch_bounds__(256)
+dia_scalar_kernel(int64_t num_rows, int64_t num_cols, int64_t pitch, int num_diags, const int32_t *__restrict__ offsets,
+                  const T *__restrict__ data, const T *__restrict__ x, T *__restrict__ y) {
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= num_rows) return;
+    T s = T(0);
+    for (int n = 0; n < num_diags; ++n) {
+        const int64_t c = r + offsets[n];
+        const T v = data[(int64_t)n * pitch + r];
+        if (v != T(0) && c >= 0 && c < num_cols) s = add_rn(s, mul_rn(v, __ldg(x + c)));
+    }
+    y[r] = s;
+}
+
+// ---- CSR -> DIA -----------------------------------------------------------------------------------------
+// Position of `off` in the ascending list, or -1.
+__device__ __forceinline__ int find_offset(const int32_t *__restrict__ offsets, int num_diags, int32_t off) {
+    int lo = 0, hi = num_diags - 1;
+    while (lo <= hi) {
+        const int mid = (lo + hi) >> 1;
+        const int32_t o = __ldg(offsets + mid);
+        if (o == off) return mid;
+        if (o < off) lo = mid + 1; else hi = mid - 1;
+    }
+    return -1;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+csr_to_dia_kernel(int64_t num_rows, const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
+                  const T *__restrict__ val, int num_diags, const int32_t *__restrict__ offsets, int64_t pitch,
+                  T *__restrict__ data, unsigned long long *unmatched) {
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= num_rows) return;
+    unsigned long long miss = 0;
+    for (int32_t e = row_ptr[r]; e < row_ptr[r + 1]; ++e) {
+        const int n = find_offset(offsets, num_diags, (int32_t)(col[e] - r));
+        if (n < 0) ++miss; else data[(int64_t)n * pitch + r] = val[e];
+    }
+    if (miss) atomicAdd(unmatched, miss);
+}
+
+// Which diagonals hold an entry: mark[(col - row) + (num_rows - 1)] = 1.
+__global__ void __launch_bounds__(256)
+mark_diagonals_kernel(int64_t num_rows, const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
+                      uint32_t *__restrict__ mark) {
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= num_rows) return;
+    for (int32_t e = row_ptr[r]; e < row_ptr[r + 1]; ++e) mark[(int64_t)col[e] - r + (num_rows - 1)] = 1u;
+}
+// Stream compaction on the scan (slides/Lecture16.pdf slides 3-13): marked slot i goes to out[excl[i]].
+__global__ void __launch_bounds__(256)
+compact_diagonals_kernel(int64_t slots, int64_t num_rows, const uint32_t *__restrict__ mark,
+                         const uint32_t *__restrict__ excl, int32_t *__restrict__ out, int max_out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= slots) return;
+    if (mark[i] && excl[i] < (uint32_t)max_out) out[excl[i]] = (int32_t)(i - (num_rows - 1));
+}
+
+template <typename T>
+int dia_impl(cme213_ctx *ctx, int64_t num_rows, int64_t num_cols, int64_t pitch, int num_diags,
+             const int32_t *d_offsets, const T *d_data, const T *d_x, T *d_y, void *stream) {
+    CME213_CHECK_CTX(ctx);
+    if (num_rows < 0 || num_cols < 0 || num_diags < 0 || pitch < num_rows) { set_error("spmv_dia: bad shape"); return CME213_ERR_INVALID; }
+    if (num_rows == 0) return CME213_OK;
+    if (!d_y || (num_diags > 0 && (!d_offsets || !d_data || !d_x))) { set_error("spmv_dia: null pointer"); return CME213_ERR_INVALID; }
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool vec_ok = pitch % 4 == 0 && pitch >= ((num_rows + 3) & ~(int64_t)3) && aligned16(d_data);
+    if (vec_ok) {
+        const int64_t blocks = div_up(div_up(num_rows, 4), 256);
+        dia_v4_kernel<T, 4><<<(unsigned)blocks, 256, 0, st>>>(num_rows, num_cols, pitch, num_diags, d_offsets, d_data, d_x,
+                                                             d_y, aligned16(d_x) ? 1 : 0, aligned16(d_y) ? 1 : 0);
+        CME213_LAUNCHED(ctx, "dia_v4_kernel");
+    } else {
+        dia_scalar_kernel<T><<<(unsigned)div_up(num_rows, 256), 256, 0, st>>>(num_rows, num_cols, pitch, num_diags,
+                                                                             d_offsets, d_data, d_x, d_y);
+        CME213_LAUNCHED(ctx, "dia_scalar_kernel");
+    }
+    return CME213_OK;
+}
+
+template <typename T>
+int csr_to_dia_impl(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr, const int32_t *d_col, const T *d_val,
+                    int num_diags, const int32_t *d_offsets, int64_t pitch, T *d_data, int64_t *unmatched_out,
+                    void *stream) {
+    CME213_CHECK_CTX(ctx);
+    if (unmatched_out) *unmatched_out = 0;
+    if (num_rows < 0 || num_diags < 0 || pitch < num_rows) { set_error("csr_to_dia: bad shape"); return CME213_ERR_INVALID; }
+    if (num_rows == 0 || num_diags == 0) return CME213_OK;
+    if (!d_row_ptr || !d_col || !d_val || !d_offsets || !d_data) { set_error("csr_to_dia: null pointer"); return CME213_ERR_INVALID; }
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    void *ws = nullptr;
+    int rc = workspace(ctx, 256, &ws);
+    if (rc) return rc;
+    unsigned long long *d_miss = (unsigned long long *)ws;
+    CME213_CUDA(cudaMemsetAsync(d_miss, 0, 8, st));
+    CME213_CUDA(cudaMemsetAsync(d_data, 0, (size_t)num_diags * (size_t)pitch * sizeof(T), st));
+    csr_to_dia_kernel<T><<<(unsigned)div_up(num_rows, 256), 256, 0, st>>>(num_rows, d_row_ptr, d_col, d_val, num_diags,
+                                                                         d_offsets, pitch, d_data, d_miss);
+    CME213_LAUNCHED(ctx, "csr_to_dia_kernel");
+    if (unmatched_out) {
+        unsigned long long miss = 0;
+        CME213_CUDA(cudaMemcpyAsync(&miss, d_miss, 8, cudaMemcpyDeviceToHost, st));
+        CME213_CUDA(cudaStreamSynchronize(st));
+        *unmatched_out = (int64_t)miss;
+    }
+    return CME213_OK;
+}
+}  // namespace
+
+CME213_API int cme213_spmv_dia_f32(cme213_ctx *ctx, int64_t num_rows, int64_t num_cols, int64_t pitch, int num_diags,
+                                   const int32_t *d_offsets, const float *d_data, const float *d_x, float *d_y,
+                                   void *stream) {
+    return dia_impl<float>(ctx, num_rows, num_cols, pitch, num_diags, d_offsets, d_data, d_x, d_y, stream);
+}
+CME213_API int cme213_spmv_dia_f64(cme213_ctx *ctx, int64_t num_rows, int64_t num_cols, int64_t pitch, int num_diags,
+                                   const int32_t *d_offsets, const double *d_data, const double *d_x, double *d_y,
+                                   void *stream) {
+    return dia_impl<double>(ctx, num_rows, num_cols, pitch, num_diags, d_offsets, d_data, d_x, d_y, stream);
+}
+CME213_API int cme213_csr_to_dia_f32(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr, const int32_t *d_col,
+                                     const float *d_val, int num_diags, const int32_t *d_offsets, int64_t pitch,
+                                     float *d_data, int64_t *unmatched_out, void *stream) {
+    return csr_to_dia_impl<float>(ctx, num_rows, d_row_ptr, d_col, d_val, num_diags, d_offsets, pitch, d_data,
+                                  unmatched_out, stream);
+}
+CME213_API int cme213_csr_to_dia_f64(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr, const int32_t *d_col,
+                                     const double *d_val, int num_diags, const int32_t *d_offsets, int64_t pitch,
+                                     double *d_data, int64_t *unmatched_out, void *stream) {
+    return csr_to_dia_impl<double>(ctx, num_rows, d_row_ptr, d_col, d_val, num_diags, d_offsets, pitch, d_data,
+                                   unmatched_out, stream);
+}
+
+CME213_API int cme213_csr_diagonals(cme213_ctx *ctx, int64_t num_rows, int64_t num_cols, const int32_t *d_row_ptr,
+                                    const int32_t *d_col, int max_diags, int32_t *d_offsets_out, int *num_diags_out,
+                                    void *stream) {
+    CME213_CHECK_CTX(ctx);
+    if (!num_diags_out) { set_error("csr_diagonals: null count pointer"); return CME213_ERR_INVALID; }
+    *num_diags_out = 0;
+    if (num_rows < 0 || num_cols < 0 || max_diags < 0) { set_error("csr_diagonals: bad shape"); return CME213_ERR_INVALID; }
+    if (num_rows == 0 || num_cols == 0) return CME213_OK;
+    if (!d_row_ptr || !d_col || (max_diags > 0 && !d_offsets_out)) { set_error("csr_diagonals: null pointer"); return CME213_ERR_INVALID; }
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t slots = num_rows + num_cols - 1;
+    const size_t a_bytes = ((size_t)(slots + 1) * 4 + 255) & ~(size_t)255;   // one extra slot: its scan value is the count
+    void *ws = nullptr;
+    int rc = workspace(ctx, 2 * a_bytes + cme213_internal_scan_u32_scratch_bytes(slots + 1), &ws);
+    if (rc) return rc;
+    uint32_t *mark = (uint32_t *)ws, *excl = (uint32_t *)((char *)ws + a_bytes);
+    void *scratch = (char *)ws + 2 * a_bytes;
+    CME213_CUDA(cudaMemsetAsync(mark, 0, a_bytes, st));
+    mark_diagonals_kernel<<<(unsigned)div_up(num_rows, 256), 256, 0, st>>>(num_rows, d_row_ptr, d_col, mark);
+    CME213_LAUNCHED(ctx, "mark_diagonals_kernel");
+    rc = cme213_internal_exclusive_scan_u32(ctx, mark, excl, slots + 1, scratch, st);
+    if (rc) return rc;
+    if (max_diags > 0) {
+        compact_diagonals_kernel<<<(unsigned)div_up(slots, 256), 256, 0, st>>>(slots, num_rows, mark, excl, d_offsets_out, max_diags);
+        CME213_LAUNCHED(ctx, "compact_diagonals_kernel");
+    }
+    uint32_t count = 0;
+    CME213_CUDA(cudaMemcpyAsync(&count, excl + slots, 4, cudaMemcpyDeviceToHost, st));
+    CME213_CUDA(cudaStreamSynchronize(st));
+    *num_diags_out = (int)count;
+    return CME213_OK;
+}

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- measures the hot path on B200 (see DESIGN.md "Measurement").
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c5|c1|scan|segscan|radixsort|fp|transpose32|
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c5|c1|scan|segscan|radixsort|dia|fp|transpose32|
                      transpose64|ell|hyb|csr_powerlaw|pagerank] [--impl ours|reference] [--extras 0|1]
 
 Default workload = BASELINE.json config C5: row-sharded CSR SpMV iteration on the 3-D 7-point
@@ -248,6 +248,47 @@ def make_radixsort(ctx, torch, args):
                       "l2": "1.07 GB of keys >> L2"}, keep=(x, a, b))
 
 
+def make_dia(ctx, torch, args):
+    # 8f.4: config C5's operator (3-D 7-point Laplacian, fp64) in DIA, converted on the device from the CSR arrays
+    import ctypes as C
+    pkg = importlib.import_module(PKG)
+    g = args.grid
+    rows = g * g * g
+    nnz = C.c_int64()
+    d_ptr = i32(rows + 1, torch)
+    ctx.call("cme213_gen_laplace3d_f64", g, g, g, 0, rows, d_ptr, None, None, C.byref(nnz))
+    d_col = i32(nnz.value, torch)
+    d_val = torch.empty(nnz.value, dtype=torch.float64, device="cuda")
+    ctx.call("cme213_gen_laplace3d_f64", g, g, g, 0, rows, d_ptr, d_col, d_val, C.byref(nnz))
+    d_off = i32(16, torch)
+    nd = C.c_int()
+    ctx.call("cme213_csr_diagonals", rows, rows, d_ptr, d_col, 16, d_off, C.byref(nd))
+    pitch = int(pkg.load().cme213_ell_pitch(rows))
+    d_dat = torch.empty(nd.value * pitch, dtype=torch.float64, device="cuda")
+    miss = C.c_int64()
+    ctx.call("cme213_csr_to_dia_f64", rows, d_ptr, d_col, d_val, nd.value, d_off, pitch, d_dat, C.byref(miss))
+    assert miss.value == 0 and nd.value == 7
+    del d_ptr, d_col, d_val
+    torch.cuda.empty_cache()
+    xa = torch.empty(rows, dtype=torch.float64, device="cuda")
+    xb = torch.empty_like(xa)
+    ctx.call("cme213_fill_uniform_f64", xa, rows, 9)
+    xa.mul_(0.05)
+    state = {"src": 0}
+
+    def step():
+        a, b = (xa, xb) if state["src"] == 0 else (xb, xa)
+        ctx.call("cme213_spmv_dia_f64", rows, rows, pitch, 7, d_off, d_dat, a, b, stream=torch.cuda.current_stream())
+        state["src"] = 1 - state["src"]
+
+    csr_bytes = nnz.value * 12 + (rows + 1) * 4 + rows * 16
+    return dict(step=step, alg_bytes=7 * rows * 8 + rows * 16, flops=2 * nnz.value, kernel="dia_v4_kernel<double>",
+                launches_per_step=1,
+                meta={"workload": "8f.4: C5's operator in DIA (7 diagonals, fp64, %d^3 grid): 72 B per row against CSR's 104" % g,
+                      "rows": rows, "csr_bytes_for_the_same_product": csr_bytes, "l2": "9.7 GB per pass >> L2"},
+                keep=(d_off, d_dat, xa, xb))
+
+
 def make_segscan(ctx, torch, args):
     n = 1 << 28
     v = torch.empty(n, dtype=torch.float32, device="cuda")
@@ -393,6 +434,8 @@ def build_workload(name, ctx, torch, args, rank=0, world=1, dist=None):
         return make_segscan(ctx, torch, args)
     if name == "radixsort":
         return make_radixsort(ctx, torch, args)
+    if name == "dia":
+        return make_dia(ctx, torch, args)
     if name == "fp":
         return make_fp(ctx, torch, args)
     if name == "transpose32":
@@ -717,7 +760,7 @@ def main():
         others = []
         del wl
         torch.cuda.empty_cache()
-        names = ["scan", "segscan", "radixsort", "fp", "transpose32", "transpose64", "c1", "ell", "hyb", "csr_powerlaw",
+        names = ["scan", "segscan", "radixsort", "dia", "fp", "transpose32", "transpose64", "c1", "ell", "hyb", "csr_powerlaw",
                  "ell_window", "hyb_window", "csr_window", "ell_regular_window", "csr_regular_window", "pagerank"]
         for name in names:
             try:

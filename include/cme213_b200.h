@@ -223,6 +223,32 @@ int cme213_csr_to_coo_tail_f64(cme213_ctx *ctx, int64_t num_rows, const int32_t 
                                const double *d_val, int K, int64_t *tail_nnz_out, int32_t *d_coo_row,
                                int32_t *d_coo_col, double *d_coo_val, void *stream);
 
+/* ---- DIA (the format bound for the stencil operators of C1 / C5) --------------------------- */
+/* y = A x, A in DIA: d_data[n * pitch + r] is the entry of row r on diagonal d_offsets[n] (column r + offset),
+ * zero where there is none; offsets ascending.  Zero entries are skipped and the sum runs in diagonal order
+ * with rounded multiply and add, so for a CSR matrix with ascending columns the result is bit-identical to
+ * cme213_spmv_csr_* (CME213_CSR_STREAM / SCALAR).  pitch >= num_rows; a pitch that is a multiple of 4 with
+ * 16-byte aligned d_data takes the 128-bit path (cme213_ell_pitch() gives one).
+ * reference: refs/Bell SC 2009.pdf section 3.1, Fig. 1/3; refs/Bell Tech Report 2008.pdf Fig. 15
+ * (spmv_dia_kernel); slides/Lecture22.pdf slide 29; the stencil itself: hw/hw2/programming/2dHeat.cu:361-366. */
+int cme213_spmv_dia_f32(cme213_ctx *ctx, int64_t num_rows, int64_t num_cols, int64_t pitch, int num_diags,
+                        const int32_t *d_offsets, const float *d_data, const float *d_x, float *d_y, void *stream);
+int cme213_spmv_dia_f64(cme213_ctx *ctx, int64_t num_rows, int64_t num_cols, int64_t pitch, int num_diags,
+                        const int32_t *d_offsets, const double *d_data, const double *d_x, double *d_y, void *stream);
+/* The occupied diagonals (col - row) of a CSR matrix, ascending, by mark + exclusive scan + compaction
+ * (slides/Lecture16.pdf slides 3-13).  *num_diags_out = how many there are (synchronises); at most max_diags of
+ * them are written to d_offsets_out.  Scratch: 8 bytes per (num_rows + num_cols) in the context workspace. */
+int cme213_csr_diagonals(cme213_ctx *ctx, int64_t num_rows, int64_t num_cols, const int32_t *d_row_ptr,
+                         const int32_t *d_col, int max_diags, int32_t *d_offsets_out, int *num_diags_out, void *stream);
+/* CSR -> DIA on the ascending offsets list d_offsets (num_diags * pitch elements are written, zero-filled).
+ * *unmatched_out (may be NULL; non-NULL synchronises) = entries that lie on none of the listed diagonals. */
+int cme213_csr_to_dia_f32(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr, const int32_t *d_col,
+                          const float *d_val, int num_diags, const int32_t *d_offsets, int64_t pitch, float *d_data,
+                          int64_t *unmatched_out, void *stream);
+int cme213_csr_to_dia_f64(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr, const int32_t *d_col,
+                          const double *d_val, int num_diags, const int32_t *d_offsets, int64_t pitch, double *d_data,
+                          int64_t *unmatched_out, void *stream);
+
 /* Scatter offsets of a blocked LSD radix pass: out[i][j] = global_excl[j] + sum of local[i'][j] over blocks i' < i
  * (arrays [num_blocks x num_buckets], row-major).  Transpose + one segmented exclusive scan + transpose.
  * reference: hw/hw4/programming/radixsort.cpp:85-97 (local_histogram_final). */

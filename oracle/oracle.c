@@ -422,6 +422,61 @@ DEFINE_TRANSPOSE_OMP(oracle_transpose_b64_omp, uint64_t)
 DEFINE_ELL_SPMV(oracle_ell_spmv_f32, float)
 DEFINE_ELL_SPMV(oracle_ell_spmv_f64, double)
 
+/* ------------------------------------------------------------------------
+ * DIA: data[pitch * n + row] holds the entry of `row` on diagonal offsets[n]
+ * (column = row + offsets[n]), zero where the matrix has none.  Follows
+ * spmv_dia_kernel, Bell TR 2008 Fig. 15 / Bell & Garland SC09 section 3.1,
+ * with the same "skip val == 0" as the ELL kernel so padding never touches x.
+ * ---------------------------------------------------------------------- */
+#define DEFINE_DIA_SPMV(NAME, T)                                                                      \
+    ORACLE_API void NAME(int64_t num_rows, int64_t num_cols, int64_t pitch, int num_diags,            \
+                         const int32_t *offsets, const T *data, const T *x, T *y) {                   \
+        for (int64_t row = 0; row < num_rows; row++) {                                                \
+            T dot = 0;                                                                                \
+            for (int n = 0; n < num_diags; n++) {                                                     \
+                int64_t col = row + offsets[n];                                                       \
+                T val = data[pitch * n + row];                                                        \
+                if (val != 0 && col >= 0 && col < num_cols) dot += val * x[col];                      \
+            }                                                                                         \
+            y[row] = dot;                                                                             \
+        }                                                                                             \
+    }
+DEFINE_DIA_SPMV(oracle_dia_spmv_f32, float)
+DEFINE_DIA_SPMV(oracle_dia_spmv_f64, double)
+
+/* The occupied diagonals of a CSR matrix in ascending order (SC09 section 3.1: "offsets"); returns how many
+ * there are and writes at most max_out of them. */
+ORACLE_API int64_t oracle_csr_diagonals(int64_t num_rows, int64_t num_cols, const int32_t *ptr, const int32_t *indices,
+                                        int64_t max_out, int32_t *out) {
+    int64_t slots = num_rows + num_cols - 1, count = 0;
+    if (slots <= 0) return 0;
+    unsigned char *mark = (unsigned char *)calloc((size_t)slots, 1);
+    for (int64_t r = 0; r < num_rows; r++)
+        for (int32_t e = ptr[r]; e < ptr[r + 1]; e++) mark[(int64_t)indices[e] - r + (num_rows - 1)] = 1;
+    for (int64_t i = 0; i < slots; i++)
+        if (mark[i]) { if (count < max_out) out[count] = (int32_t)(i - (num_rows - 1)); count++; }
+    free(mark);
+    return count;
+}
+
+/* CSR -> DIA on a given ascending offsets list; returns the number of entries on no listed diagonal. */
+#define DEFINE_CSR_TO_DIA(NAME, T)                                                                    \
+    ORACLE_API int64_t NAME(int64_t num_rows, const int32_t *ptr, const int32_t *indices, const T *vals, \
+                            int num_diags, const int32_t *offsets, int64_t pitch, T *data) {          \
+        int64_t miss = 0;                                                                             \
+        memset(data, 0, sizeof(T) * (size_t)num_diags * (size_t)pitch);                               \
+        for (int64_t r = 0; r < num_rows; r++)                                                        \
+            for (int32_t e = ptr[r]; e < ptr[r + 1]; e++) {                                           \
+                int n = -1;                                                                           \
+                for (int k = 0; k < num_diags; k++)                                                   \
+                    if ((int64_t)offsets[k] == (int64_t)indices[e] - r) { n = k; break; }             \
+                if (n < 0) miss++; else data[pitch * n + r] = vals[e];                                \
+            }                                                                                         \
+        return miss;                                                                                  \
+    }
+DEFINE_CSR_TO_DIA(oracle_csr_to_dia_f32, float)
+DEFINE_CSR_TO_DIA(oracle_csr_to_dia_f64, double)
+
 /* COO, y += A x, one entry at a time in storage order (Bell TR 2008 Fig. 23's
  * serial semantics; the segmented-reduction kernel of Fig. 24 computes the
  * same sums in a different order). */

@@ -293,6 +293,34 @@ def ell_spmv(num_rows, pitch, K, idx, dat, x):
     return y
 
 
+def csr_diagonals(ptr, col, num_cols, max_out=1 << 20):
+    ptr, col = _c(ptr, np.int32), _c(col, np.int32)
+    out = np.zeros(max_out, dtype=np.int32)
+    lib().oracle_csr_diagonals.restype = C.c_int64
+    n = int(lib().oracle_csr_diagonals(C.c_int64(len(ptr) - 1), C.c_int64(num_cols), _p(ptr), _p(col), C.c_int64(max_out), _p(out)))
+    return n, out[:min(n, max_out)].copy()
+
+
+def csr_to_dia(ptr, col, val, offsets, pitch):
+    ptr, col, offsets = _c(ptr, np.int32), _c(col, np.int32), _c(offsets, np.int32)
+    dt = _dt(val)
+    val = _c(val, dt)
+    dat = np.zeros(len(offsets) * pitch, dtype=dt)
+    fn = getattr(lib(), "oracle_csr_to_dia_%s" % ("f64" if dt == np.float64 else "f32"))
+    fn.restype = C.c_int64
+    miss = int(fn(C.c_int64(len(ptr) - 1), _p(ptr), _p(col), _p(val), C.c_int(len(offsets)), _p(offsets), C.c_int64(pitch), _p(dat)))
+    return dat, miss
+
+
+def dia_spmv(num_rows, num_cols, pitch, offsets, dat, x):
+    dt = _dt(dat)
+    offsets, dat, x = _c(offsets, np.int32), _c(dat, dt), _c(x, dt)
+    y = np.empty(num_rows, dtype=dt)
+    name = "oracle_dia_spmv_%s" % ("f64" if dt == np.float64 else "f32")
+    getattr(lib(), name)(C.c_int64(num_rows), C.c_int64(num_cols), C.c_int64(pitch), C.c_int(len(offsets)), _p(offsets), _p(dat), _p(x), _p(y))
+    return y
+
+
 def csr_to_coo_tail(ptr, col, val, K):
     ptr, col = _c(ptr, np.int32), _c(col, np.int32)
     dt = _dt(val)
