@@ -80,6 +80,8 @@ PROTOTYPES = {
     "cme213_csr_diagonals": (_i, [_p, _i64, _i64, _p, _p, _i, _p, _pi, _p]),
     "cme213_csr_to_dia_f32": (_i, [_p, _i64, _p, _p, _p, _i, _p, _i64, _p, _pi64, _p]),
     "cme213_csr_to_dia_f64": (_i, [_p, _i64, _p, _p, _p, _i, _p, _i64, _p, _pi64, _p]),
+    "cme213_stencil_laplace_f32": (_i, [_p, _i, _i, _i, C.c_float, _i64, _i64, _p, _p, _p]),
+    "cme213_stencil_laplace_f64": (_i, [_p, _i, _i, _i, C.c_double, _i64, _i64, _p, _p, _p]),
     "cme213_block_offsets_u32": (_i, [_p, _p, _p, _p, _i64, _i64, _p]),
     "cme213_radix_sort_pass_u32": (_i, [_p, _p, _p, _i64, _i, _i, _p]),
     "cme213_radix_sort_u32": (_i, [_p, _p, _p, _i64, _i, _p]),

@@ -162,6 +162,97 @@ compact_diagonals_kernel(int64_t slots, int64_t num_rows, const uint32_t *__rest
     if (mark[i] && excl[i] < (uint32_t)max_out) out[excl[i]] = (int32_t)(i - (num_rows - 1));
 }
 
+// ---- matrix-free: the 7-point (nz > 1) / 5-point (nz == 1) Laplacian of the generators, no matrix arrays at all ----
+// Same legs, coefficients (centre given by the caller: 6 / 4 in the generators; neighbours -1) and summation order as the CSR rows written by
+// cme213_gen_laplace3d_f64 / cme213_gen_laplace2d_f32, so y is bit-identical to the CSR / DIA product.  The
+// reference's stencil code is hw/hw2/programming/2dHeat.cu:361-366 (stencil2); 16 (fp64) / 8 (fp32) bytes per row.
+template <typename T>
+__device__ __forceinline__ T stencil_point(const T *__restrict__ x, int64_t i, int ix, int iy, int iz, int nx, int ny,
+                                           int nz, int64_t plane, T centre) {
+    T s = T(0);
+    if (iz > 0) s = add_rn(s, mul_rn(T(-1), __ldg(x + i - plane)));
+    if (iy > 0) s = add_rn(s, mul_rn(T(-1), __ldg(x + i - nx)));
+    if (ix > 0) s = add_rn(s, mul_rn(T(-1), __ldg(x + i - 1)));
+    s = add_rn(s, mul_rn(centre, __ldg(x + i)));
+    if (ix < nx - 1) s = add_rn(s, mul_rn(T(-1), __ldg(x + i + 1)));
+    if (iy < ny - 1) s = add_rn(s, mul_rn(T(-1), __ldg(x + i + nx)));
+    if (iz < nz - 1) s = add_rn(s, mul_rn(T(-1), __ldg(x + i + plane)));
+    return s;
+}
+
+// Four consecutive points of one grid line per thread (nx % 4 == 0, 16-byte aligned x and y, row range on 4s).
+template <typename T>
+__global__ void __launch_bounds__(256)
+stencil_v4_kernel(int nx, int ny, int nz, int64_t row_begin, int64_t row_end, T centre, const T *__restrict__ x,
+                  T *__restrict__ y) {
+    const int64_t i = row_begin + ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i >= row_end) return;
+    const int64_t plane = (int64_t)nx * ny;
+    const int ix = (int)(i % nx), iy = (int)((i / nx) % ny), iz = (int)(i / plane);
+    T c[4], s[4] = {T(0), T(0), T(0), T(0)}, v[4];
+    load4_cached(x + i, c);
+    if (iz > 0) { load4_cached(x + i - plane, v);
+#pragma unroll
+        for (int t = 0; t < 4; ++t) s[t] = add_rn(s[t], mul_rn(T(-1), v[t])); }
+    if (iy > 0) { load4_cached(x + i - nx, v);
+#pragma unroll
+        for (int t = 0; t < 4; ++t) s[t] = add_rn(s[t], mul_rn(T(-1), v[t])); }
+    if (ix > 0) s[0] = add_rn(s[0], mul_rn(T(-1), __ldg(x + i - 1)));
+#pragma unroll
+    for (int t = 1; t < 4; ++t) s[t] = add_rn(s[t], mul_rn(T(-1), c[t - 1]));
+#pragma unroll
+    for (int t = 0; t < 4; ++t) s[t] = add_rn(s[t], mul_rn(centre, c[t]));
+#pragma unroll
+    for (int t = 0; t < 3; ++t) s[t] = add_rn(s[t], mul_rn(T(-1), c[t + 1]));
+    if (ix + 4 < nx) s[3] = add_rn(s[3], mul_rn(T(-1), __ldg(x + i + 4)));
+    if (iy < ny - 1) { load4_cached(x + i + nx, v);
+#pragma unroll
+        for (int t = 0; t < 4; ++t) s[t] = add_rn(s[t], mul_rn(T(-1), v[t])); }
+    if (iz < nz - 1) { load4_cached(x + i + plane, v);
+#pragma unroll
+        for (int t = 0; t < 4; ++t) s[t] = add_rn(s[t], mul_rn(T(-1), v[t])); }
+    if (sizeof(T) == 4) {
+        st_stream(reinterpret_cast<float4 *>(y + i), make_float4((float)s[0], (float)s[1], (float)s[2], (float)s[3]));
+    } else {
+        st_stream(reinterpret_cast<double2 *>(y + i), make_double2((double)s[0], (double)s[1]));
+        st_stream(reinterpret_cast<double2 *>(y + i) + 1, make_double2((double)s[2], (double)s[3]));
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+stencil_scalar_kernel(int nx, int ny, int nz, int64_t row_begin, int64_t row_end, T centre, const T *__restrict__ x,
+                      T *__restrict__ y) {
+    const int64_t i = row_begin + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= row_end) return;
+    const int64_t plane = (int64_t)nx * ny;
+    y[i] = stencil_point(x, i, (int)(i % nx), (int)((i / nx) % ny), (int)(i / plane), nx, ny, nz, plane, centre);
+}
+
+template <typename T>
+int stencil_impl(cme213_ctx *ctx, int nx, int ny, int nz, T centre, int64_t row_begin, int64_t row_end, const T *d_x,
+                 T *d_y, void *stream) {
+    CME213_CHECK_CTX(ctx);
+    const int64_t rows_total = (int64_t)nx * ny * nz;
+    if (nx <= 0 || ny <= 0 || nz <= 0 || row_begin < 0 || row_end < row_begin || row_end > rows_total) {
+        set_error("stencil_laplace: bad shape");
+        return CME213_ERR_INVALID;
+    }
+    if (row_end == row_begin) return CME213_OK;
+    if (!d_x || !d_y || d_x == d_y) { set_error("stencil_laplace: bad pointers"); return CME213_ERR_INVALID; }
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t rows = row_end - row_begin;
+    if (nx % 4 == 0 && row_begin % 4 == 0 && rows % 4 == 0 && aligned16(d_x) && aligned16(d_y)) {
+        stencil_v4_kernel<T><<<(unsigned)div_up(rows / 4, 256), 256, 0, st>>>(nx, ny, nz, row_begin, row_end, centre, d_x, d_y);
+        CME213_LAUNCHED(ctx, "stencil_v4_kernel");
+    } else {
+        stencil_scalar_kernel<T><<<(unsigned)div_up(rows, 256), 256, 0, st>>>(nx, ny, nz, row_begin, row_end, centre, d_x, d_y);
+        CME213_LAUNCHED(ctx, "stencil_scalar_kernel");
+    }
+    return CME213_OK;
+}
+
 template <typename T>
 int dia_impl(cme213_ctx *ctx, int64_t num_rows, int64_t num_cols, int64_t pitch, int num_diags,
              const int32_t *d_offsets, const T *d_data, const T *d_x, T *d_y, void *stream) {
@@ -270,4 +361,13 @@ CME213_API int cme213_csr_diagonals(cme213_ctx *ctx, int64_t num_rows, int64_t n
     CME213_CUDA(cudaStreamSynchronize(st));
     *num_diags_out = (int)count;
     return CME213_OK;
+}
+
+CME213_API int cme213_stencil_laplace_f32(cme213_ctx *ctx, int nx, int ny, int nz, float centre, int64_t row_begin,
+                                          int64_t row_end, const float *d_x, float *d_y, void *stream) {
+    return stencil_impl<float>(ctx, nx, ny, nz, centre, row_begin, row_end, d_x, d_y, stream);
+}
+CME213_API int cme213_stencil_laplace_f64(cme213_ctx *ctx, int nx, int ny, int nz, double centre, int64_t row_begin,
+                                          int64_t row_end, const double *d_x, double *d_y, void *stream) {
+    return stencil_impl<double>(ctx, nx, ny, nz, centre, row_begin, row_end, d_x, d_y, stream);
 }

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- measures the hot path on B200 (see DESIGN.md "Measurement").
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c5|c1|scan|segscan|radixsort|dia|fp|transpose32|
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c5|c1|scan|segscan|radixsort|dia|stencil|fp|transpose32|
                      transpose64|ell|hyb|csr_powerlaw|pagerank] [--impl ours|reference] [--extras 0|1]
 
 Default workload = BASELINE.json config C5: row-sharded CSR SpMV iteration on the 3-D 7-point
@@ -289,6 +289,28 @@ def make_dia(ctx, torch, args):
                 keep=(d_off, d_dat, xa, xb))
 
 
+def make_stencil(ctx, torch, args):
+    # 8f.4: config C5's operator with no matrix arrays at all (only x and y move): the upper bound for C5
+    g = args.grid
+    rows = g * g * g
+    xa = torch.empty(rows, dtype=torch.float64, device="cuda")
+    xb = torch.empty_like(xa)
+    ctx.call("cme213_fill_uniform_f64", xa, rows, 9)
+    xa.mul_(0.05)
+    state = {"src": 0}
+
+    def step():
+        a, b = (xa, xb) if state["src"] == 0 else (xb, xa)
+        ctx.call("cme213_stencil_laplace_f64", g, g, g, 6.0, 0, rows, a, b, stream=torch.cuda.current_stream())
+        state["src"] = 1 - state["src"]
+
+    nnz = 7 * rows - 6 * g * g
+    return dict(step=step, alg_bytes=rows * 16, flops=2 * nnz, kernel="stencil_v4_kernel<double>", launches_per_step=1,
+                meta={"workload": "8f.4: C5's operator matrix-free (7-point stencil, fp64, %d^3 grid): 16 B per row" % g,
+                      "rows": rows, "csr_bytes_for_the_same_product": nnz * 12 + (rows + 1) * 4 + rows * 16,
+                      "l2": "2.1 GB per pass >> L2"}, keep=(xa, xb))
+
+
 def make_segscan(ctx, torch, args):
     n = 1 << 28
     v = torch.empty(n, dtype=torch.float32, device="cuda")
@@ -436,6 +458,8 @@ def build_workload(name, ctx, torch, args, rank=0, world=1, dist=None):
         return make_radixsort(ctx, torch, args)
     if name == "dia":
         return make_dia(ctx, torch, args)
+    if name == "stencil":
+        return make_stencil(ctx, torch, args)
     if name == "fp":
         return make_fp(ctx, torch, args)
     if name == "transpose32":
@@ -760,7 +784,7 @@ def main():
         others = []
         del wl
         torch.cuda.empty_cache()
-        names = ["scan", "segscan", "radixsort", "dia", "fp", "transpose32", "transpose64", "c1", "ell", "hyb", "csr_powerlaw",
+        names = ["scan", "segscan", "radixsort", "dia", "stencil", "fp", "transpose32", "transpose64", "c1", "ell", "hyb", "csr_powerlaw",
                  "ell_window", "hyb_window", "csr_window", "ell_regular_window", "csr_regular_window", "pagerank"]
         for name in names:
             try:

@@ -249,6 +249,17 @@ int cme213_csr_to_dia_f64(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_ro
                           const double *d_val, int num_diags, const int32_t *d_offsets, int64_t pitch, double *d_data,
                           int64_t *unmatched_out, void *stream);
 
+/* Matrix-free form of the generators' operator (cme213_gen_laplace2d_f32: nz = 1, centre 4; cme213_gen_laplace3d_f64:
+ * centre 6): y[i] = centre * x[i] - sum of the existing grid neighbours of point i, for rows [row_begin, row_end) of
+ * the nx * ny * nz grid in natural order (x fastest).  Legs and summation order are those of the CSR rows, so y is
+ * bit-identical to the CSR / DIA product; only x and y move (16 / 8 bytes per row): the upper bound for C1 / C5.
+ * d_x and d_y are full-length vectors and must not alias.
+ * reference: hw/hw2/programming/2dHeat.cu:361-366 (stencil2) and :431-461 (gpuGlobal). */
+int cme213_stencil_laplace_f32(cme213_ctx *ctx, int nx, int ny, int nz, float centre, int64_t row_begin,
+                               int64_t row_end, const float *d_x, float *d_y, void *stream);
+int cme213_stencil_laplace_f64(cme213_ctx *ctx, int nx, int ny, int nz, double centre, int64_t row_begin,
+                               int64_t row_end, const double *d_x, double *d_y, void *stream);
+
 /* Scatter offsets of a blocked LSD radix pass: out[i][j] = global_excl[j] + sum of local[i'][j] over blocks i' < i
  * (arrays [num_blocks x num_buckets], row-major).  Transpose + one segmented exclusive scan + transpose.
  * reference: hw/hw4/programming/radixsort.cpp:85-97 (local_histogram_final). */

@@ -141,3 +141,60 @@ def test_dia_full_size_matches_csr(ctx, cme):
     ctx.call("cme213_spmv_csr_f64", 0, rows, d_ptr, d_col, d_val, x, y_csr, 0)
     torch.cuda.synchronize()
     assert torch.equal(y_dia, y_csr)
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("shape", [(1, 1, 1), (4, 1, 1), (7, 5, 1), (8, 8, 1), (9, 7, 5), (32, 16, 8), (36, 3, 6), (64, 64, 9)])
+def test_matrix_free_stencil_equals_csr_bit_exact(ctx, dtype, shape):
+    nx, ny, nz = shape
+    rows = nx * ny * nz
+    ptr, col, val = g.laplace3d(nx, ny, nz, dtype=dtype)       # centre 6
+    x = np.random.default_rng(rows + 1).uniform(-1, 1, rows).astype(dtype)
+    d_y = dev_empty(rows, dtype)
+    ctx.call("cme213_stencil_laplace_" + sfx(dtype), nx, ny, nz, 6.0, 0, rows, dev(x), d_y)
+    assert np.array_equal(host(d_y), oracle.csr_spmv(ptr, col, val, x))
+    # a row range (as a shard would call it): untouched outside, identical inside
+    lo, hi = (rows // 3) // 4 * 4, max((rows // 3) // 4 * 4, (2 * rows // 3) // 4 * 4)
+    d_y2 = dev(np.full(rows, 7, dtype))
+    ctx.call("cme213_stencil_laplace_" + sfx(dtype), nx, ny, nz, 6.0, lo, hi, dev(x), d_y2)
+    got = host(d_y2)
+    assert np.array_equal(got[lo:hi], host(d_y)[lo:hi]) and (got[:lo] == 7).all() and (got[hi:] == 7).all()
+    # odd range -> scalar kernel
+    if rows > 3:
+        d_y3 = dev(np.full(rows, 7, dtype))
+        ctx.call("cme213_stencil_laplace_" + sfx(dtype), nx, ny, nz, 6.0, 1, rows - 1, dev(x), d_y3)
+        assert np.array_equal(host(d_y3)[1:-1], host(d_y)[1:-1])
+
+
+def test_matrix_free_stencil_2d_generator_and_errors(ctx, cme):
+    nx, ny = 24, 13
+    ptr, col, val = g.laplace2d(nx, ny)                         # cme213_gen_laplace2d_f32's matrix: centre 4
+    x = np.random.default_rng(2).uniform(-1, 1, nx * ny).astype(np.float32)
+    d_y = dev_empty(nx * ny, np.float32)
+    ctx.call("cme213_stencil_laplace_f32", nx, ny, 1, 4.0, 0, nx * ny, dev(x), d_y)
+    assert np.array_equal(host(d_y), oracle.csr_spmv(ptr, col, val, x))
+    d_x = dev(x)
+    for args in ((0, ny, 1, 4.0, 0, 0, d_x, d_y), (nx, ny, 1, 4.0, 0, nx * ny + 1, d_x, d_y), (nx, ny, 1, 4.0, 0, 8, d_x, d_x),
+                 (nx, ny, 1, 4.0, 0, 8, None, d_y)):
+        with pytest.raises(cme.Cme213Error):
+            ctx.call("cme213_stencil_laplace_f32", *args)
+
+
+def test_matrix_free_stencil_full_size_matches_dia(ctx, cme):
+    # 256^3: matrix-free == DIA == CSR on the device (the DIA/CSR pair is checked above)
+    import torch
+    gdim = 256
+    rows = gdim ** 3
+    nnz = C.c_int64()
+    d_ptr = torch.empty(rows + 1, dtype=torch.int32, device="cuda")
+    ctx.call("cme213_gen_laplace3d_f64", gdim, gdim, gdim, 0, rows, d_ptr, None, None, C.byref(nnz))
+    d_col = torch.empty(nnz.value, dtype=torch.int32, device="cuda")
+    d_val = torch.empty(nnz.value, dtype=torch.float64, device="cuda")
+    ctx.call("cme213_gen_laplace3d_f64", gdim, gdim, gdim, 0, rows, d_ptr, d_col, d_val, C.byref(nnz))
+    x = torch.empty(rows, dtype=torch.float64, device="cuda")
+    ctx.call("cme213_fill_uniform_f64", x, rows, 4)
+    y_mf, y_csr = torch.empty_like(x), torch.empty_like(x)
+    ctx.call("cme213_stencil_laplace_f64", gdim, gdim, gdim, 6.0, 0, rows, x, y_mf)
+    ctx.call("cme213_spmv_csr_f64", 0, rows, d_ptr, d_col, d_val, x, y_csr, 0)
+    torch.cuda.synchronize()
+    assert torch.equal(y_mf, y_csr)
