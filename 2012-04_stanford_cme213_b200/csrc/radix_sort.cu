@@ -12,7 +12,6 @@
 //                        in shared memory, then written out in runs (DOWNSWEEP 1, radixsort.cpp:99-109)
 // Algorithmic bytes per pass: 12 n (keys read twice, written once) + 8 * radix * n / 8192 for the table.
 #include "internal.cuh"
-#include <stdlib.h>
 
 using namespace cme213;
 
@@ -77,21 +76,25 @@ radix_hist_kernel(const uint32_t *__restrict__ keys, int64_t n, int start_bit, u
 // (warp w owns 512 consecutive keys, item i of lane l is key 32*i + l of them), so "item by item, lane by lane"
 // is memory order and the ranks below keep equal digits in input order.
 constexpr int RS_START_PAD = 260;
-constexpr size_t RS_SCATTER_SMEM = (size_t)(RS_TILE + RS_WARPS * RS_BINS + RS_START_PAD + RS_MAX_RADIX) * 4;
+constexpr size_t RS_SCATTER_SMEM = (size_t)(RS_TILE + 2 * RS_WARPS * RS_BINS + RS_START_PAD + RS_MAX_RADIX) * 4;
 
-// Finding the lanes of the warp that hold the same digit: __match_any_sync is one instruction, but MATCH.ANY runs
-// on the address-divergence unit at about one warp instruction per 64 cycles per SM (kernel 91 % ADU-bound,
-// 1.97 ms per pass, profiles/r01_ncu_radix_scatter_v1_match.txt); eight ballots + selects made it ALU-bound
-// (85 %, 1.27 ms, profiles/r01_ncu_radix_scatter_v2_ballot.txt).  Here every lane ORs its bit into a per-warp,
-// per-digit word in shared memory and reads the word back: two LSU instructions.
-template <int MINB>
-__global__ void __launch_bounds__(RS_THREADS, MINB)
+// Finding the lanes of the warp that hold the same digit.  Measured on B200 (2^28 keys, ms per 8-bit pass of this kernel):
+//   __match_any_sync        1.97  MATCH.ANY runs on the address-divergence unit at about one warp instruction per
+//                                 64 cycles per SM: 91 % ADU-bound (profiles/r01_ncu_radix_scatter_v1_match.txt)
+//   eight ballots + selects 1.27  85 % ALU-bound (..._v2_ballot.txt)
+//   shared-memory OR        1.10  every lane ORs its bit into a per-warp, per-digit word and reads the word back:
+//                                 89 % shared-memory-bound (..._v3_atomicor.txt)
+//   the same + early counts 0.97  (this kernel) one random shared-memory access per key fewer
+// Mixing the methods so that the three pipes work side by side was tried (4/6/6 ... 0/8/8 items) and lost to the
+// plain shared-memory version once the early counts were in (5.09-5.40 against 4.79 ms per sort).
+__global__ void __launch_bounds__(RS_THREADS, 2)
 radix_scatter_kernel(const uint32_t *__restrict__ keys_in, uint32_t *__restrict__ keys_out, int64_t n, int start_bit,
                      uint32_t mask, int radix, const uint32_t *__restrict__ table, int64_t pitch) {
     extern __shared__ __align__(16) uint32_t rs_smem[];
     uint32_t *s_keys = rs_smem;                          // [RS_TILE] the block regrouped by digit
-    uint32_t *s_wh = s_keys + RS_TILE;                   // [RS_WARPS][RS_BINS] per-warp digit counters
-    uint32_t *s_start = s_wh + RS_WARPS * RS_BINS;       // [RS_BINS] first slot of each digit inside the block
+    uint32_t *s_wh = s_keys + RS_TILE;                   // [RS_WARPS][RS_BINS] per-warp digit counters, then next free slots
+    uint32_t *s_mm = s_wh + RS_WARPS * RS_BINS;          // [RS_WARPS][RS_BINS] match words of the OR method
+    uint32_t *s_start = s_mm + RS_WARPS * RS_BINS;       // [RS_BINS] first slot of each digit inside the block
     uint32_t *s_gofs = s_start + RS_START_PAD;           // [radix] global offset minus s_start
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t base = (int64_t)blockIdx.x * RS_TILE;
@@ -106,28 +109,17 @@ radix_scatter_kernel(const uint32_t *__restrict__ keys_in, uint32_t *__restrict_
         const int li = wbase + i * 32;
         key[i] = li < cnt ? ld_stream(keys_in + base + li) : 0xFFFFFFFFu;
     }
-    for (int i = tid; i < RS_WARPS * RS_BINS; i += RS_THREADS) { s_wh[i] = 0; s_keys[i] = 0; }
+    for (int i = tid; i < 2 * RS_WARPS * RS_BINS; i += RS_THREADS) s_wh[i] = 0;   // s_wh and s_mm are adjacent
     __syncthreads();
 
+    // 1. per-warp digit counts first ("early counts"): the block-wide offsets are then known before the ranking,
+    //    so the ranking can put every key straight into its slot of the regrouped block.
     uint32_t *wh = s_wh + warp * RS_BINS;
-    uint32_t *mm = s_keys + warp * RS_BINS;   // match words; s_keys is not needed as key storage until the regroup
-    const uint32_t me = 1u << lane, lt = me - 1u;
-    uint32_t rank2[RS_ITEMS / 2];   // two 16-bit ranks per register (a warp holds 512 keys)
 #pragma unroll
     for (int i = 0; i < RS_ITEMS; ++i) {
         const bool valid = full || (wbase + i * 32 < cnt);
         const uint32_t d = valid ? ((key[i] >> start_bit) & mask) : (uint32_t)radix;   // slots past the end: bin `radix`
-        atomicOr(&mm[d], me);
-        __syncwarp();
-        const uint32_t peers = mm[d];
-        __syncwarp();
-        const int leader = 31 - __clz(peers);
-        uint32_t old = 0;
-        if (lane == leader) { mm[d] = 0; old = wh[d]; wh[d] = old + __popc(peers); }
-        old = __shfl_sync(0xFFFFFFFFu, old, leader);
-        const uint32_t r = old + __popc(peers & lt);
-        if (i & 1) rank2[i >> 1] |= r << 16; else rank2[i >> 1] = r;
-        __syncwarp();
+        atomicAdd(&wh[d], 1u);
     }
     __syncthreads();
 
@@ -162,7 +154,7 @@ radix_scatter_kernel(const uint32_t *__restrict__ keys_in, uint32_t *__restrict_
         }
     }
     __syncthreads();
-    if (tid < RS_BINS) {            // counters -> first slot of (warp, digit) inside the regrouped block
+    if (tid < RS_BINS) {            // counts -> next free slot of (warp, digit) inside the regrouped block
         uint32_t run = s_start[tid];
         if (tid < radix) s_gofs[tid] = tofs - run;
 #pragma unroll
@@ -173,12 +165,26 @@ radix_scatter_kernel(const uint32_t *__restrict__ keys_in, uint32_t *__restrict_
         }
     }
     __syncthreads();
+
+    // 2. stable ranking, item by item: the highest lane of each same-digit group reserves the group's slots
+    uint32_t *mm = s_mm + warp * RS_BINS;
+    const uint32_t me = 1u << lane, lt = me - 1u;
 #pragma unroll
     for (int i = 0; i < RS_ITEMS; ++i) {
         const bool valid = full || (wbase + i * 32 < cnt);
         const uint32_t d = valid ? ((key[i] >> start_bit) & mask) : (uint32_t)radix;
-        const uint32_t r = (i & 1) ? (rank2[i >> 1] >> 16) : (rank2[i >> 1] & 0xFFFFu);
-        s_keys[wh[d] + r] = key[i];
+        atomicOr(&mm[d], me);
+        __syncwarp();
+        const uint32_t peers = mm[d];
+        __syncwarp();
+        const int leader = 31 - __clz(peers);
+        uint32_t slot = 0;
+        if (lane == leader) {
+            mm[d] = 0;
+            slot = atomicAdd(&wh[d], (uint32_t)__popc(peers));
+        }
+        slot = __shfl_sync(0xFFFFFFFFu, slot, leader);
+        s_keys[slot + __popc(peers & lt)] = key[i];
     }
     __syncthreads();
 #pragma unroll 4
@@ -217,8 +223,7 @@ int run_pass(cme213_ctx *ctx, const uint32_t *d_in, uint32_t *d_out, int64_t n, 
     CME213_LAUNCHED(ctx, "radix_hist_kernel");
     int rc = cme213_internal_exclusive_scan_u32(ctx, table, table, p.pitch * radix, scratch, st);
     if (rc) return rc;
-    static const int minb = [] { const char *e = getenv("CME213_RS_MINB"); return e ? atoi(e) : 2; }();   // tuning hook
-    auto kern = minb == 2 ? radix_scatter_kernel<2> : radix_scatter_kernel<3>;
+    const auto kern = radix_scatter_kernel;
     // per device and cheap: set on every call rather than tracked
     CME213_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RS_SCATTER_SMEM));
     kern<<<(unsigned)p.blocks, RS_THREADS, RS_SCATTER_SMEM, st>>>(d_in, d_out, n, start_bit, mask, radix, table, p.pitch);
