@@ -227,7 +227,7 @@ def make_scan(ctx, torch, args):
 
 
 def make_radixsort(ctx, torch, args):
-    # 8f.4: LSD radix sort of 2^28 uint32 keys, 8-bit digits (the reference's default numBits, radixsort.cpp:165;
+    # 8f.4: LSD radix sort of 2^28 uint32 keys, 8-bit digits (the reference's default numBits, radixsort.cpp:166;
     # its default size is 40 M keys).  The four passes run out of place from a pristine buffer so that every
     # timed step sorts the same unsorted keys.
     n = 1 << 28

@@ -343,7 +343,7 @@ int cme213_fp_iterate_host_f64(int n, int p, int q, int iters, const double *h_a
 /* Host-pointer twins of the primitives. */
 int cme213_exclusive_scan_u32_host(const uint32_t *h_in, uint32_t *h_out, int64_t n);
 /* radixSortParallel on host memory (radixsort.cpp:111-121): h_keys sorted in place; kernel_ms_out (may be NULL)
- * gets the device time of the passes, the figure the reference's main() prints (radixsort.cpp:191-196). */
+ * gets the device time of the passes, the figure the reference's main() prints (radixsort.cpp:204-207). */
 int cme213_radix_sort_u32_host(uint32_t *h_keys, int64_t n, int num_bits, float *kernel_ms_out);
 int cme213_transpose_host_b32(const void *h_in, void *h_out, int64_t rows, int64_t cols);
 int cme213_transpose_host_b64(const void *h_in, void *h_out, int64_t rows, int64_t cols);

@@ -57,7 +57,7 @@ def main():
              ell_idx_rows=np.array([[0, 1, -1], [1, 2, -1], [0, 2, 3], [1, 3, -1]], np.int32),
              coo_row=np.array([0, 0, 1, 1, 2, 2, 2, 3, 3], np.int32))
     # 5. the reference's radix sort passes (hw/hw4/programming/radixsort.cpp) on 12 000 seeded keys: 31-bit values
-    #    like its rand() input (:172) with a low-entropy stretch so that stability matters
+    #    like its rand() input (:173-175) with a low-entropy stretch so that stability matters
     assert oracle.ref_lib("radixsort") is not None
     rng = np.random.default_rng(2012)
     keys = rng.integers(0, 2**31, 12000, dtype=np.int64).astype(np.uint32)

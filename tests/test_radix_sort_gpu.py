@@ -67,7 +67,7 @@ def test_sort_degenerate_inputs(ctx):
     for keys in (np.zeros(n, np.uint32), np.full(n, 0xFFFFFFFF, np.uint32), np.arange(n, dtype=np.uint32),
                  np.arange(n, dtype=np.uint32)[::-1].copy(), rand_keys(n, 1, hi=4), rand_keys(n, 2, hi=2**31) & np.uint32(0xFF00FF00)):
         assert np.array_equal(gpu_sort(ctx, keys), np.sort(keys))
-    # rand()-style 31-bit keys as in the reference's main() (radixsort.cpp:172)
+    # rand()-style 31-bit keys as in the reference's main() (radixsort.cpp:173-175)
     keys = rand_keys(123457, 9, hi=2**31)
     assert np.array_equal(gpu_sort(ctx, keys), np.sort(keys))
 
@@ -103,8 +103,8 @@ def test_sort_host_twin(cme):
 
 
 def test_sort_full_size_properties(ctx):
-    # the reference's default size is 40 M keys (radixsort.cpp:164); checked at 2^28 on the device:
-    # sortedness, and the multiset is kept (sum and xor of the keys, and of a hash of the keys).
+    # the reference's default size is 40 M keys (radixsort.cpp:165); checked at 2^28 on the device:
+    # sortedness, and the multiset is kept (sum of the keys and of a hash of the keys).
     import torch
     n = 1 << 28
     x = torch.empty(n, dtype=torch.int32, device="cuda")
