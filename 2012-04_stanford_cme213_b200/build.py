@@ -59,7 +59,7 @@ def build(force=False, verbose=False):
 
 
 DRIVERS = {"fp": ["fp_main.cpp", "matrix_io.cpp"], "pagerank": ["pagerank_main.cpp"],
-           "check_output": ["check_output_main.cpp", "matrix_io.cpp"]}
+           "check_output": ["check_output_main.cpp", "matrix_io.cpp"], "radixsort": ["radixsort_main.cpp"]}
 
 
 def build_drivers(force=False):

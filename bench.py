@@ -552,6 +552,8 @@ def run_reference(args):
     oracle.build()
     if args.workload == "pagerank":
         return run_reference_pagerank(args, np, oracle, g)
+    if args.workload == "radixsort":
+        return run_reference_radixsort(args, np, oracle)
     grid = args.grid
     planes = 32 if grid >= 32 else grid
     rows = planes * grid * grid
@@ -573,6 +575,36 @@ def run_reference(args):
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": "C5: CSR SpMV iteration, 3-D 7-point Laplacian %d^3, fp64 (CPU, bounded sample)" % grid},
         "cpu_baseline": {"value": v, "unit": "GB/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}), flush=True)
+
+
+def run_reference_radixsort(args, np, oracle):
+    """--impl reference --workload radixsort: the reference's OWN radixSortParallelPass loop (radixsort.cpp:44-121,
+    compiled from the checkout into oracle/_ref, OpenMP over its 8192-key blocks) on its default problem size
+    (40 M keys, numBits 8, radixsort.cpp:165-166); the oracle's blocked restatement (kind "port") when _ref is absent."""
+    n = 40_000_000
+    keys = np.random.default_rng(5).integers(0, 2**31, n, dtype=np.int64).astype(np.uint32)   # rand() range, :174
+    have_ref = oracle.ref_lib("radixsort") is not None
+    threads = oracle.num_threads()
+
+    def run():
+        if have_ref:
+            return oracle.ref_radix_sort(keys, 8)[1]          # seconds inside the passes, copies excluded
+        t0 = time.perf_counter()
+        oracle.radix_sort_u32(keys, 8, block_size=8192)
+        return time.perf_counter() - t0
+    for _ in range(max(1, min(args.warmup, 2))):
+        run()
+    steps = max(1, min(args.steps, 10))
+    el = sum(run() for _ in range(steps))
+    v = 48.0 * n * steps / el / 1e9
+    print(json.dumps({
+        "impl": "reference", "metric": "algorithmic_gbs", "value": v, "unit": "GB/s", "n_gpus": args.gpus, "steps": steps,
+        "warmup": args.warmup, "ms_per_step": el / steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "u32", "data": "synthetic", "keys_per_s": n * steps / el,
+        "config": {"workload": "8f.4: LSD radix sort of uint32 keys, 4 passes of 8 bits (CPU, 40 M keys)"},
+        "cpu_baseline": {"value": v, "unit": "GB/s", "cores": threads, "kind": "reference" if have_ref else "port",
+                         "sample": "radixSortParallelPass x4 of radixsort.cpp on 40,000,000 keys (its default size), %d OpenMP threads" % threads},
         "e2e": {"value": v, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}), flush=True)
 
 

@@ -68,3 +68,13 @@ def test_pagerank_driver(tmp_path):
     r = subprocess.run([os.path.join(BIN, "pagerank"), "300002", "8", "20", "7"], cwd=tmp_path, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "gpu graph propagate took" in r.stdout and "Worked! CUDA and reference output match." in r.stdout
+
+
+def test_radixsort_driver(tmp_path):
+    # hw/hw4/programming/radixsort.cpp:162-214 with the GPU sort in the place of radixSortParallel
+    r = subprocess.run([os.path.join(BIN, "radixsort"), "3000001", "8"], cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "n_elements: 3000001" in r.stdout and "parallel radix:" in r.stdout
+    assert "Worked! GPU radix sort and std::sort output match." in r.stdout
+    r = subprocess.run([os.path.join(BIN, "radixsort"), "100000", "4"], cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "Worked!" in r.stdout, r.stdout + r.stderr
