@@ -180,42 +180,80 @@ __device__ __forceinline__ T stencil_point(const T *__restrict__ x, int64_t i, i
     return s;
 }
 
-// Four consecutive points of one grid line per thread (nx % 4 == 0, 16-byte aligned x and y, row range on 4s).
-template <typename T>
+// One 16-byte vector of consecutive points per thread (4 floats / 2 doubles), so every warp-wide load is one
+// contiguous 512-byte request; the x legs of a thread's edge points come from the neighbouring lanes by shuffle.
+// (The first version gave a thread four doubles = two 16-byte loads 32 bytes apart, fetched the x legs with scalar
+// loads and divided 64-bit indices: 32 sectors per request, L1 wavefront pipe 98 % busy, 0.48 ms --
+// profiles/r01_ncu_stencil_v1_l1bound.txt.  This one: 0.464 ms.)
+// Needs nx % NP == 0, 16-byte aligned x and y, row range on multiples of NP.
+template <typename T> struct Vec16;
+template <> struct Vec16<float> {
+    static constexpr int NP = 4;
+    static __device__ __forceinline__ void load(const float *p, float (&v)[4]) {
+        const float4 t = __ldg(reinterpret_cast<const float4 *>(p));
+        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    }
+    static __device__ __forceinline__ void store(float *p, const float (&v)[4]) {
+        st_stream(reinterpret_cast<float4 *>(p), make_float4(v[0], v[1], v[2], v[3]));
+    }
+};
+template <> struct Vec16<double> {
+    static constexpr int NP = 2;
+    static __device__ __forceinline__ void load(const double *p, double (&v)[2]) {
+        const double2 t = __ldg(reinterpret_cast<const double2 *>(p));
+        v[0] = t.x; v[1] = t.y;
+    }
+    static __device__ __forceinline__ void store(double *p, const double (&v)[2]) {
+        st_stream(reinterpret_cast<double2 *>(p), make_double2(v[0], v[1]));
+    }
+};
+
+template <typename T, int GROUPS>
 __global__ void __launch_bounds__(256)
-stencil_v4_kernel(int nx, int ny, int nz, int64_t row_begin, int64_t row_end, T centre, const T *__restrict__ x,
-                  T *__restrict__ y) {
-    const int64_t i = row_begin + ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
-    if (i >= row_end) return;
+stencil_vec_kernel(int nx, int ny, int nz, int64_t row_begin, int64_t row_end, T centre, const T *__restrict__ x,
+                   T *__restrict__ y) {
+    constexpr int NP = Vec16<T>::NP;
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t plane = (int64_t)nx * ny;
-    const int ix = (int)(i % nx), iy = (int)((i / nx) % ny), iz = (int)(i / plane);
-    T c[4], s[4] = {T(0), T(0), T(0), T(0)}, v[4];
-    load4_cached(x + i, c);
-    if (iz > 0) { load4_cached(x + i - plane, v);
+    // a warp owns GROUPS consecutive 512-byte segments, so a CTA of 256 threads covers 2 KiB * GROUPS of x: with
+    // lines of that length or less the y legs of one line are the centre loads of its neighbour in the same CTA (L1 hits)
 #pragma unroll
-        for (int t = 0; t < 4; ++t) s[t] = add_rn(s[t], mul_rn(T(-1), v[t])); }
-    if (iy > 0) { load4_cached(x + i - nx, v);
+    for (int g = 0; g < GROUPS; ++g) {
+        const int64_t i = row_begin + ((warp * GROUPS + g) * 32 + lane) * NP;
+        const bool alive = i < row_end;      // no early exit: the shuffles below need the whole warp
+        T c[NP], s[NP], v[NP];
 #pragma unroll
-        for (int t = 0; t < 4; ++t) s[t] = add_rn(s[t], mul_rn(T(-1), v[t])); }
-    if (ix > 0) s[0] = add_rn(s[0], mul_rn(T(-1), __ldg(x + i - 1)));
+        for (int t = 0; t < NP; ++t) { c[t] = T(0); s[t] = T(0); }
+        if (alive) Vec16<T>::load(x + i, c);
+        T left = __shfl_up_sync(0xFFFFFFFFu, c[NP - 1], 1), right = __shfl_down_sync(0xFFFFFFFFu, c[0], 1);
+        if (!alive) continue;
+        // 32-bit index arithmetic (the grid has fewer than 2^31 points): 64-bit divisions cost more than the loads
+        const uint32_t iu = (uint32_t)i, line = iu / (uint32_t)nx;
+        const int ix = (int)(iu - line * (uint32_t)nx), iz = (int)(line / (uint32_t)ny), iy = (int)(line - (uint32_t)iz * (uint32_t)ny);
+        if (lane == 0 && ix > 0) left = __ldg(x + i - 1);
+        if ((lane == 31 || i + NP >= row_end) && ix + NP < nx) right = __ldg(x + i + NP);
+        if (iz > 0) { Vec16<T>::load(x + i - plane, v);
 #pragma unroll
-    for (int t = 1; t < 4; ++t) s[t] = add_rn(s[t], mul_rn(T(-1), c[t - 1]));
+            for (int t = 0; t < NP; ++t) s[t] = add_rn(s[t], mul_rn(T(-1), v[t])); }
+        if (iy > 0) { Vec16<T>::load(x + i - nx, v);
 #pragma unroll
-    for (int t = 0; t < 4; ++t) s[t] = add_rn(s[t], mul_rn(centre, c[t]));
+            for (int t = 0; t < NP; ++t) s[t] = add_rn(s[t], mul_rn(T(-1), v[t])); }
+        if (ix > 0) s[0] = add_rn(s[0], mul_rn(T(-1), left));
 #pragma unroll
-    for (int t = 0; t < 3; ++t) s[t] = add_rn(s[t], mul_rn(T(-1), c[t + 1]));
-    if (ix + 4 < nx) s[3] = add_rn(s[3], mul_rn(T(-1), __ldg(x + i + 4)));
-    if (iy < ny - 1) { load4_cached(x + i + nx, v);
+        for (int t = 1; t < NP; ++t) s[t] = add_rn(s[t], mul_rn(T(-1), c[t - 1]));
 #pragma unroll
-        for (int t = 0; t < 4; ++t) s[t] = add_rn(s[t], mul_rn(T(-1), v[t])); }
-    if (iz < nz - 1) { load4_cached(x + i + plane, v);
+        for (int t = 0; t < NP; ++t) s[t] = add_rn(s[t], mul_rn(centre, c[t]));
 #pragma unroll
-        for (int t = 0; t < 4; ++t) s[t] = add_rn(s[t], mul_rn(T(-1), v[t])); }
-    if (sizeof(T) == 4) {
-        st_stream(reinterpret_cast<float4 *>(y + i), make_float4((float)s[0], (float)s[1], (float)s[2], (float)s[3]));
-    } else {
-        st_stream(reinterpret_cast<double2 *>(y + i), make_double2((double)s[0], (double)s[1]));
-        st_stream(reinterpret_cast<double2 *>(y + i) + 1, make_double2((double)s[2], (double)s[3]));
+        for (int t = 0; t < NP - 1; ++t) s[t] = add_rn(s[t], mul_rn(T(-1), c[t + 1]));
+        if (ix + NP < nx) s[NP - 1] = add_rn(s[NP - 1], mul_rn(T(-1), right));
+        if (iy < ny - 1) { Vec16<T>::load(x + i + nx, v);
+#pragma unroll
+            for (int t = 0; t < NP; ++t) s[t] = add_rn(s[t], mul_rn(T(-1), v[t])); }
+        if (iz < nz - 1) { Vec16<T>::load(x + i + plane, v);
+#pragma unroll
+            for (int t = 0; t < NP; ++t) s[t] = add_rn(s[t], mul_rn(T(-1), v[t])); }
+        Vec16<T>::store(y + i, s);
     }
 }
 
@@ -226,7 +264,8 @@ stencil_scalar_kernel(int nx, int ny, int nz, int64_t row_begin, int64_t row_end
     const int64_t i = row_begin + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= row_end) return;
     const int64_t plane = (int64_t)nx * ny;
-    y[i] = stencil_point(x, i, (int)(i % nx), (int)((i / nx) % ny), (int)(i / plane), nx, ny, nz, plane, centre);
+    const uint32_t iu = (uint32_t)i, line = iu / (uint32_t)nx, iz = line / (uint32_t)ny;
+    y[i] = stencil_point(x, i, (int)(iu - line * (uint32_t)nx), (int)(line - iz * (uint32_t)ny), (int)iz, nx, ny, nz, plane, centre);
 }
 
 template <typename T>
@@ -234,7 +273,8 @@ int stencil_impl(cme213_ctx *ctx, int nx, int ny, int nz, T centre, int64_t row_
                  T *d_y, void *stream) {
     CME213_CHECK_CTX(ctx);
     const int64_t rows_total = (int64_t)nx * ny * nz;
-    if (nx <= 0 || ny <= 0 || nz <= 0 || row_begin < 0 || row_end < row_begin || row_end > rows_total) {
+    if (nx <= 0 || ny <= 0 || nz <= 0 || row_begin < 0 || row_end < row_begin || row_end > rows_total ||
+        rows_total > 0x7FFFFFFFLL) {   // 32-bit indices, as in the generators
         set_error("stencil_laplace: bad shape");
         return CME213_ERR_INVALID;
     }
@@ -243,9 +283,12 @@ int stencil_impl(cme213_ctx *ctx, int nx, int ny, int nz, T centre, int64_t row_
     DeviceGuard g(ctx->device);
     cudaStream_t st = (cudaStream_t)stream;
     const int64_t rows = row_end - row_begin;
-    if (nx % 4 == 0 && row_begin % 4 == 0 && rows % 4 == 0 && aligned16(d_x) && aligned16(d_y)) {
-        stencil_v4_kernel<T><<<(unsigned)div_up(rows / 4, 256), 256, 0, st>>>(nx, ny, nz, row_begin, row_end, centre, d_x, d_y);
-        CME213_LAUNCHED(ctx, "stencil_v4_kernel");
+    constexpr int NP = Vec16<T>::NP;
+    if (nx % NP == 0 && row_begin % NP == 0 && rows % NP == 0 && aligned16(d_x) && aligned16(d_y)) {
+        // 256 threads x one vector each measured best (0.464 ms at 512^3 fp64); 2 or 4 vectors per thread and larger
+        // CTAs were slower (0.49-0.85 ms)
+        stencil_vec_kernel<T, 1><<<(unsigned)div_up(rows / NP, 256), 256, 0, st>>>(nx, ny, nz, row_begin, row_end, centre, d_x, d_y);
+        CME213_LAUNCHED(ctx, "stencil_vec_kernel");
     } else {
         stencil_scalar_kernel<T><<<(unsigned)div_up(rows, 256), 256, 0, st>>>(nx, ny, nz, row_begin, row_end, centre, d_x, d_y);
         CME213_LAUNCHED(ctx, "stencil_scalar_kernel");

@@ -305,7 +305,7 @@ def make_stencil(ctx, torch, args):
         state["src"] = 1 - state["src"]
 
     nnz = 7 * rows - 6 * g * g
-    return dict(step=step, alg_bytes=rows * 16, flops=2 * nnz, kernel="stencil_v4_kernel<double>", launches_per_step=1,
+    return dict(step=step, alg_bytes=rows * 16, flops=2 * nnz, kernel="stencil_vec_kernel<double>", launches_per_step=1,
                 meta={"workload": "8f.4: C5's operator matrix-free (7-point stencil, fp64, %d^3 grid): 16 B per row" % g,
                       "rows": rows, "csr_bytes_for_the_same_product": nnz * 12 + (rows + 1) * 4 + rows * 16,
                       "l2": "2.1 GB per pass >> L2"}, keep=(xa, xb))

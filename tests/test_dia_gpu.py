@@ -144,7 +144,8 @@ def test_dia_full_size_matches_csr(ctx, cme):
 
 
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
-@pytest.mark.parametrize("shape", [(1, 1, 1), (4, 1, 1), (7, 5, 1), (8, 8, 1), (9, 7, 5), (32, 16, 8), (36, 3, 6), (64, 64, 9)])
+@pytest.mark.parametrize("shape", [(1, 1, 1), (4, 1, 1), (7, 5, 1), (8, 8, 1), (9, 7, 5), (32, 16, 8), (36, 3, 6), (64, 64, 9), (132, 9, 40),
+                                   (256, 20, 4), (4, 4, 70)])
 def test_matrix_free_stencil_equals_csr_bit_exact(ctx, dtype, shape):
     nx, ny, nz = shape
     rows = nx * ny * nz
@@ -159,6 +160,14 @@ def test_matrix_free_stencil_equals_csr_bit_exact(ctx, dtype, shape):
     ctx.call("cme213_stencil_laplace_" + sfx(dtype), nx, ny, nz, 6.0, lo, hi, dev(x), d_y2)
     got = host(d_y2)
     assert np.array_equal(got[lo:hi], host(d_y)[lo:hi]) and (got[:lo] == 7).all() and (got[hi:] == 7).all()
+    # whole planes (how a z-slab shard calls it) -> the plane-marching kernel when nx % 4 == 0
+    if nz >= 6:
+        zl, zh = 1, nz - 1
+        d_y4 = dev(np.full(rows, 7, dtype))
+        ctx.call("cme213_stencil_laplace_" + sfx(dtype), nx, ny, nz, 6.0, zl * nx * ny, zh * nx * ny, dev(x), d_y4)
+        got = host(d_y4)
+        assert np.array_equal(got[zl * nx * ny:zh * nx * ny], host(d_y)[zl * nx * ny:zh * nx * ny])
+        assert (got[:zl * nx * ny] == 7).all() and (got[zh * nx * ny:] == 7).all()
     # odd range -> scalar kernel
     if rows > 3:
         d_y3 = dev(np.full(rows, 7, dtype))
