@@ -96,3 +96,82 @@ def test_row_partition_and_bandwidth():
     assert sh.half_bandwidth(torch.from_numpy(ptr), torch.from_numpy(col)) == 20
     p2, c2, _ = g.laplace3d(5, 4, 3, 20, 40)
     assert sh.half_bandwidth(torch.from_numpy(p2), torch.from_numpy(c2), 20) == 20
+
+
+# ---- fused exchange on CPU: torch shared-memory tensors stand in for the CUDA-IPC peer mappings --------------------
+class _FakePeers:
+    """PeerVectors look-alike: prev(which) / next(which) give the neighbour's full-length vector (a tensor that every
+    process maps) instead of a device address."""
+
+    def __init__(self, vectors, rank, world):
+        self.v, self.rank, self.world = vectors, rank, world
+
+    def prev(self, which):
+        return self.v[self.rank - 1][which] if self.rank > 0 else None
+
+    def next(self, which):
+        return self.v[self.rank + 1][which] if self.rank < self.world - 1 else None
+
+
+def _fused_worker(rank, world, port, grid, iters, vectors, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import importlib
+        import oracle
+        from oracle import generators as g
+        sh = importlib.import_module("2012-04_stanford_cme213_b200.sharded")
+        nx, ny, nz = grid
+        rows = nx * ny * nz
+        lo, hi = sh.row_partition(rows, world)[rank]
+        ptr, col, val = g.laplace3d(nx, ny, nz, lo, hi)
+
+        def rows_of(a, b, x_full):
+            p = ptr[a - lo:b - lo + 1]
+            return oracle.csr_spmv(p - p[0], col[p[0]:p[-1]], val[p[0]:p[-1]], x_full.numpy())
+
+        def spmv(a, b, x_full, y_full):
+            if b > a:
+                y_full.numpy()[a:b] = rows_of(a, b, x_full)
+
+        def push(a, b, h, x_full, y_full, peer_prev, peer_next):
+            # what cme213_spmv_csr_f64_halo_push does: both boundary planes, each stored locally and into the neighbour
+            first, last = rows_of(a, a + h, x_full), rows_of(b - h, b, x_full)
+            y_full.numpy()[a:a + h] = first
+            y_full.numpy()[b - h:b] = last
+            if peer_prev is not None:
+                peer_prev.numpy()[a:a + h] = first
+            if peer_next is not None:
+                peer_next.numpy()[b - h:b] = last
+        spmv.push = push
+
+        xa, xb = vectors[rank]
+        it = sh.ShardedIterate(rows, world, rank, spmv, xa, xb, halo=nx * ny, mode="fused", dist=dist,
+                               peers=_FakePeers(vectors, rank, world))
+        assert it.mode == "fused"
+        it.iterate(iters)
+        full = it.gather_result(0).numpy()
+        if rank == 0:
+            fp, fc, fv = g.laplace3d(nx, ny, nz)
+            x0 = np.random.default_rng(1).uniform(0, 1, rows)
+            out.put(bool(np.array_equal(full, oracle.csr_iterate(fp, fc, fv, x0, iters))))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,grid", [(2, (6, 5, 8)), (3, (5, 4, 9)), (3, (5, 4, 6))])
+def test_fused_exchange_logic_matches_single_process(world, grid):
+    rows = grid[0] * grid[1] * grid[2]
+    x0 = np.random.default_rng(1).uniform(0, 1, rows)
+    vectors = [(torch.from_numpy(x0.copy()).share_memory_(), torch.zeros(rows, dtype=torch.float64).share_memory_())
+               for _ in range(world)]
+    ctx = mp.get_context("spawn")
+    out = ctx.SimpleQueue()
+    port = _free_port()
+    procs = [ctx.Process(target=_fused_worker, args=(r, world, port, grid, 4, vectors, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    assert out.get(), "fused exchange result differs from the single-process oracle"
