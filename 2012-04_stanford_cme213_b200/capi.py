@@ -102,6 +102,7 @@ PROTOTYPES = {
     "cme213_fp_iterate_host_f64": (_i, [_i, _i, _i, _i, _p, _p, _p, _p, _p, _pf]),
     "cme213_exclusive_scan_u32_host": (_i, [_p, _p, _i64]),
     "cme213_radix_sort_u32_host": (_i, [_p, _i64, _i, _pf]),
+    "cme213_radix_sort_pass_u32_host": (_i, [_p, _p, _i64, C.c_uint, C.c_uint, C.c_uint]),
     "cme213_transpose_host_b32": (_i, [_p, _p, _i64, _i64]),
     "cme213_transpose_host_b64": (_i, [_p, _p, _i64, _i64]),
 }

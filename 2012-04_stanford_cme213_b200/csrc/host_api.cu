@@ -277,6 +277,34 @@ CME213_API int cme213_radix_sort_u32_host(uint32_t *h_keys, int64_t n, int num_b
     CME213_CUDA(cudaMemcpy(h_keys, d_keys, (size_t)n * 4, cudaMemcpyDeviceToHost));
     return CME213_OK;
 }
+CME213_API int cme213_radix_sort_pass_u32_host(const uint32_t *h_keys, uint32_t *h_sorted, int64_t n, unsigned num_bits,
+                                               unsigned start_bit, unsigned block_size) {
+    (void)block_size;   // the reference's OpenMP block size (radixsort.cpp:44): the stable pass does not depend on it
+    if (n < 0) { set_error("radix_sort_pass_u32_host: negative size"); return CME213_ERR_INVALID; }
+    if (num_bits < 1 || num_bits > 16 || start_bit > 31) {
+        set_error("radix_sort_pass_u32_host: num_bits must be 1..16 and start_bit 0..31");
+        return CME213_ERR_INVALID;
+    }
+    if (n == 0) return CME213_OK;
+    if (!h_keys || !h_sorted) { set_error("radix_sort_pass_u32_host: null pointer"); return CME213_ERR_INVALID; }
+    CtxHolder c;
+    TRY(c.init());
+    DeviceBuffers buf;
+    uint32_t *d_a, *d_b;
+    TRY(buf.alloc(&d_a, (size_t)n));
+    TRY(buf.alloc(&d_b, (size_t)n));
+    CME213_CUDA(cudaMemcpy(d_a, h_keys, (size_t)n * 4, cudaMemcpyHostToDevice));
+    // a digit wider than 8 bits = two stable device passes, low half first
+    const unsigned lo_bits = num_bits > 8 ? 8 : num_bits;
+    TRY(cme213_radix_sort_pass_u32(c.ctx, d_a, d_b, n, (int)start_bit, (int)lo_bits, nullptr));
+    uint32_t *d_res = d_b;
+    if (num_bits > 8 && start_bit + 8 < 32) {
+        TRY(cme213_radix_sort_pass_u32(c.ctx, d_b, d_a, n, (int)start_bit + 8, (int)(num_bits - 8), nullptr));
+        d_res = d_a;
+    }
+    CME213_CUDA(cudaMemcpy(h_sorted, d_res, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    return CME213_OK;
+}
 CME213_API int cme213_transpose_host_b32(const void *h_in, void *h_out, int64_t rows, int64_t cols) {
     return transpose_host<uint32_t>(h_in, h_out, rows, cols);
 }

@@ -554,6 +554,8 @@ def run_reference(args):
         return run_reference_pagerank(args, np, oracle, g)
     if args.workload == "radixsort":
         return run_reference_radixsort(args, np, oracle)
+    if args.workload in ("scan", "fp", "transpose32", "transpose64"):
+        return run_reference_primitive(args, np, oracle, g)
     grid = args.grid
     planes = 32 if grid >= 32 else grid
     rows = planes * grid * grid
@@ -605,6 +607,55 @@ def run_reference_radixsort(args, np, oracle):
         "config": {"workload": "8f.4: LSD radix sort of uint32 keys, 4 passes of 8 bits (CPU, 40 M keys)"},
         "cpu_baseline": {"value": v, "unit": "GB/s", "cores": threads, "kind": "reference" if have_ref else "port",
                          "sample": "radixSortParallelPass x4 of radixsort.cpp on 40,000,000 keys (its default size), %d OpenMP threads" % threads},
+        "e2e": {"value": v, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}), flush=True)
+
+
+def run_reference_primitive(args, np, oracle, g):
+    """--impl reference for the single-GPU primitives, on bounded samples of the GPU workloads:
+    scan        the 3-line exclusive scan of radixsort.cpp:76-81 restated, OpenMP two-pass blocked variant (port)
+    fp          the shipped CPU path of fp.cu:124-150 restated (xx = x[k] hoisted, OpenMP multiply + per-segment sums, port)
+    transposeNN the index formula of Lecture06 slide 9 restated, OpenMP over row tiles (port; the reference has no code)"""
+    import ctypes
+    threads = oracle.num_threads()
+    rng = np.random.default_rng(3)
+    w = args.workload
+    if w == "scan":
+        n = 1 << 26
+        x = rng.integers(0, 2**32, n, dtype=np.uint64).astype(np.uint32)
+        out, L, P = np.zeros_like(x), oracle.lib(), (lambda a: a.ctypes.data_as(ctypes.c_void_p))
+        run, alg = (lambda: L.oracle_exclusive_scan_u32_omp(P(x), P(out), ctypes.c_int64(n))), 8 * n   # buffers allocated once
+        name, sample, dtype = "C2a: exclusive scan of uint32 (CPU)", "2^26 of the 2^28 elements, OpenMP blocked two-pass scan", "u32"
+    elif w == "fp":
+        n, q = 1 << 24, 1 << 20
+        a = rng.uniform(-1, 1, n).astype(np.float32)
+        xv = rng.uniform(-1, 1, q).astype(np.float32)
+        k = rng.integers(0, q, n).astype(np.int32)
+        sseg = np.concatenate([np.arange(0, n, 64), [n]]).astype(np.int32)
+        xx, cur, L, P = xv[k], a.copy(), oracle.lib(), (lambda t: t.ctypes.data_as(ctypes.c_void_p))   # xx = x[k] hoisted as in fp.cu:124-125
+        run = lambda: L.oracle_fp_cpu_iterate_f32(ctypes.c_int(n), ctypes.c_int(len(sseg)), P(cur), P(sseg), P(xx), ctypes.c_int(1))
+        alg = 12 * n + 4 * q + n // 8
+        name, sample, dtype = "C2c: final-project step a*x[k] + segmented scan (CPU)", "n = 2^24 of 2^28, q = 2^20, segments of 64, fp.cu's OpenMP loops", "f32"
+    else:
+        bits = 32 if w == "transpose32" else 64
+        m = 8192
+        a = rng.integers(0, 2**31, (m, m)).astype(np.uint32 if bits == 32 else np.uint64)
+        out, L, P = np.zeros_like(a), oracle.lib(), (lambda t: t.ctypes.data_as(ctypes.c_void_p))
+        fn = L.oracle_transpose_b32_omp if bits == 32 else L.oracle_transpose_b64_omp
+        run, alg = (lambda: fn(P(a), P(out), ctypes.c_int64(m), ctypes.c_int64(m))), 2 * m * m * (bits // 8)
+        name, sample, dtype = "C3: transpose, %d-bit elements (CPU)" % bits, "8192^2 of the 16384^2 matrix, OpenMP over row tiles", "b%d" % bits
+    for _ in range(max(1, min(args.warmup, 2))):
+        run()
+    steps = max(1, min(args.steps, 10))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        run()
+    el = time.perf_counter() - t0
+    v = alg * steps / el / 1e9
+    print(json.dumps({
+        "impl": "reference", "metric": "algorithmic_gbs", "value": v, "unit": "GB/s", "n_gpus": args.gpus, "steps": steps,
+        "warmup": args.warmup, "ms_per_step": el / steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": dtype, "data": "synthetic", "config": {"workload": name},
+        "cpu_baseline": {"value": v, "unit": "GB/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}), flush=True)
 
 

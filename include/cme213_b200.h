@@ -345,6 +345,11 @@ int cme213_exclusive_scan_u32_host(const uint32_t *h_in, uint32_t *h_out, int64_
 /* radixSortParallel on host memory (radixsort.cpp:111-121): h_keys sorted in place; kernel_ms_out (may be NULL)
  * gets the device time of the passes, the figure the reference's main() prints (radixsort.cpp:204-207). */
 int cme213_radix_sort_u32_host(uint32_t *h_keys, int64_t n, int num_bits, float *kernel_ms_out);
+/* radixSortParallelPass(keys, sorted, numBits, startBit, blockSize) on host memory (radixsort.cpp:44, the scan's only
+ * public caller in the reference): one stable counting pass on numBits (1..16) bits from startBit; block_size is accepted
+ * and ignored (the result does not depend on it). */
+int cme213_radix_sort_pass_u32_host(const uint32_t *h_keys, uint32_t *h_sorted, int64_t n, unsigned num_bits,
+                                    unsigned start_bit, unsigned block_size);
 int cme213_transpose_host_b32(const void *h_in, void *h_out, int64_t rows, int64_t cols);
 int cme213_transpose_host_b64(const void *h_in, void *h_out, int64_t rows, int64_t cols);
 

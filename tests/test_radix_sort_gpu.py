@@ -102,6 +102,22 @@ def test_sort_host_twin(cme):
     assert np.array_equal(work, np.sort(keys))
 
 
+def test_pass_host_twin_reference_signature(cme):
+    # radixSortParallelPass(keys, sorted, numBits, startBit, blockSize): also digits wider than 8 bits
+    gd = golden("radixsort_ref_n12000.npz")
+    keys = np.ascontiguousarray(gd["keys"])
+    out = np.empty_like(keys)
+    P = lambda a: a.ctypes.data_as(C.c_void_p)
+    fn = cme.load().cme213_radix_sort_pass_u32_host
+    assert fn(P(keys), P(out), len(keys), 8, 0, 8192) == 0
+    assert np.array_equal(out, gd["pass_0_8"])
+    for bits, start in ((16, 0), (11, 5), (13, 16), (12, 24), (5, 13)):
+        assert fn(P(keys), P(out), len(keys), bits, start, 1000) == 0
+        assert np.array_equal(out, oracle.radix_pass_u32(keys, start, bits)), (bits, start)
+    assert fn(P(keys), P(out), len(keys), 17, 0, 8192) == cme.capi.ERR_INVALID
+    assert fn(None, P(out), len(keys), 8, 0, 8192) == cme.capi.ERR_INVALID
+
+
 def test_sort_full_size_properties(ctx):
     # the reference's default size is 40 M keys (radixsort.cpp:165); checked at 2^28 on the device:
     # sortedness, and the multiset is kept (sum of the keys and of a hash of the keys).
