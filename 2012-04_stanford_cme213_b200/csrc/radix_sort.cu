@@ -8,8 +8,9 @@
 //   exclusive scan       ONE scan over the whole digit-major table replaces UPSWEEP 2 + SCAN + DOWNSWEEP 2
 //                        (radixsort.cpp:60-97): entry (d, b) becomes "keys with a smaller digit" + "keys with
 //                        digit d in earlier blocks" = the block's scatter offset for digit d
-//   radix_scatter_kernel stable ranks inside the block (warp match + per-warp counters), keys regrouped by digit
-//                        in shared memory, then written out in runs (DOWNSWEEP 1, radixsort.cpp:99-109)
+//   radix_scatter_kernel per-warp digit counts, block-wide offsets, then stable ranks item by item (same-digit lanes
+//                        found through a shared-memory OR) that put the keys straight into a digit-grouped copy of
+//                        the block in shared memory, written out in runs (DOWNSWEEP 1, radixsort.cpp:99-109)
 // Algorithmic bytes per pass: 12 n (keys read twice, written once) + 8 * radix * n / 8192 for the table.
 #include "internal.cuh"
 
