@@ -90,6 +90,7 @@ PROTOTYPES = {
     "cme213_gen_powerlaw_lengths": (_i, [_p, _i64, _i, _u32, _u32, _i, _u32, _p, _pi64, _p]),
     "cme213_gen_random_csr_fill_f32": (_i, [_p, _i64, _i64, _p, _i64, _u32, _p, _p, _p]),
     "cme213_gen_pagerank_graph": (_i, [_p, _i, _i, _u32, _p, _p, _p, _p, _pi64, _p]),
+    "cme213_gen_segment_offsets": (_i, [_p, _i64, _i64, _u32, _p, _pi64, _p]),
     "cme213_fill_uniform_f32": (_i, [_p, _p, _i64, _u32, _p]),
     "cme213_fill_uniform_f64": (_i, [_p, _p, _i64, _u32, _p]),
     "cme213_fill_hash_u32": (_i, [_p, _p, _i64, _u32, _u32, _p]),

@@ -286,3 +286,69 @@ CME213_API int cme213_fill_random_flags(cme213_ctx *ctx, uint32_t *d_flag_bits, 
     uint32_t *d_out = d_flag_bits;
     FILL_ENTRY("fill_random_flags", uint32_t, fill_flags_kernel, d_out, n, seed, prob_num)
 }
+
+// ---- segment start offsets the way the final project's input script makes them -----------------------------
+// hw/hw_final/programming/aux/readMM.py:44-49: s = random.sample(range(n), p); s.sort(); s[0] = 0; s[p-1] = n.
+// Here: num_cuts hashed positions in [1, n), sorted with the library's radix sort, duplicates removed by
+// mark + exclusive scan + compaction (slides/Lecture16.pdf slides 3-13), framed by 0 and n.
+namespace {
+__global__ void cut_points_kernel(uint32_t *keys, int64_t num_cuts, uint32_t seed, uint32_t n) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < num_cuts) keys[i] = 1u + hash32(seed, (uint64_t)i) % (n - 1u);
+}
+__global__ void mark_first_of_run_kernel(const uint32_t *keys, int64_t num_cuts, uint32_t *mark) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i <= num_cuts) mark[i] = (i < num_cuts && (i == 0 || keys[i] != keys[i - 1])) ? 1u : 0u;
+}
+__global__ void compact_offsets_kernel(const uint32_t *keys, const uint32_t *mark, const uint32_t *excl, int64_t num_cuts,
+                                       uint32_t n, int32_t *s_out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < num_cuts && mark[i]) s_out[1 + excl[i]] = (int32_t)keys[i];
+    if (i == num_cuts) { s_out[0] = 0; s_out[1 + excl[num_cuts]] = (int32_t)n; }
+}
+}  // namespace
+
+CME213_API int cme213_gen_segment_offsets(cme213_ctx *ctx, int64_t n, int64_t num_cuts, uint32_t seed, int32_t *d_s_out,
+                                          int64_t *p_out, void *stream) {
+    CME213_CHECK_CTX(ctx);
+    if (p_out) *p_out = 0;
+    if (n < 1 || n > 0x7FFFFFFFLL || num_cuts < 0 || num_cuts > 0x7FFFFFFELL || !d_s_out || !p_out || (num_cuts > 0 && n < 2)) {
+        set_error("gen_segment_offsets: bad arguments");
+        return CME213_ERR_INVALID;
+    }
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    // set-up code, not a timed path: its four temporaries come from one cudaMalloc (the sort and the scan use the
+    // context workspace themselves)
+    const size_t words = (size_t)num_cuts + 1;
+    uint32_t *tmp = nullptr;
+    CME213_CUDA(cudaMalloc(&tmp, 4 * words * sizeof(uint32_t)));
+    uint32_t *keys = tmp, *keys2 = tmp + words, *mark = tmp + 2 * words, *excl = tmp + 3 * words;
+    int rc = CME213_OK;
+    const unsigned grid = (unsigned)div_up((int64_t)words, 256);
+    if (num_cuts > 0) {
+        cut_points_kernel<<<grid, 256, 0, st>>>(keys, num_cuts, seed, (uint32_t)n);
+        ctx->launches++;
+        rc = cme213_radix_sort_u32(ctx, keys, keys2, num_cuts, 8, stream);
+    }
+    if (rc == CME213_OK) {
+        mark_first_of_run_kernel<<<grid, 256, 0, st>>>(keys, num_cuts, mark);
+        ctx->launches++;
+        rc = cme213_exclusive_scan_u32(ctx, mark, excl, (int64_t)words, stream);
+    }
+    uint32_t distinct = 0;
+    if (rc == CME213_OK) {
+        compact_offsets_kernel<<<grid, 256, 0, st>>>(keys, mark, excl, num_cuts, (uint32_t)n, d_s_out);
+        ctx->launches++;
+        cudaError_t e = cudaMemcpyAsync(&distinct, excl + num_cuts, 4, cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        if (e == cudaSuccess) e = cudaGetLastError();
+        if (e != cudaSuccess) rc = cuda_fail(e, "gen_segment_offsets");
+    } else {
+        cudaStreamSynchronize(st);
+    }
+    cudaFree(tmp);
+    if (rc == CME213_OK) *p_out = (int64_t)distinct + 2;
+    return rc;
+}
+

@@ -316,14 +316,21 @@ def make_segscan(ctx, torch, args):
     v = torch.empty(n, dtype=torch.float32, device="cuda")
     ctx.call("cme213_fill_uniform_f32", v, n, 4)
     bits = i32((n + 31) // 32, torch)
-    ctx.call("cme213_fill_random_flags", bits, n, 5, (1 << 32) // 64)
+    # segment offsets as readMM.py:44-49 makes them (sorted random cut points, n/64 of them), then the head-flag bitmask
+    import ctypes as C
+    cuts = n // 64
+    d_s = i32(cuts + 2, torch)
+    p = C.c_int64()
+    ctx.call("cme213_gen_segment_offsets", n, cuts, 5, d_s, C.byref(p))
+    ctx.call("cme213_segment_flags_from_offsets", d_s, int(p.value), n, bits)
+    del d_s
     out = torch.empty_like(v)
 
     def step():
         ctx.call("cme213_segscan_inclusive_f32", v, bits, out, n, stream=torch.cuda.current_stream())
 
     return dict(step=step, alg_bytes=8 * n + n // 8, flops=n, kernel="lookback_scan_kernel<f32,seg>", launches_per_step=1,
-                meta={"workload": "C2b: inclusive segmented fp32 scan, n=2^28, random segments of mean length 64", "n": n,
+                meta={"workload": "C2b: inclusive segmented fp32 scan, n=2^28, segments from n/64 sorted random cut points (readMM.py recipe, mean length 64)", "n": n,
                       "l2": "2.2 GB per pass >> L2"}, keep=(v, bits, out))
 
 

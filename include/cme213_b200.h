@@ -310,6 +310,13 @@ int cme213_gen_pagerank_graph(cme213_ctx *ctx, int num_elements, int avg_edges, 
  * and random head flags with probability num/2^32 per element (bit 0 always set). */
 int cme213_fill_uniform_f32(cme213_ctx *ctx, float *d_out, int64_t n, uint32_t seed, void *stream);
 int cme213_fill_uniform_f64(cme213_ctx *ctx, double *d_out, int64_t n, uint32_t seed, void *stream);
+/* Segment start offsets the way the final project's input script draws them
+ * (hw/hw_final/programming/aux/readMM.py:44-49: sorted random cut points, s[0] = 0, s[p-1] = n): num_cuts hashed
+ * positions in [1, n) -> cme213_radix_sort_u32 -> duplicates dropped by mark + scan + compaction -> framed by 0 and n.
+ * d_s_out needs num_cuts + 2 entries; *p_out = entries written (distinct cuts + 2).  Synchronises; allocates its
+ * temporaries (set-up code). */
+int cme213_gen_segment_offsets(cme213_ctx *ctx, int64_t n, int64_t num_cuts, uint32_t seed, int32_t *d_s_out,
+                               int64_t *p_out, void *stream);
 int cme213_fill_hash_u32(cme213_ctx *ctx, uint32_t *d_out, int64_t n, uint32_t seed, uint32_t modulus, void *stream);
 int cme213_fill_random_flags(cme213_ctx *ctx, uint32_t *d_flag_bits, int64_t n, uint32_t seed, uint32_t prob_num,
                              void *stream);

@@ -164,3 +164,10 @@ def fp_inputs(n, p, q, seed, dtype=np.float32):
     s = np.concatenate([[0], cuts, [n]]).astype(np.int32)
     k = rng.integers(0, q, n).astype(np.int32)
     return a, s, k, x
+
+
+
+def segment_offsets(n, num_cuts, seed):
+    """cme213_gen_segment_offsets restated: readMM.py:44-49's sorted random cut points, duplicates dropped."""
+    cuts = np.uint64(1) + hash32(seed, np.arange(num_cuts, dtype=np.uint64)).astype(np.uint64) % np.uint64(max(n - 1, 1))
+    return np.concatenate([[0], np.unique(cuts), [n]]).astype(np.int32)

@@ -71,3 +71,29 @@ def test_pagerank_graph(ctx):
     assert nnz.value == len(edges)
     assert np.array_equal(host(d_ind, np.uint32), ind) and np.array_equal(host(d_edges, np.uint32), edges)
     assert np.array_equal(host(d_inv), inv) and np.array_equal(host(d_nodes), nodes)
+
+
+@pytest.mark.parametrize("n,cuts", [(1, 0), (2, 5), (10, 0), (100, 30), (100, 400), (1000003, 15000), (1 << 24, (1 << 24) // 64)])
+def test_segment_offsets_like_readmm(ctx, n, cuts):
+    # readMM.py:44-49: sorted random cut points framed by 0 and n; built on the device with the radix sort and the scan
+    d_s = dev_empty(cuts + 2, np.int32)
+    p = C.c_int64()
+    ctx.call("cme213_gen_segment_offsets", n, cuts, 77, d_s, C.byref(p))
+    want = g.segment_offsets(n, cuts, 77)
+    assert p.value == len(want)
+    s = host(d_s)[:p.value]
+    assert np.array_equal(s, want)
+    # the loader's invariants (aux/mp1-util.h:118-147): s[0] = 0, s[p-1] = n, strictly increasing
+    assert s[0] == 0 and s[-1] == n and (np.diff(s) > 0).all()
+
+
+def test_segment_offsets_feed_the_flag_builder(ctx):
+    n, cuts = 300000, 5000
+    d_s = dev_empty(cuts + 2, np.int32)
+    p = C.c_int64()
+    ctx.call("cme213_gen_segment_offsets", n, cuts, 5, d_s, C.byref(p))
+    bits = dev_empty((n + 31) // 32, np.uint32)
+    ctx.call("cme213_segment_flags_from_offsets", d_s, int(p.value), n, bits)
+    want = np.zeros(n, bool)
+    want[g.segment_offsets(n, cuts, 5)[:-1]] = True
+    assert np.array_equal(host(bits, np.uint32), g.pack_flags(want))
