@@ -85,6 +85,9 @@ PROTOTYPES = {
     "cme213_block_offsets_u32": (_i, [_p, _p, _p, _p, _i64, _i64, _p]),
     "cme213_radix_sort_pass_u32": (_i, [_p, _p, _p, _i64, _i, _i, _p]),
     "cme213_radix_sort_u32": (_i, [_p, _p, _p, _i64, _i, _p]),
+    "cme213_radix_sort_pairs_u32": (_i, [_p, _p, _p, _p, _p, _i64, _i, _p]),
+    "cme213_coo_to_csr_f32": (_i, [_p, _i64, _i64, _i64, _p, _p, _p, _p, _p, _p, _p]),
+    "cme213_coo_to_csr_f64": (_i, [_p, _i64, _i64, _i64, _p, _p, _p, _p, _p, _p, _p]),
     "cme213_gen_laplace2d_f32": (_i, [_p, _i, _i, _p, _p, _p, _pi64, _p]),
     "cme213_gen_laplace3d_f64": (_i, [_p, _i, _i, _i, _i64, _i64, _p, _p, _p, _pi64, _p]),
     "cme213_gen_powerlaw_lengths": (_i, [_p, _i64, _i, _u32, _u32, _i, _u32, _p, _pi64, _p]),

@@ -88,15 +88,19 @@ constexpr size_t RS_SCATTER_SMEM = (size_t)(RS_TILE + 2 * RS_WARPS * RS_BINS + R
 //   the same + early counts 0.97  (this kernel) one random shared-memory access per key fewer
 // Mixing the methods so that the three pipes work side by side was tried (4/6/6 ... 0/8/8 items) and lost to the
 // plain shared-memory version once the early counts were in (5.09-5.40 against 4.79 ms per sort).
+// PAIRS: a 32-bit payload travels with every key (second shared-memory copy of the block, same slots).
+template <bool PAIRS>
 __global__ void __launch_bounds__(RS_THREADS, 2)
 radix_scatter_kernel(const uint32_t *__restrict__ keys_in, uint32_t *__restrict__ keys_out, int64_t n, int start_bit,
-                     uint32_t mask, int radix, const uint32_t *__restrict__ table, int64_t pitch) {
+                     uint32_t mask, int radix, const uint32_t *__restrict__ table, int64_t pitch,
+                     const uint32_t *__restrict__ vals_in, uint32_t *__restrict__ vals_out) {
     extern __shared__ __align__(16) uint32_t rs_smem[];
     uint32_t *s_keys = rs_smem;                          // [RS_TILE] the block regrouped by digit
     uint32_t *s_wh = s_keys + RS_TILE;                   // [RS_WARPS][RS_BINS] per-warp digit counters, then next free slots
     uint32_t *s_mm = s_wh + RS_WARPS * RS_BINS;          // [RS_WARPS][RS_BINS] match words of the OR method
     uint32_t *s_start = s_mm + RS_WARPS * RS_BINS;       // [RS_BINS] first slot of each digit inside the block
     uint32_t *s_gofs = s_start + RS_START_PAD;           // [radix] global offset minus s_start
+    uint32_t *s_vals = s_gofs + RS_MAX_RADIX;            // [RS_TILE] PAIRS only: the payloads, regrouped like the keys
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t base = (int64_t)blockIdx.x * RS_TILE;
     const int cnt = (int)((n - base) < RS_TILE ? (n - base) : RS_TILE);
@@ -185,7 +189,9 @@ radix_scatter_kernel(const uint32_t *__restrict__ keys_in, uint32_t *__restrict_
             slot = atomicAdd(&wh[d], (uint32_t)__popc(peers));
         }
         slot = __shfl_sync(0xFFFFFFFFu, slot, leader);
-        s_keys[slot + __popc(peers & lt)] = key[i];
+        const uint32_t pos = slot + __popc(peers & lt);
+        s_keys[pos] = key[i];
+        if (PAIRS) s_vals[pos] = valid ? vals_in[base + wbase + i * 32] : 0u;
     }
     __syncthreads();
 #pragma unroll 4
@@ -193,7 +199,9 @@ radix_scatter_kernel(const uint32_t *__restrict__ keys_in, uint32_t *__restrict_
         const int j = k * RS_THREADS + tid;
         if (j < cnt) {
             const uint32_t kv = s_keys[j];
-            keys_out[(size_t)(s_gofs[(kv >> start_bit) & mask] + (uint32_t)j)] = kv;
+            const size_t g = (size_t)(s_gofs[(kv >> start_bit) & mask] + (uint32_t)j);
+            keys_out[g] = kv;
+            if (PAIRS) vals_out[g] = s_vals[j];
         }
     }
 }
@@ -214,7 +222,8 @@ PassPlan plan_pass(int64_t n) {
 
 // One pass with the workspace already in hand.
 int run_pass(cme213_ctx *ctx, const uint32_t *d_in, uint32_t *d_out, int64_t n, int start_bit, int num_bits,
-             const PassPlan &p, void *ws, cudaStream_t st) {
+             const PassPlan &p, void *ws, cudaStream_t st, const uint32_t *d_vals_in = nullptr,
+             uint32_t *d_vals_out = nullptr) {
     const int radix = 1 << num_bits;
     const uint32_t mask = (uint32_t)radix - 1u;
     uint32_t *table = (uint32_t *)ws;
@@ -224,10 +233,18 @@ int run_pass(cme213_ctx *ctx, const uint32_t *d_in, uint32_t *d_out, int64_t n, 
     CME213_LAUNCHED(ctx, "radix_hist_kernel");
     int rc = cme213_internal_exclusive_scan_u32(ctx, table, table, p.pitch * radix, scratch, st);
     if (rc) return rc;
-    const auto kern = radix_scatter_kernel;
     // per device and cheap: set on every call rather than tracked
-    CME213_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RS_SCATTER_SMEM));
-    kern<<<(unsigned)p.blocks, RS_THREADS, RS_SCATTER_SMEM, st>>>(d_in, d_out, n, start_bit, mask, radix, table, p.pitch);
+    if (d_vals_in) {
+        constexpr size_t smem = RS_SCATTER_SMEM + (size_t)RS_TILE * 4;
+        CME213_CUDA(cudaFuncSetAttribute(radix_scatter_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        radix_scatter_kernel<true><<<(unsigned)p.blocks, RS_THREADS, smem, st>>>(d_in, d_out, n, start_bit, mask, radix, table,
+                                                                               p.pitch, d_vals_in, d_vals_out);
+    } else {
+        CME213_CUDA(cudaFuncSetAttribute(radix_scatter_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)RS_SCATTER_SMEM));
+        radix_scatter_kernel<false><<<(unsigned)p.blocks, RS_THREADS, RS_SCATTER_SMEM, st>>>(d_in, d_out, n, start_bit, mask,
+                                                                                           radix, table, p.pitch, nullptr, nullptr);
+    }
     CME213_LAUNCHED(ctx, "radix_scatter_kernel");
     return CME213_OK;
 }
@@ -286,5 +303,39 @@ CME213_API int cme213_radix_sort_u32(cme213_ctx *ctx, uint32_t *d_keys, uint32_t
     }
     if (passes & 1)   // the reference runs its passes in pairs so the result ends in `keys` (radixsort.cpp:117-120)
         CME213_CUDA(cudaMemcpyAsync(d_keys, d_keys_tmp, (size_t)n * 4, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return CME213_OK;
+}
+
+// Key-value form: d_vals travels with d_keys.  Sorts on the key bits [0, end_bit) only (8-bit digits), which is what
+// the COO -> CSR conversion needs (row and column indices use few bits).  Stable; the result ends in d_keys / d_vals.
+CME213_API int cme213_radix_sort_pairs_u32(cme213_ctx *ctx, uint32_t *d_keys, uint32_t *d_keys_tmp, uint32_t *d_vals,
+                                           uint32_t *d_vals_tmp, int64_t n, int end_bit, void *stream) {
+    CME213_CHECK_CTX(ctx);
+    int rc = check_sort_args("radix_sort_pairs_u32", d_keys, d_keys_tmp, n);
+    if (rc) return rc;
+    rc = check_sort_args("radix_sort_pairs_u32", d_vals, d_vals_tmp, n);
+    if (rc) return rc;
+    if (end_bit < 0 || end_bit > 32) { set_error("radix_sort_pairs_u32: end_bit must be 0..32"); return CME213_ERR_INVALID; }
+    if (n == 0 || end_bit == 0) return CME213_OK;
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    const PassPlan p = plan_pass(n);
+    void *ws = nullptr;
+    rc = workspace(ctx, p.total_bytes, &ws);
+    if (rc) return rc;
+    uint32_t *ks = d_keys, *kd = d_keys_tmp, *vs = d_vals, *vd = d_vals_tmp;
+    int passes = 0;
+    for (int start = 0; start < end_bit; start += 8) {
+        const int bits = end_bit - start < 8 ? end_bit - start : 8;
+        rc = run_pass(ctx, ks, kd, n, start, bits, p, ws, st, vs, vd);
+        if (rc) return rc;
+        uint32_t *t = ks; ks = kd; kd = t;
+        t = vs; vs = vd; vd = t;
+        ++passes;
+    }
+    if (passes & 1) {
+        CME213_CUDA(cudaMemcpyAsync(d_keys, d_keys_tmp, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
+        CME213_CUDA(cudaMemcpyAsync(d_vals, d_vals_tmp, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
+    }
     return CME213_OK;
 }

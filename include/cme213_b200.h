@@ -223,6 +223,23 @@ int cme213_csr_to_coo_tail_f64(cme213_ctx *ctx, int64_t num_rows, const int32_t 
                                const double *d_val, int K, int64_t *tail_nnz_out, int32_t *d_coo_row,
                                int32_t *d_coo_col, double *d_coo_val, void *stream);
 
+/* Key-value form of the sort: the 32-bit payload d_vals travels with d_keys; only the key bits [0, end_bit) are
+ * sorted on (8-bit digits), stable; the result ends in d_keys / d_vals.  No counterpart in the reference (its sort is
+ * keys only); it exists for cme213_coo_to_csr_*. */
+int cme213_radix_sort_pairs_u32(cme213_ctx *ctx, uint32_t *d_keys, uint32_t *d_keys_tmp, uint32_t *d_vals,
+                                uint32_t *d_vals_tmp, int64_t n, int end_bit, void *stream);
+/* Unsorted COO triplets -> CSR with ascending columns (duplicates kept, in input order): two stable key-value sorts of a
+ * permutation (by column, then by row), one gather, row_ptr from the run boundaries.  The input side of the path:
+ * MatrixMarket files reach hw/hw_final/programming/aux/readMM.py:18-24 as COO triplets (a.row, a.col, a.data).
+ * d_row_ptr needs num_rows + 1 entries, d_col / d_val nnz.  Entries outside the matrix -> CME213_ERR_INVALID.
+ * Synchronises; allocates its temporaries (set-up code). */
+int cme213_coo_to_csr_f32(cme213_ctx *ctx, int64_t num_rows, int64_t num_cols, int64_t nnz, const int32_t *d_coo_row,
+                          const int32_t *d_coo_col, const float *d_coo_val, int32_t *d_row_ptr, int32_t *d_col,
+                          float *d_val, void *stream);
+int cme213_coo_to_csr_f64(cme213_ctx *ctx, int64_t num_rows, int64_t num_cols, int64_t nnz, const int32_t *d_coo_row,
+                          const int32_t *d_coo_col, const double *d_coo_val, int32_t *d_row_ptr, int32_t *d_col,
+                          double *d_val, void *stream);
+
 /* ---- DIA (the format bound for the stencil operators of C1 / C5) --------------------------- */
 /* y = A x, A in DIA: d_data[n * pitch + r] is the entry of row r on diagonal d_offsets[n] (column r + offset),
  * zero where there is none; offsets ascending.  Zero entries are skipped and the sum runs in diagonal order

@@ -171,3 +171,13 @@ def segment_offsets(n, num_cuts, seed):
     """cme213_gen_segment_offsets restated: readMM.py:44-49's sorted random cut points, duplicates dropped."""
     cuts = np.uint64(1) + hash32(seed, np.arange(num_cuts, dtype=np.uint64)).astype(np.uint64) % np.uint64(max(n - 1, 1))
     return np.concatenate([[0], np.unique(cuts), [n]]).astype(np.int32)
+
+
+def coo_to_csr(num_rows, row, col, val):
+    """cme213_coo_to_csr_* restated: stable sort by (row, column), duplicates kept in input order; what scipy's
+    coo -> csr does for the MatrixMarket inputs of readMM.py:18-24 (without summing duplicates)."""
+    row, col = np.asarray(row, dtype=np.int64), np.asarray(col, dtype=np.int64)
+    order = np.lexsort((col, row))          # last key is the primary one; lexsort is stable
+    ptr = np.zeros(num_rows + 1, dtype=np.int64)
+    np.add.at(ptr, row + 1, 1)
+    return np.cumsum(ptr).astype(np.int32), col[order].astype(np.int32), np.asarray(val)[order]
