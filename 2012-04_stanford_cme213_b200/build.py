@@ -1,6 +1,6 @@
 """Builds libcme213_b200.so in-tree with nvcc for sm_100a (no JIT cache, no torch extension).
 
-Usage: python build.py [--force] [--verbose]
+Usage: python build.py [--force] [--verbose] [--tuning]   (--tuning compiles the environment-variable tuning hooks in)
 The shared object sits next to this file so that it travels with the repository snapshot.
 """
 import os
@@ -18,17 +18,23 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", 
               "-Xcompiler", "-fPIC,-fvisibility=hidden,-Wall", "-Xptxas", "-v"]
 
 
-def _newest_dep():
-    t = 0.0
+def source_hash():
+    """sha1 over csrc/, host-independent: the library carries it (cme213_build_id) and capi.load() compares, so a
+    stale git-ignored .so cannot be used silently against newer sources."""
+    import hashlib
+    h = hashlib.sha1()
     for root in (CSRC, os.path.join(HERE, "..", "include")):
-        for f in os.listdir(root):
-            t = max(t, os.path.getmtime(os.path.join(root, f)))
-    return max(t, os.path.getmtime(__file__))
+        for f in sorted(os.listdir(root)):
+            if f.endswith((".cu", ".cuh", ".h")):
+                h.update(f.encode())
+                with open(os.path.join(root, f), "rb") as fh:
+                    h.update(fh.read())
+    return h.hexdigest()[:16]
 
 
-def _compile(src, verbose):
+def _compile(src, verbose, extra=()):
     obj = os.path.join(OBJ, src.replace(".cu", ".o"))
-    cmd = ["nvcc"] + NVCC_FLAGS + ["-c", os.path.join(CSRC, src), "-o", obj]
+    cmd = ["nvcc"] + NVCC_FLAGS + list(extra) + ["-c", os.path.join(CSRC, src), "-o", obj]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if verbose or r.returncode != 0:
         sys.stderr.write(" ".join(cmd) + "\n" + r.stdout + r.stderr)
@@ -39,22 +45,33 @@ def _compile(src, verbose):
     return obj
 
 
-def build(force=False, verbose=False):
+def built_hash():
+    try:
+        with open(os.path.join(OBJ, "source_hash.txt")) as f:
+            return f.read().strip()
+    except OSError:
+        return None
+
+
+def build(force=False, verbose=False, tuning=False):
     sources = [s for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
-    if not force and os.path.exists(LIB) and os.path.getmtime(LIB) >= _newest_dep():
+    want = source_hash() + ("-tuning" if tuning else "")
+    if not force and os.path.exists(LIB) and built_hash() == want:
         return LIB
     if subprocess.run(["which", "nvcc"], capture_output=True).returncode != 0:
-        if os.path.exists(LIB):
-            return LIB  # GPU box without a need to rebuild: use the shipped library
-        raise RuntimeError("nvcc not found and no prebuilt libcme213_b200.so")
+        raise RuntimeError("libcme213_b200.so is missing or older than csrc/ (built %s, sources %s) and nvcc is not here to "
+                           "rebuild it" % (built_hash(), want))
     os.makedirs(OBJ, exist_ok=True)
+    extra = ['-DCME213_SOURCE_HASH="%s"' % want] + (["-DCME213_TUNING"] if tuning else [])
     with ThreadPoolExecutor(max_workers=min(8, len(sources))) as ex:
-        objs = list(ex.map(lambda s: _compile(s, verbose), sources))
+        objs = list(ex.map(lambda s: _compile(s, verbose, extra), sources))
     cmd = ["nvcc", "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         sys.stderr.write(r.stdout + r.stderr)
         raise RuntimeError("link failed")
+    with open(os.path.join(OBJ, "source_hash.txt"), "w") as f:
+        f.write(want + "\n")
     return LIB
 
 
@@ -81,5 +98,5 @@ def build_drivers(force=False):
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv, tuning="--tuning" in sys.argv))
     build_drivers(force="--force" in sys.argv)

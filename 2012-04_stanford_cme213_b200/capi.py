@@ -38,6 +38,7 @@ PROTOTYPES = {
     "cme213_ctx_launch_count": (_i64, [_p]),
     "cme213_last_error": (C.c_char_p, []),
     "cme213_version": (_i, []),
+    "cme213_build_id": (C.c_char_p, []),
     "cme213_transpose_b32": (_i, [_p, _p, _p, _i64, _i64, _i64, _i64, _p]),
     "cme213_transpose_b64": (_i, [_p, _p, _p, _i64, _i64, _i64, _i64, _p]),
     "cme213_exclusive_scan_u32": (_i, [_p, _p, _p, _i64, _p]),
@@ -128,6 +129,19 @@ def load():
         fn = getattr(lib, name)  # AttributeError here means header and library disagree
         fn.restype = res
         fn.argtypes = args
+    # the .so is a git-ignored build artefact: refuse one that was built from other sources than those beside it
+    try:
+        import importlib.util
+        spec = importlib.util.spec_from_file_location("cme213_build", os.path.join(HERE, "build.py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        want = mod.source_hash()
+    except Exception:  # sources not shipped beside the library: nothing to compare with
+        want = None
+    have = lib.cme213_build_id().decode()
+    if want is not None and have.replace("-tuning", "") != want:
+        raise RuntimeError("libcme213_b200.so was built from other sources (library %s, sources %s): rebuild with "
+                           "`python 2012-04_stanford_cme213_b200/build.py`" % (have, want))
     _lib = lib
     return lib
 

@@ -13,6 +13,9 @@ struct cme213_ctx {
     int sm_count;
     void *ws;          // scratch workspace, grown on demand
     size_t ws_bytes;
+    cudaStream_t ws_stream;  // stream of the workspace's latest user (see cme213::workspace)
+    bool ws_used;
+    cudaEvent_t ws_event;
     int64_t launches;  // kernels launched through this context
     // CSR AUTO decisions (spmv_csr.cu), remembered per (row_ptr, row range)
     static constexpr int CSR_CACHE = 16;
@@ -25,8 +28,12 @@ namespace cme213 {
 
 void set_error(const char *fmt, ...);
 int cuda_fail(cudaError_t e, const char *what);
-// Returns a workspace of at least `bytes` (256-byte aligned), growing it if needed.
-int workspace(cme213_ctx *ctx, size_t bytes, void **out);
+// Returns a workspace of at least `bytes` (256-byte aligned), growing it if needed.  Every call shares the one
+// buffer: when the previous user ran on a different stream, `st` is first made to wait (event, no host sync) for
+// everything that user enqueued, so calls through one context from several streams do not trample each other's
+// descriptors.  Skipped while `st` is being captured (a wait on un-captured work would invalidate the capture):
+// there the caller orders its streams.  Growth synchronises the device and must happen outside a capture.
+int workspace(cme213_ctx *ctx, size_t bytes, void **out, cudaStream_t st);
 
 struct DeviceGuard {
     int prev;

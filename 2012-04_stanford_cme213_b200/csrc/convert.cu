@@ -120,7 +120,7 @@ int csr_to_ell_impl(cme213_ctx *ctx, int64_t num_rows, int64_t num_cols, const i
     if (chunk > pitch) chunk = pitch;
     void *ws = nullptr;
     const size_t idx_bytes = ((size_t)chunk * Kp * 4 + 255) & ~(size_t)255;
-    int rc = workspace(ctx, idx_bytes + (size_t)chunk * Kp * sizeof(T), &ws);
+    int rc = workspace(ctx, idx_bytes + (size_t)chunk * Kp * sizeof(T), &ws, st);
     if (rc) return rc;
     int32_t *stage_idx = (int32_t *)ws;
     T *stage_val = (T *)((char *)ws + idx_bytes);
@@ -155,7 +155,7 @@ CME213_API int cme213_hyb_pick_k(cme213_ctx *ctx, int64_t num_rows, const int32_
     cudaStream_t st = (cudaStream_t)stream;
     void *ws = nullptr;
     const size_t bytes = HIST_BINS * 8 + 256;
-    int rc = workspace(ctx, bytes, &ws);
+    int rc = workspace(ctx, bytes, &ws, st);
     if (rc) return rc;
     CME213_CUDA(cudaMemsetAsync(ws, 0, bytes, st));
     unsigned long long *d_hist = (unsigned long long *)ws;
@@ -205,7 +205,7 @@ static int csr_to_coo_tail_impl(cme213_ctx *ctx, int64_t num_rows, const int32_t
     const int64_t n = num_rows + 1;
     const size_t count_bytes = ((size_t)n * 4 + 255) & ~(size_t)255;
     void *ws = nullptr;
-    int rc = workspace(ctx, count_bytes + cme213_internal_scan_u32_scratch_bytes(n), &ws);
+    int rc = workspace(ctx, count_bytes + cme213_internal_scan_u32_scratch_bytes(n), &ws, st);
     if (rc) return rc;
     uint32_t *d_count = (uint32_t *)ws;
     tail_count_kernel<<<(unsigned)div_up(n, 256), 256, 0, st>>>(num_rows, d_row_ptr, K, d_count);
@@ -255,7 +255,7 @@ CME213_API int cme213_block_offsets_u32(cme213_ctx *ctx, const uint32_t *d_local
     const size_t t_bytes = ((size_t)total * 4 + 255) & ~(size_t)255;
     const size_t f_bytes = ((size_t)cme213_flag_words(total) * 4 + 255) & ~(size_t)255;
     void *ws = nullptr;
-    int rc = workspace(ctx, t_bytes + f_bytes + cme213_internal_segscan_u32_scratch_bytes(total), &ws);
+    int rc = workspace(ctx, t_bytes + f_bytes + cme213_internal_segscan_u32_scratch_bytes(total), &ws, st);
     if (rc) return rc;
     uint32_t *d_t = (uint32_t *)ws;
     uint32_t *d_flags = (uint32_t *)((char *)ws + t_bytes);

@@ -18,7 +18,23 @@ int cuda_fail(cudaError_t e, const char *what) {
     return e == cudaErrorMemoryAllocation ? CME213_ERR_ALLOC : CME213_ERR_CUDA;
 }
 
-int workspace(cme213_ctx *ctx, size_t bytes, void **out) {
+int workspace(cme213_ctx *ctx, size_t bytes, void **out, cudaStream_t st) {
+    if (ctx->ws_used && ctx->ws_stream != st) {
+        cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing(st, &cap) != cudaSuccess) { cudaGetLastError(); cap = cudaStreamCaptureStatusNone; }
+        if (cap == cudaStreamCaptureStatusNone) {
+            if (!ctx->ws_event) CME213_CUDA(cudaEventCreateWithFlags(&ctx->ws_event, cudaEventDisableTiming));
+            // everything the previous user enqueued on its stream (calls are serialised on the host, so it is all there)
+            if (cudaEventRecord(ctx->ws_event, ctx->ws_stream) == cudaSuccess) {
+                CME213_CUDA(cudaStreamWaitEvent(st, ctx->ws_event, 0));
+            } else {
+                cudaGetLastError();                      // the previous stream is gone (destroyed or mid-capture)
+                CME213_CUDA(cudaDeviceSynchronize());
+            }
+        }
+    }
+    ctx->ws_stream = st;
+    ctx->ws_used = true;
     if (bytes > ctx->ws_bytes) {
         // Growth path: only on first use or when a larger problem arrives.
         if (ctx->ws) {
@@ -37,7 +53,11 @@ int workspace(cme213_ctx *ctx, size_t bytes, void **out) {
 }  // namespace cme213
 
 CME213_API const char *cme213_last_error(void) { return cme213::g_err; }
-CME213_API int cme213_version(void) { return 100; }
+CME213_API int cme213_version(void) { return 200; }
+#ifndef CME213_SOURCE_HASH
+#define CME213_SOURCE_HASH "unknown"
+#endif
+CME213_API const char *cme213_build_id(void) { return CME213_SOURCE_HASH; }
 
 CME213_API int cme213_ctx_create(int device, cme213_ctx **out) {
     if (!out) { cme213::set_error("null out pointer"); return CME213_ERR_INVALID; }
@@ -63,6 +83,7 @@ CME213_API int cme213_ctx_destroy(cme213_ctx *ctx) {
     if (!ctx) return CME213_OK;
     cme213::DeviceGuard g(ctx->device);
     if (ctx->ws) cudaFree(ctx->ws);
+    if (ctx->ws_event) cudaEventDestroy(ctx->ws_event);
     free(ctx);
     return CME213_OK;
 }

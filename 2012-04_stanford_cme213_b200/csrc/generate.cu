@@ -13,7 +13,7 @@ using namespace cme213;
 // ---- scan of lengths held in d_row_ptr[0..rows] (last slot 0) -> CSR row pointers -----------------
 int lengths_to_row_ptr(cme213_ctx *ctx, int32_t *d_row_ptr, int64_t rows, int64_t *nnz_out, cudaStream_t st) {
     void *ws = nullptr;
-    int rc = workspace(ctx, cme213_internal_scan_u32_scratch_bytes(rows + 1), &ws);
+    int rc = workspace(ctx, cme213_internal_scan_u32_scratch_bytes(rows + 1), &ws, st);
     if (rc) return rc;
     rc = cme213_internal_exclusive_scan_u32(ctx, (const uint32_t *)d_row_ptr, (uint32_t *)d_row_ptr, rows + 1, ws, st);
     if (rc) return rc;

@@ -1002,7 +1002,7 @@ int launch_direct(cme213_ctx *ctx, const P &p, int64_t n, bool vec_ok, cudaStrea
     const int64_t tiles = div_up(n, (int64_t)THREADS * VECS * P::IPV);
     if (tiles > 0x7FFFFFFFLL) { set_error("%s: n too large", name); return CME213_ERR_UNSUPPORTED; }
     if (!scratch_mem) {
-        int rc = workspace(ctx, scratch_bytes(tiles, sizeof(T)), &scratch_mem);
+        int rc = workspace(ctx, scratch_bytes(tiles, sizeof(T)), &scratch_mem, st);
         if (rc) return rc;
     }
     CME213_CUDA(cudaMemsetAsync(scratch_mem, 0, scratch_bytes(tiles, sizeof(T)), st));
@@ -1041,7 +1041,7 @@ int launch_bulk(cme213_ctx *ctx, const P &p, int64_t n, cudaStream_t st, const c
     const int64_t waves = div_up(tiles, grid);
     const size_t bytes = wave_scratch_bytes(tiles, waves, sizeof(T));
     if (!scratch_mem) {
-        int rc = workspace(ctx, bytes, &scratch_mem);
+        int rc = workspace(ctx, bytes, &scratch_mem, st);
         if (rc) return rc;
     } else if (bytes > scratch_avail) {
         set_error("%s: scratch too small (%zu > %zu)", name, bytes, scratch_avail);
@@ -1050,7 +1050,11 @@ int launch_bulk(cme213_ctx *ctx, const P &p, int64_t n, cudaStream_t st, const c
     CME213_CUDA(cudaMemsetAsync(scratch_mem, 0, bytes, st));
     WaveScratch ws = wave_scratch_carve(scratch_mem, tiles, waves, sizeof(T));
     static unsigned long long *d_trace = nullptr;
+#ifdef CME213_TUNING   // per-phase trace of the persistent scan (scripts/trace_scan.sh): not in the shipped library
     const bool tracing = getenv("CME213_SCAN_TRACE") != nullptr;
+#else
+    constexpr bool tracing = false;
+#endif
     const size_t trace_words = (size_t)(grid + 1) * TRACE_MAX_IT * 8;
     if (tracing) {
         if (!d_trace) CME213_CUDA(cudaMalloc(&d_trace, (size_t)1024 * TRACE_MAX_IT * 8 * 8));
@@ -1079,7 +1083,7 @@ int launch_bulk(cme213_ctx *ctx, const P &p, int64_t n, cudaStream_t st, const c
         const char *nm[8] = {"", "wait_data", "local+S1", "pub+atomic", "scanner", "poll", "S2+cst", "store"};
         for (int k = 1; k < 8; k++) fprintf(stderr, " %s %.0f(n=%ld)", nm[k], cnt[k] ? sum[k] / cnt[k] : 0.0, cnt[k]);
         fprintf(stderr, "\n");
-        if (const char *path = getenv("CME213_SCAN_TRACE_FILE")) {
+        if (const char *path = tracing ? getenv("CME213_SCAN_TRACE_FILE") : nullptr) {
             FILE *f = fopen(path, "wb");
             if (f) {
                 long hdr[3] = {(long)grid + 1, (long)TRACE_MAX_IT, (long)waves};

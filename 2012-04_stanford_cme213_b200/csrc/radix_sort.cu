@@ -188,6 +188,7 @@ radix_scatter_kernel(const uint32_t *__restrict__ keys_in, uint32_t *__restrict_
             mm[d] = 0;
             slot = atomicAdd(&wh[d], (uint32_t)__popc(peers));
         }
+        __syncwarp();   // orders the leader's reset of mm[d] before the next item's atomicOr (a shuffle alone gives no memory ordering)
         slot = __shfl_sync(0xFFFFFFFFu, slot, leader);
         const uint32_t pos = slot + __popc(peers & lt);
         s_keys[pos] = key[i];
@@ -271,7 +272,7 @@ CME213_API int cme213_radix_sort_pass_u32(cme213_ctx *ctx, const uint32_t *d_key
     DeviceGuard g(ctx->device);
     const PassPlan p = plan_pass(n);
     void *ws = nullptr;
-    rc = workspace(ctx, p.total_bytes, &ws);
+    rc = workspace(ctx, p.total_bytes, &ws, (cudaStream_t)stream);
     if (rc) return rc;
     return run_pass(ctx, d_keys_in, d_keys_out, n, start_bit, num_bits, p, ws, (cudaStream_t)stream);
 }
@@ -289,7 +290,7 @@ CME213_API int cme213_radix_sort_u32(cme213_ctx *ctx, uint32_t *d_keys, uint32_t
     DeviceGuard g(ctx->device);
     const PassPlan p = plan_pass(n);
     void *ws = nullptr;
-    rc = workspace(ctx, p.total_bytes, &ws);
+    rc = workspace(ctx, p.total_bytes, &ws, (cudaStream_t)stream);
     if (rc) return rc;
     // Digits wider than 8 bits are split in two device passes: the sorted result does not depend on the digit width.
     const int bits = num_bits > 8 ? 8 : num_bits;
@@ -321,7 +322,7 @@ CME213_API int cme213_radix_sort_pairs_u32(cme213_ctx *ctx, uint32_t *d_keys, ui
     cudaStream_t st = (cudaStream_t)stream;
     const PassPlan p = plan_pass(n);
     void *ws = nullptr;
-    rc = workspace(ctx, p.total_bytes, &ws);
+    rc = workspace(ctx, p.total_bytes, &ws, (cudaStream_t)stream);
     if (rc) return rc;
     uint32_t *ks = d_keys, *kd = d_keys_tmp, *vs = d_vals, *vd = d_vals_tmp;
     int passes = 0;

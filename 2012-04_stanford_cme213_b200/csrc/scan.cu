@@ -265,6 +265,7 @@ __global__ void flags_from_offsets_kernel(const int32_t *__restrict__ s, int p, 
 template <class P>
 int run(cme213_ctx *ctx, const P &p, int64_t n, bool vec_ok, void *stream, const char *name) {
     DeviceGuard g(ctx->device);
+#ifdef CME213_TUNING   // tuning hooks (kernel-shape sweeps by environment variable): compiled out of the shipped library
     if constexpr (P::BULK) {
         if (const char *cfg = getenv("CME213_SCAN_CFG")) {  // tuning hook: "threads,vecs,-stages,defer" picks a blocked-kernel shape
             int T_ = 0, V_ = 0, S_ = 0, D_ = 1;
@@ -288,6 +289,7 @@ int run(cme213_ctx *ctx, const P &p, int64_t n, bool vec_ok, void *stream, const
 #undef CME213_TRY_DIRECT
         }
     }
+#endif
     return scan::launch<P>(ctx, p, n, vec_ok, (cudaStream_t)stream, name);
 }
 
@@ -440,6 +442,22 @@ CME213_API int cme213_exclusive_scan_u32_static(const uint32_t *d_in, uint32_t *
     int dev = -1;
     CME213_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64) { set_error("exclusive_scan_u32_static: device index %d not supported", dev); return CME213_ERR_UNSUPPORTED; }
+    // The scratch array used is the CURRENT device's copy, so the buffers have to live there too (a query, not an
+    // allocation): a buffer of another GPU would otherwise be scanned by a kernel running on the wrong device.
+    for (const void *p : {(const void *)d_in, (const void *)d_out}) {
+        cudaPointerAttributes at;
+        cudaError_t qe = cudaPointerGetAttributes(&at, p);
+        if (qe != cudaSuccess) { cudaGetLastError(); return cuda_fail(qe, "cudaPointerGetAttributes"); }
+        if (at.type == cudaMemoryTypeDevice && at.device != dev) {
+            set_error("exclusive_scan_u32_static: buffer %p lives on device %d but device %d is current; make the "
+                      "buffers' device current before the call", p, at.device, dev);
+            return CME213_ERR_INVALID;
+        }
+        if (at.type == cudaMemoryTypeUnregistered) {
+            set_error("exclusive_scan_u32_static: %p is not a device pointer", p);
+            return CME213_ERR_INVALID;
+        }
+    }
     if (!g_static_scan_ptr[dev]) {
         // set-up, first call on this device: resolve the device address of the array
         void *ptr = nullptr;

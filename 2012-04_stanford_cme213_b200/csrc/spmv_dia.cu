@@ -140,18 +140,22 @@ csr_to_dia_kernel(int64_t num_rows, const int32_t *__restrict__ row_ptr, const i
     unsigned long long miss = 0;
     for (int32_t e = row_ptr[r]; e < row_ptr[r + 1]; ++e) {
         const int n = find_offset(offsets, num_diags, (int32_t)(col[e] - r));
-        if (n < 0) ++miss; else data[(int64_t)n * pitch + r] = val[e];
+        if (n < 0) ++miss; else atomicAdd(&data[(int64_t)n * pitch + r], val[e]);   // data starts at zero: duplicates of (row, col) are summed
     }
     if (miss) atomicAdd(unmatched, miss);
 }
 
 // Which diagonals hold an entry: mark[(col - row) + (num_rows - 1)] = 1.
 __global__ void __launch_bounds__(256)
-mark_diagonals_kernel(int64_t num_rows, const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
-                      uint32_t *__restrict__ mark) {
+mark_diagonals_kernel(int64_t num_rows, int64_t num_cols, const int32_t *__restrict__ row_ptr,
+                      const int32_t *__restrict__ col, uint32_t *__restrict__ mark, unsigned int *__restrict__ bad) {
     const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= num_rows) return;
-    for (int32_t e = row_ptr[r]; e < row_ptr[r + 1]; ++e) mark[(int64_t)col[e] - r + (num_rows - 1)] = 1u;
+    for (int32_t e = row_ptr[r]; e < row_ptr[r + 1]; ++e) {
+        const int64_t c = col[e];
+        if (c < 0 || c >= num_cols) { atomicAdd(bad, 1u); continue; }   // malformed input: counted, never written
+        mark[c - r + (num_rows - 1)] = 1u;
+    }
 }
 // Stream compaction on the scan (slides/Lecture16.pdf slides 3-13): marked slot i goes to out[excl[i]].
 __global__ void __launch_bounds__(256)
@@ -331,7 +335,7 @@ int csr_to_dia_impl(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr,
     DeviceGuard g(ctx->device);
     cudaStream_t st = (cudaStream_t)stream;
     void *ws = nullptr;
-    int rc = workspace(ctx, 256, &ws);
+    int rc = workspace(ctx, 256, &ws, st);
     if (rc) return rc;
     unsigned long long *d_miss = (unsigned long long *)ws;
     CME213_CUDA(cudaMemsetAsync(d_miss, 0, 8, st));
@@ -386,12 +390,14 @@ CME213_API int cme213_csr_diagonals(cme213_ctx *ctx, int64_t num_rows, int64_t n
     const int64_t slots = num_rows + num_cols - 1;
     const size_t a_bytes = ((size_t)(slots + 1) * 4 + 255) & ~(size_t)255;   // one extra slot: its scan value is the count
     void *ws = nullptr;
-    int rc = workspace(ctx, 2 * a_bytes + cme213_internal_scan_u32_scratch_bytes(slots + 1), &ws);
+    int rc = workspace(ctx, 2 * a_bytes + 256 + cme213_internal_scan_u32_scratch_bytes(slots + 1), &ws, st);
     if (rc) return rc;
     uint32_t *mark = (uint32_t *)ws, *excl = (uint32_t *)((char *)ws + a_bytes);
-    void *scratch = (char *)ws + 2 * a_bytes;
+    unsigned int *bad = (unsigned int *)((char *)ws + 2 * a_bytes);
+    void *scratch = (char *)ws + 2 * a_bytes + 256;
     CME213_CUDA(cudaMemsetAsync(mark, 0, a_bytes, st));
-    mark_diagonals_kernel<<<(unsigned)div_up(num_rows, 256), 256, 0, st>>>(num_rows, d_row_ptr, d_col, mark);
+    CME213_CUDA(cudaMemsetAsync(bad, 0, 256, st));
+    mark_diagonals_kernel<<<(unsigned)div_up(num_rows, 256), 256, 0, st>>>(num_rows, num_cols, d_row_ptr, d_col, mark, bad);
     CME213_LAUNCHED(ctx, "mark_diagonals_kernel");
     rc = cme213_internal_exclusive_scan_u32(ctx, mark, excl, slots + 1, scratch, st);
     if (rc) return rc;
@@ -399,9 +405,14 @@ CME213_API int cme213_csr_diagonals(cme213_ctx *ctx, int64_t num_rows, int64_t n
         compact_diagonals_kernel<<<(unsigned)div_up(slots, 256), 256, 0, st>>>(slots, num_rows, mark, excl, d_offsets_out, max_diags);
         CME213_LAUNCHED(ctx, "compact_diagonals_kernel");
     }
-    uint32_t count = 0;
+    uint32_t count = 0, nbad = 0;
     CME213_CUDA(cudaMemcpyAsync(&count, excl + slots, 4, cudaMemcpyDeviceToHost, st));
+    CME213_CUDA(cudaMemcpyAsync(&nbad, bad, 4, cudaMemcpyDeviceToHost, st));
     CME213_CUDA(cudaStreamSynchronize(st));
+    if (nbad) {   // same rule as cme213_coo_to_csr_*: indices outside the matrix are an error, not silently dropped
+        set_error("csr_diagonals: %u column indices outside [0, %lld)", nbad, (long long)num_cols);
+        return CME213_ERR_INVALID;
+    }
     *num_diags_out = (int)count;
     return CME213_OK;
 }

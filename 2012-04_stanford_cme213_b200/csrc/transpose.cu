@@ -137,10 +137,10 @@ int transpose_impl(cme213_ctx *ctx, const void *d_in, void *d_out, int64_t rows,
     cme213::DeviceGuard g(ctx->device);
     cudaStream_t st = (cudaStream_t)stream;
     constexpr int V = 16 / sizeof(T);
-    // 16-byte vectors need aligned rows on both sides.  `cols` itself may be ragged as long as the
-    // input pitch covers the last vector (the extra lanes are loaded and then dropped).
+    // 16-byte vectors need aligned rows on both sides and whole vectors per row: a ragged `cols` would make the last
+    // load of the last row read past rows*ld_in-(ld_in-cols), which the header does not ask the caller to allocate.
     const bool vec_ok = cme213::aligned16(d_in) && cme213::aligned16(d_out) && rows % V == 0 &&
-                        (cols % V == 0 || ld_in >= ((cols + V - 1) / V) * V) && ld_in % V == 0 && ld_out % V == 0;
+                        cols % V == 0 && ld_in % V == 0 && ld_out % V == 0;
     if (vec_ok) {
         const int64_t tiles_r = cme213::div_up(rows, TILE_R), tiles_c = cme213::div_up(cols, TILE_BYTES_C / (int)sizeof(T));
         if (tiles_r * tiles_c > 0x7FFFFFFFLL || tiles_c > 0x7FFFFFFFLL) {

@@ -26,7 +26,35 @@ sys.path.insert(0, ROOT)
 PKG = "2012-04_stanford_cme213_b200"
 
 
-NCU_TRAFFIC_C5_BYTES = 15193800000  # 14.14 GB read + 1.05 GB written per csr_stream_lean_kernel<double> launch (profiles/r01_ncu_csr_stream_lean_f64_final.txt)
+# roofline.traffic is READ from the committed ncu summary of the dominant kernel (made by scripts/ncu_summary.py from an
+# `ncu --set full` capture of this command), never typed in: {workload: (file under profiles/, kernel-name fragment)}.
+NCU_SUMMARY = {"c5": ("ncu_c5_csr_kernel.txt", "csr_stream_lean_kernel<double")}
+
+
+def ncu_traffic(workload):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch, from profiles/<file>; None when the file is absent,
+    names another kernel or cannot be parsed (then the bench line says traffic: null rather than a stale figure)."""
+    if workload not in NCU_SUMMARY:
+        return None, None
+    fname, frag = NCU_SUMMARY[workload]
+    path = os.path.join(ROOT, "profiles", fname)
+    scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0, "Tbyte": 1e12}
+    try:
+        total, seen_kernel = 0.0, False
+        with open(path) as f:
+            for line in f:
+                t = line.split()
+                if line.startswith("kernel:"):
+                    if seen_kernel:
+                        break               # first kernel block only
+                    if frag not in line:
+                        return None, None
+                    seen_kernel = True
+                elif seen_kernel and t and t[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                    total += float(t[1]) * scale[t[2]]
+        return (total, "profiles/" + fname) if total > 0 else (None, None)
+    except Exception:
+        return None, None
 
 
 def log(*a):
@@ -167,7 +195,7 @@ def make_c5(ctx, torch, args, rank, world, dist):
     local_alg = nnz.value * 12 + (nloc + 1) * 4 + nloc * 8 * 2
     return dict(step=step, alg_bytes=alg, local_alg_bytes=local_alg, flops=2 * nnz_total, kernel="csr_stream_lean_kernel<double>",
                 launches_per_step=1 if it.mode not in ("halo", "p2p", "fused") else 2,
-                meta={"workload": "C5: CSR SpMV iteration, 3-D 7-point Laplacian %d^3, fp64, row-sharded over %d GPU(s)" % (g, world),
+                meta={"workload": C5_WORKLOAD % g, "sharding": "rows split over %d GPU(s)" % world,
                       "rows": rows, "nnz": nnz_total, "exchange": it.mode, "comm_bytes_per_rank_per_step": it.comm_bytes_per_step,
                       "launch": ("CUDA graph of two passes (kernels + NCCL %s)" % ({"p2p": "send/recv", "fused": "1-element all-reduce; halo pushed by the kernel"}.get(it.mode, "all-gather"))) if replay is not None else "eager",
                       "cta_order": ("z fastest inside strips of %d grid lines" % args.order_strip) if args.order_strip > 0 else "row order",
@@ -517,31 +545,31 @@ def time_steps(torch, step, steps, warmup, dist=None):
 # ---------------------------------------------------------------------------------------------------
 # CPU baseline (oracle = checker; timed here only as the reported baseline)
 # ---------------------------------------------------------------------------------------------------
-def cpu_baseline_c5(torch, wl, grid, budget_s=12.0):
-    """Reference-style CPU loop (csr_spmv of slides/Lecture22.pdf slide 20, OpenMP over rows) on a
-    bounded sample of the same matrix: the first planes of this rank's shard."""
+C5_WORKLOAD = "C5: CSR SpMV iteration, 3-D 7-point Laplacian %d^3, fp64"
+
+
+def cpu_baseline_c5(host, grid, budget_s=12.0):
+    """Reference-style CPU loop (csr_spmv of slides/Lecture22.pdf slide 20, OpenMP over rows) on the WHOLE matrix of the
+    workload -- the host copy the end-to-end leg uploads -- for about `budget_s` seconds of passes."""
     import numpy as np
     import oracle
-    lo, hi, d_ptr, d_col, d_val, nnz = wl["shard"]
-    planes = max(1, min(32, (hi - lo) // (grid * grid)))
-    rows = planes * grid * grid
-    ptr = d_ptr[:rows + 1].cpu().numpy()
-    n = int(ptr[-1])
-    col, val = d_col[:n].cpu().numpy(), d_val[:n].cpu().numpy()
-    x = np.random.default_rng(0).uniform(-1, 1, lo + rows + grid * grid + 1)
+    ptr, col, val = host["ptr"].numpy(), host["col"].numpy(), host["val"].numpy()
+    rows, n = len(ptr) - 1, len(col)
+    x = np.random.default_rng(0).uniform(-1, 1, rows)
+    y = np.empty_like(x)
     threads = oracle.num_threads()
-    oracle.csr_spmv(ptr, col, val, x, omp=True)  # warm-up
+    oracle.csr_spmv_into(ptr, col, val, x, y)  # warm-up
     reps, t0 = 0, time.perf_counter()
     while True:
-        oracle.csr_spmv(ptr, col, val, x, omp=True)
+        oracle.csr_spmv_into(ptr, col, val, x, y)
         reps += 1
         el = time.perf_counter() - t0
         if el > budget_s or reps >= 50:
             break
     alg = n * 12 + (rows + 1) * 4 + rows * 16
     return {"value": alg * reps / el / 1e9, "unit": "GB/s", "cores": threads, "kind": "port",
-            "sample": "first %d planes of the %d^3 grid (%d rows, %d nnz), %d passes, OpenMP over rows, %d threads"
-                      % (planes, grid, rows, n, reps, threads)}
+            "sample": "the whole %d^3 matrix (%d rows, %d nnz), %d passes in %.1f s, OpenMP over rows, %d threads"
+                      % (grid, rows, n, reps, el, threads)}
 
 
 def run_reference(args):
@@ -563,26 +591,32 @@ def run_reference(args):
         return run_reference_radixsort(args, np, oracle)
     if args.workload in ("scan", "fp", "transpose32", "transpose64"):
         return run_reference_primitive(args, np, oracle, g)
+    # C5 on the WHOLE matrix (13.9 GB on the host for 512^3): the same config as the GPU arm, one step = one pass y = A x
     grid = args.grid
-    planes = 32 if grid >= 32 else grid
-    rows = planes * grid * grid
-    ptr, col, val = g.laplace3d(grid, grid, grid, 0, rows)
-    x = np.random.default_rng(0).uniform(-1, 1, grid ** 3)
-    y_alg = len(col) * 12 + (rows + 1) * 4 + rows * 16
+    rows = grid ** 3
+    t_gen = time.perf_counter()
+    ptr, col, val = oracle.laplace3d_host(grid, grid, grid)
+    t_gen = time.perf_counter() - t_gen
+    x = np.random.default_rng(0).uniform(-1, 1, rows) * 0.05
+    y = np.empty_like(x)
+    alg = len(col) * 12 + (rows + 1) * 4 + rows * 16
     threads = oracle.num_threads()
     for _ in range(args.warmup):
-        oracle.csr_spmv(ptr, col, val, x, omp=True)
+        oracle.csr_spmv_into(ptr, col, val, x, y)
+        x, y = y, x
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        oracle.csr_spmv(ptr, col, val, x, omp=True)
+        oracle.csr_spmv_into(ptr, col, val, x, y)
+        x, y = y, x                                  # the ping-pong of pagerank.cu:128-132
     el = time.perf_counter() - t0
-    v = y_alg * args.steps / el / 1e9
-    sample = "each step = one SpMV over the first %d planes of the %d^3 grid (%d rows, %d nnz)" % (planes, grid, rows, len(col))
+    v = alg * args.steps / el / 1e9
+    sample = ("each step = one SpMV over the whole %d^3 matrix (%d rows, %d nnz), OpenMP over rows, %d threads; matrix built on "
+              "the host in %.1f s (untimed)" % (grid, rows, len(col), threads, t_gen))
     print(json.dumps({
         "impl": "reference", "metric": "spmv_algorithmic_gbs", "value": v, "unit": "GB/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": el / args.steps * 1e3, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "C5: CSR SpMV iteration, 3-D 7-point Laplacian %d^3, fp64 (CPU, bounded sample)" % grid},
+        "config": {"workload": C5_WORKLOAD % grid, "rows": rows, "nnz": len(col), "host": "CPU, whole matrix"},
         "cpu_baseline": {"value": v, "unit": "GB/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}), flush=True)
 
@@ -711,6 +745,7 @@ def e2e_c5(torch, pkg, wl, args, rank, world, dist):
         return e2e_c5_sharded(torch, pkg, wl, args, rank, world, dist, iters)
     pin = lambda t: t.cpu().pin_memory()
     h_ptr, h_col, h_val = pin(d_ptr), pin(d_col), pin(d_val)
+    wl["host"] = {"ptr": h_ptr, "col": h_col, "val": h_val}   # the CPU baseline runs on this same host copy
     h_x = torch.empty(rows_total, dtype=torch.float64).pin_memory()
     h_x.copy_(wl["keep"][3].cpu() if wl["keep"][3].numel() == rows_total else torch.rand(rows_total, dtype=torch.float64))
     h_x.mul_(1e-3)
@@ -851,8 +886,8 @@ def main():
     # dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel, from the committed
     # `ncu --set full` capture of this same command (profiles/r01_ncu_csr_stream_f64_*.txt); only valid for the
     # default single-GPU C5 workload
-    traffic = NCU_TRAFFIC_C5_BYTES if (args.workload == "c5" and world == 1 and args.grid == 512) else None
-    roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic,
+    traffic, traffic_src = ncu_traffic(args.workload) if (world == 1 and args.grid == 512) else (None, None)
+    roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic, "traffic_source": traffic_src,
             "kernel": wl["kernel"], "kernel_ms": kms, "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)" if peak_kind == "measured" else "fallback 6650 GB/s",
             "frac_of_8TBs_spec": ach / 8000.0, "gflops": wl["flops"] / max(world, 1) / (kms * 1e-3) / 1e9 if args.workload == "c5" else wl["flops"] / (kms * 1e-3) / 1e9}
 
@@ -862,14 +897,17 @@ def main():
            "data": "synthetic", "config": wl["meta"], "gflops": wl["flops"] / (ms_step * 1e-3) / 1e9,
            "roofline": roof, "gpu_launches": launches, "clocks": clocks}
 
-    if rank == 0 and args.workload == "c5" and not args.no_cpu and world == 1:
-        import oracle
-        oracle.build()
-        out["cpu_baseline"] = cpu_baseline_c5(torch, wl, args.grid)
     if args.workload == "c5" and not args.no_e2e:
         e = e2e_c5(torch, pkg, wl, args, rank, world, dist)
         if e is not None:
             out["e2e"] = e
+    if rank == 0 and args.workload == "c5" and not args.no_cpu and world == 1:
+        import oracle
+        oracle.build()
+        if "host" not in wl:
+            lo, hi, d_ptr, d_col, d_val, _ = wl["shard"]
+            wl["host"] = {"ptr": d_ptr.cpu(), "col": d_col.cpu(), "val": d_val.cpu()}
+        out["cpu_baseline"] = cpu_baseline_c5(wl["host"], args.grid)
     if world == 1 and args.extras and args.workload == "c5":
         others = []
         del wl

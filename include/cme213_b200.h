@@ -51,7 +51,16 @@ typedef struct cme213_ctx cme213_ctx;
 /* ---- context ---------------------------------------------------------- */
 /* Binds to a CUDA device and owns a scratch workspace that grows on demand
  * (cudaMalloc on first use / growth, never inside a steady-state loop).
- * reference: the callee-owns-device-memory rule of hw/hw1/programming/pagerank.cu:85-93. */
+ * reference: the callee-owns-device-memory rule of hw/hw1/programming/pagerank.cu:85-93.
+ * Sharing rules of that one workspace (scans, radix sort, format conversions, cme213_block_offsets_u32 and
+ * the generators that scan all keep their descriptors / tables in it):
+ *   - a context is driven by one host thread at a time;
+ *   - calls on different streams through the same context are ordered by the library: before a call re-uses the
+ *     workspace on another stream than the previous user's, that stream waits (event, no host sync) for what the
+ *     previous user enqueued.  This wait is skipped while the stream is being captured into a CUDA graph -- order
+ *     the streams yourself there, or give each stream its own context (contexts are cheap);
+ *   - growth (first use, or a larger problem than any before) calls cudaDeviceSynchronize + cudaFree + cudaMalloc:
+ *     run the largest problem once during set-up, outside any stream capture. */
 int cme213_ctx_create(int device, cme213_ctx **out);
 int cme213_ctx_destroy(cme213_ctx *ctx);
 int cme213_ctx_device(const cme213_ctx *ctx);
@@ -60,6 +69,9 @@ int cme213_ctx_sm_count(const cme213_ctx *ctx);
 int64_t cme213_ctx_launch_count(const cme213_ctx *ctx);
 const char *cme213_last_error(void);
 int cme213_version(void);
+/* Hash of the sources (csrc/, include/) this binary was built from; the Python binding refuses a library whose id
+ * differs from the sources beside it (the .so is a build artefact and could be stale). */
+const char *cme213_build_id(void);
 
 /* ---- transpose --------------------------------------------------------- */
 /* out[c*ld_out + r] = in[r*ld_in + c] for r < rows, c < cols (row-major, out of place).
@@ -85,6 +97,9 @@ int cme213_exclusive_scan_u32(cme213_ctx *ctx, const uint32_t *d_in, uint32_t *d
  * cudaFree or other allocating call.  Consequences:
  *   - n is limited to cme213_exclusive_scan_u32_static_max_n() = 2^28 elements; larger n returns
  *     CME213_ERR_UNSUPPORTED and touches nothing;
+ *   - every GPU has its own copy of the array and the call uses the copy of the CURRENT device: make the
+ *     device that holds d_in / d_out current (cudaSetDevice) before calling; buffers of another device are
+ *     refused with CME213_ERR_INVALID;
  *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress); make that
  *     first call during set-up, before any stream capture begins;
  *   - all calls on a device share the one array (each call clears the part it uses first), so two calls whose
@@ -254,11 +269,13 @@ int cme213_spmv_dia_f64(cme213_ctx *ctx, int64_t num_rows, int64_t num_cols, int
                         const int32_t *d_offsets, const double *d_data, const double *d_x, double *d_y, void *stream);
 /* The occupied diagonals (col - row) of a CSR matrix, ascending, by mark + exclusive scan + compaction
  * (slides/Lecture16.pdf slides 3-13).  *num_diags_out = how many there are (synchronises); at most max_diags of
- * them are written to d_offsets_out.  Scratch: 8 bytes per (num_rows + num_cols) in the context workspace. */
+ * them are written to d_offsets_out.  Column indices outside [0, num_cols) -> CME213_ERR_INVALID (as in
+ * cme213_coo_to_csr_*).  Scratch: 8 bytes per (num_rows + num_cols) in the context workspace. */
 int cme213_csr_diagonals(cme213_ctx *ctx, int64_t num_rows, int64_t num_cols, const int32_t *d_row_ptr,
                          const int32_t *d_col, int max_diags, int32_t *d_offsets_out, int *num_diags_out, void *stream);
 /* CSR -> DIA on the ascending offsets list d_offsets (num_diags * pitch elements are written, zero-filled).
- * *unmatched_out (may be NULL; non-NULL synchronises) = entries that lie on none of the listed diagonals. */
+ * *unmatched_out (may be NULL; non-NULL synchronises) = entries that lie on none of the listed diagonals.
+ * Duplicate (row, col) entries are summed (DIA has one slot per position). */
 int cme213_csr_to_dia_f32(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr, const int32_t *d_col,
                           const float *d_val, int num_diags, const int32_t *d_offsets, int64_t pitch, float *d_data,
                           int64_t *unmatched_out, void *stream);

@@ -604,3 +604,37 @@ ORACLE_API void oracle_error_norms(const double *a, const double *b, int64_t n, 
     out[2] = a2 > 0 ? sqrt(d2) / sqrt(a2) : 0;
     out[3] = ainf > 0 ? dinf / ainf : 0;
 }
+
+/* ---- generator restatement: the 7-point Laplacian rows of cme213_gen_laplace3d_f64 (csrc/generate.cu), built on the host
+ * with OpenMP so that bench.py's CPU arm can run config C5 on the WHOLE 512^3 matrix (938 M nonzeros) in seconds instead
+ * of the minutes numpy needs.  Same row layout as oracle/generators.py:laplace3d (legs -z,-y,-x,centre,+x,+y,+z; centre 6,
+ * neighbours -1; natural order, x fastest).  Two passes: row lengths -> serial prefix (the scan of radixsort.cpp:76-81) -> fill. */
+ORACLE_API int64_t oracle_gen_laplace3d_f64(int nx, int ny, int nz, int64_t row_begin, int64_t row_end, int32_t *ptr,
+                                            int32_t *indices, double *data) {
+    const int64_t plane = (int64_t)nx * ny, rows = row_end - row_begin;
+    if (rows <= 0) return 0;
+#pragma omp parallel for schedule(static)
+    for (int64_t t = 0; t < rows; t++) {
+        const int64_t i = row_begin + t;
+        const int ix = (int)(i % nx), iy = (int)((i / nx) % ny), iz = (int)(i / plane);
+        ptr[t + 1] = 1 + (iz > 0) + (iy > 0) + (ix > 0) + (ix < nx - 1) + (iy < ny - 1) + (iz < nz - 1);
+    }
+    ptr[0] = 0;
+    int64_t sum = 0;
+    for (int64_t t = 1; t <= rows; t++) { sum += ptr[t]; ptr[t] = (int32_t)sum; }
+    if (!indices || !data) return sum;
+#pragma omp parallel for schedule(static)
+    for (int64_t t = 0; t < rows; t++) {
+        const int64_t i = row_begin + t;
+        const int ix = (int)(i % nx), iy = (int)((i / nx) % ny), iz = (int)(i / plane);
+        int64_t e = ptr[t];
+        if (iz > 0) { indices[e] = (int32_t)(i - plane); data[e++] = -1.0; }
+        if (iy > 0) { indices[e] = (int32_t)(i - nx); data[e++] = -1.0; }
+        if (ix > 0) { indices[e] = (int32_t)(i - 1); data[e++] = -1.0; }
+        indices[e] = (int32_t)i; data[e++] = 6.0;
+        if (ix < nx - 1) { indices[e] = (int32_t)(i + 1); data[e++] = -1.0; }
+        if (iy < ny - 1) { indices[e] = (int32_t)(i + nx); data[e++] = -1.0; }
+        if (iz < nz - 1) { indices[e] = (int32_t)(i + plane); data[e++] = -1.0; }
+    }
+    return sum;
+}

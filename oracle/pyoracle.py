@@ -99,6 +99,28 @@ def csr_spmv(ptr, col, val, x, omp=False):
     return y
 
 
+def laplace3d_host(nx, ny, nz, row_begin=0, row_end=None):
+    """generators.laplace3d built by the C restatement (OpenMP): the same arrays, fast enough for the whole 512^3 grid."""
+    n = nx * ny * nz
+    row_end = n if row_end is None else row_end
+    rows = row_end - row_begin
+    L = lib()
+    L.oracle_gen_laplace3d_f64.restype = C.c_int64
+    ptr = np.empty(rows + 1, np.int32)
+    nnz = L.oracle_gen_laplace3d_f64(C.c_int(nx), C.c_int(ny), C.c_int(nz), C.c_int64(row_begin), C.c_int64(row_end), _p(ptr), None, None)
+    col, val = np.empty(nnz, np.int32), np.empty(nnz, np.float64)
+    L.oracle_gen_laplace3d_f64(C.c_int(nx), C.c_int(ny), C.c_int(nz), C.c_int64(row_begin), C.c_int64(row_end), _p(ptr), _p(col), _p(val))
+    return ptr, col, val
+
+
+def csr_spmv_into(ptr, col, val, x, y, omp=True):
+    """csr_spmv on preallocated, already contiguous arrays (no copies: for timing loops over multi-GB matrices)."""
+    f64 = val.dtype == np.float64
+    name = "oracle_csr_spmv_%s%s" % ("f64" if f64 else "f32", "_omp" if omp else "")
+    getattr(lib(), name)(C.c_int64(len(ptr) - 1), _p(ptr), _p(col), _p(val), _p(x), _p(y))
+    return y
+
+
 def csr_abs_bound(ptr, col, val, x):
     ptr, col = _c(ptr, np.int32), _c(col, np.int32)
     dt = np.float64 if np.asarray(val).dtype == np.float64 else np.float32

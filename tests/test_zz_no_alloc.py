@@ -43,3 +43,40 @@ def test_static_scan_rejects_sizes_beyond_its_scratch(cme):
     assert rc == cme.capi.ERR_UNSUPPORTED and b"exceeds" in lib.cme213_last_error()
     assert lib.cme213_exclusive_scan_u32_static(None, None, 0, None) == 0
     assert lib.cme213_exclusive_scan_u32_static(None, None, -1, None) == cme.capi.ERR_INVALID
+
+
+def test_static_scan_at_its_size_limit_allocates_nothing(cme, ctx):
+    """n = 2^28 is the largest input the built-in array can serve (its descriptors fill the array exactly).  After a
+    set-up call (which resolves the array's address and lets the driver load the kernel), further calls must leave the
+    device's free memory untouched: that is the whole point of the entry point for callers that cannot allocate."""
+    import torch
+    lib = cme.load()
+    n = int(lib.cme213_exclusive_scan_u32_static_max_n())
+    d_in, d_ref, d_out = dev_empty(n, np.uint32), dev_empty(n, np.uint32), dev_empty(n, np.uint32)
+    ctx.call("cme213_fill_hash_u32", d_in, n, 77, 0)              # full-range values: the sums wrap mod 2^32
+    ctx.call("cme213_exclusive_scan_u32", d_in, d_ref, n)
+    P = lambda t: C.c_void_p(t.data_ptr())
+    assert lib.cme213_exclusive_scan_u32_static(P(d_in), P(d_out), 4096, None) == 0   # set-up call on this device
+    torch.cuda.synchronize()
+    free_before = torch.cuda.mem_get_info()[0]                    # cudaMemGetInfo
+    for _ in range(2):                                            # two calls in a row share the array
+        d_out.zero_()
+        rc = lib.cme213_exclusive_scan_u32_static(P(d_in), P(d_out), n, None)
+        assert rc == 0, lib.cme213_last_error()
+        torch.cuda.synchronize()
+        assert torch.equal(d_out, d_ref)                          # bit-exact against the regular entry point
+    assert torch.cuda.mem_get_info()[0] == free_before            # nothing was allocated (or freed) by the calls
+    # size-independent property on the full range: out[i+1] - out[i] == in[i] (mod 2^32), out[0] == 0
+    assert int(d_out[0]) == 0
+    assert torch.equal(d_out[1:] - d_out[:-1], d_in[:-1])
+
+
+def test_static_scan_refuses_buffers_of_another_device(cme):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    lib = cme.load()
+    other = torch.zeros(1024, dtype=torch.int32, device="cuda:1")
+    torch.cuda.set_device(0)
+    rc = lib.cme213_exclusive_scan_u32_static(C.c_void_p(other.data_ptr()), C.c_void_p(other.data_ptr()), 1024, None)
+    assert rc == cme.capi.ERR_INVALID and b"device" in lib.cme213_last_error()
