@@ -12,7 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libcme213_b200.so")
-SOURCES = ["ctx.cu", "transpose.cu", "scan.cu", "spmv_csr.cu", "spmv_ell.cu", "spmv_dia.cu", "convert.cu", "radix_sort.cu", "coo_to_csr.cu", "generate.cu",
+SOURCES = ["ctx.cu", "transpose.cu", "scan.cu", "spmv_csr.cu", "spmv_ell.cu", "spmv_dia.cu", "convert.cu", "radix_sort.cu", "coo_to_csr.cu", "generate.cu", "sharded.cu",
            "host_api.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC,-fvisibility=hidden,-Wall", "-Xptxas", "-v"]
@@ -76,7 +76,8 @@ def build(force=False, verbose=False, tuning=False):
 
 
 DRIVERS = {"fp": ["fp_main.cpp", "matrix_io.cpp"], "pagerank": ["pagerank_main.cpp"],
-           "check_output": ["check_output_main.cpp", "matrix_io.cpp"], "radixsort": ["radixsort_main.cpp"]}
+           "check_output": ["check_output_main.cpp", "matrix_io.cpp"], "radixsort": ["radixsort_main.cpp"],
+           "csr_iterate": ["csr_iterate_main.cpp"]}
 
 
 def build_drivers(force=False):

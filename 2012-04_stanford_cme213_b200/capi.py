@@ -10,7 +10,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libcme213_b200.so")
 
 OK = 0
-ERR_INVALID, ERR_CUDA, ERR_ALLOC, ERR_UNSUPPORTED = -1, -2, -3, -4
+ERR_INVALID, ERR_CUDA, ERR_ALLOC, ERR_UNSUPPORTED, ERR_TIMEOUT = -1, -2, -3, -4, -5
+SHARD_AUTO, SHARD_HALO, SHARD_GATHER, SHARD_GATHER_SPLIT = 0, 1, 2, 3
 CSR_AUTO, CSR_SCALAR, CSR_VECTOR, CSR_STREAM, CSR_STREAM_PADDED = 0, 1, 2, 3, 4
 
 
@@ -63,6 +64,21 @@ PROTOTYPES = {
     "cme213_ipc_export": (_i, [_p, _p]),
     "cme213_ipc_open": (_i, [_p, C.POINTER(_p)]),
     "cme213_ipc_close": (_i, [_p]),
+    "cme213_partition_rows": (_i, [_i64, _i, _p, _i64, _p]),
+    "cme213_shard_create_f64": (_i, [_p, _i, _i, _i64, _p, _p, _p, _p, _i, C.POINTER(_p)]),
+    "cme213_shard_destroy": (_i, [_p]),
+    "cme213_shard_handle_bytes": (_i, []),
+    "cme213_shard_export": (_i, [_p, _p]),
+    "cme213_shard_connect": (_i, [_p, _p]),
+    "cme213_shard_connect_local": (_i, [C.POINTER(_p), _i]),
+    "cme213_shard_mode": (_i, [_p]),
+    "cme213_shard_rows": (_i, [_p, _pi64, _pi64]),
+    "cme213_shard_comm_bytes_per_step": (_i64, [_p]),
+    "cme213_shard_vector": (_p, [_p, _i]),
+    "cme213_shard_step": (_i, [_p, _i, _p]),
+    "cme213_shard_iterate": (_i, [_p, _i, _p]),
+    "cme213_shard_finish": (_i, [_p, _p]),
+    "cme213_csr_iterate_sharded_host_f64": (_i, [_i, _i64, _i64, _p, _p, _p, _p, _p, _i, _i, _pf]),
     "cme213_pagerank_propagate": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _p]),
     "cme213_spmv_ell_f32": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _p, _p]),
     "cme213_spmv_ell_f64": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _p, _p]),

@@ -163,6 +163,111 @@ int transpose_host(const void *h_in, void *h_out, int64_t rows, int64_t cols) {
 }
 }  // namespace
 
+// One process driving num_gpus devices: the sharded counterpart of csr_iterate_host (a C++ driver's entry point).
+CME213_API int cme213_csr_iterate_sharded_host_f64(int num_gpus, int64_t num_rows, int64_t nnz, const int32_t *h_row_ptr,
+                                                   const int32_t *h_col, const double *h_val, const double *h_x_input,
+                                                   double *h_x_result, int nr_iterations, int mode, float *kernel_ms_out) {
+    if (num_gpus < 1 || num_gpus > 64 || num_rows < 0 || nnz < 0 || nr_iterations < 0 || nr_iterations % 2 != 0) {
+        set_error("csr_iterate_sharded_host: bad sizes or odd iteration count");
+        return CME213_ERR_INVALID;
+    }
+    if (num_rows > 0 && (!h_row_ptr || !h_x_input || !h_x_result || (nnz > 0 && (!h_col || !h_val)))) {
+        set_error("csr_iterate_sharded_host: null pointer");
+        return CME213_ERR_INVALID;
+    }
+    if (kernel_ms_out) *kernel_ms_out = 0.f;
+    if (num_rows == 0) return CME213_OK;
+    int count = 0;
+    CME213_CUDA(cudaGetDeviceCount(&count));
+    if (num_gpus > count) { set_error("csr_iterate_sharded_host: %d GPUs asked for, %d visible", num_gpus, count); return CME213_ERR_INVALID; }
+    int prev_dev = 0;
+    cudaGetDevice(&prev_dev);
+    struct Rank {
+        cme213_ctx *ctx = nullptr;
+        cme213_shard *shard = nullptr;
+        cudaStream_t st = nullptr;
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        int32_t *d_ptr = nullptr, *d_col = nullptr;
+        double *d_val = nullptr;
+    };
+    std::vector<Rank> R(num_gpus);
+    std::vector<int64_t> bounds(num_gpus + 1);
+    std::vector<cme213_shard *> shards(num_gpus, nullptr);
+    int rc = cme213_partition_rows(num_rows, num_gpus, h_row_ptr, 128, bounds.data());
+    auto cleanup = [&]() {
+        for (int d = 0; d < num_gpus; d++) {
+            cudaSetDevice(d);
+            cudaDeviceSynchronize();
+        }
+        for (int d = 0; d < num_gpus; d++) {
+            cudaSetDevice(d);
+            cme213_shard_destroy(R[d].shard);
+            for (void *p : {(void *)R[d].d_ptr, (void *)R[d].d_col, (void *)R[d].d_val}) if (p) cudaFree(p);
+            if (R[d].e0) cudaEventDestroy(R[d].e0);
+            if (R[d].e1) cudaEventDestroy(R[d].e1);
+            if (R[d].st) cudaStreamDestroy(R[d].st);
+            cme213_ctx_destroy(R[d].ctx);
+        }
+        cudaGetLastError();
+        cudaSetDevice(prev_dev);
+    };
+#define STEP(expr) do { int _rc = (expr); if (_rc) { cleanup(); return _rc; } } while (0)
+#define STEP_CUDA(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) { int _rc = cuda_fail(_e, #call); cleanup(); return _rc; } } while (0)
+    STEP(rc);
+    std::vector<int32_t> rebased;
+    for (int d = 0; d < num_gpus; d++) {
+        STEP_CUDA(cudaSetDevice(d));
+        STEP(cme213_ctx_create(d, &R[d].ctx));
+        STEP_CUDA(cudaStreamCreateWithFlags(&R[d].st, cudaStreamNonBlocking));
+        STEP_CUDA(cudaEventCreate(&R[d].e0));
+        STEP_CUDA(cudaEventCreate(&R[d].e1));
+        const int64_t lo = bounds[d], hi = bounds[d + 1], n = hi - lo;
+        const int64_t e0 = h_row_ptr[lo], e1 = h_row_ptr[hi];
+        rebased.resize((size_t)n + 1);
+        for (int64_t i = 0; i <= n; i++) rebased[(size_t)i] = (int32_t)(h_row_ptr[lo + i] - e0);
+        STEP_CUDA(cudaMalloc(&R[d].d_ptr, ((size_t)n + 1) * 4));
+        STEP_CUDA(cudaMalloc(&R[d].d_col, (size_t)(e1 - e0 > 0 ? e1 - e0 : 1) * 4));
+        STEP_CUDA(cudaMalloc(&R[d].d_val, (size_t)(e1 - e0 > 0 ? e1 - e0 : 1) * 8));
+        STEP_CUDA(cudaMemcpy(R[d].d_ptr, rebased.data(), ((size_t)n + 1) * 4, cudaMemcpyHostToDevice));
+        if (e1 > e0) {
+            STEP_CUDA(cudaMemcpy(R[d].d_col, h_col + e0, (size_t)(e1 - e0) * 4, cudaMemcpyHostToDevice));
+            STEP_CUDA(cudaMemcpy(R[d].d_val, h_val + e0, (size_t)(e1 - e0) * 8, cudaMemcpyHostToDevice));
+        }
+        STEP(cme213_shard_create_f64(R[d].ctx, d, num_gpus, num_rows, bounds.data(), R[d].d_ptr, R[d].d_col, R[d].d_val, mode, &R[d].shard));
+        shards[d] = R[d].shard;
+        STEP_CUDA(cudaMemcpy(cme213_shard_vector(R[d].shard, 0), h_x_input, (size_t)num_rows * 8, cudaMemcpyHostToDevice));
+    }
+    STEP(cme213_shard_connect_local(shards.data(), num_gpus));
+    for (int d = 0; d < num_gpus; d++) { STEP_CUDA(cudaSetDevice(d)); STEP_CUDA(cudaDeviceSynchronize()); }
+    // the timed loop (pagerank.cu:118-134): every GPU runs its passes; a pass waits for its neighbours on the device,
+    // never on the host, so the launches of all GPUs are simply issued round-robin from this thread
+    for (int d = 0; d < num_gpus; d++) { STEP_CUDA(cudaSetDevice(d)); STEP_CUDA(cudaEventRecord(R[d].e0, R[d].st)); }
+    for (int it = 0; it < nr_iterations; it++) {
+        for (int d = 0; d < num_gpus; d++) STEP(cme213_shard_step(R[d].shard, it & 1, R[d].st));
+        if ((it & 63) == 63)   // bound the launch queues: a full queue on one GPU must not keep this thread from feeding the next
+            for (int d = 0; d < num_gpus; d++) { STEP_CUDA(cudaSetDevice(d)); STEP_CUDA(cudaStreamSynchronize(R[d].st)); }
+    }
+    for (int d = 0; d < num_gpus; d++) { STEP_CUDA(cudaSetDevice(d)); STEP_CUDA(cudaEventRecord(R[d].e1, R[d].st)); }
+    float worst = 0.f;
+    for (int d = 0; d < num_gpus; d++) {
+        STEP_CUDA(cudaSetDevice(d));
+        STEP(cme213_shard_finish(R[d].shard, R[d].st));
+        float ms = 0.f;
+        STEP_CUDA(cudaEventElapsedTime(&ms, R[d].e0, R[d].e1));
+        worst = ms > worst ? ms : worst;
+    }
+    if (kernel_ms_out) *kernel_ms_out = worst;
+    for (int d = 0; d < num_gpus; d++) {
+        STEP_CUDA(cudaSetDevice(d));
+        const int64_t lo = bounds[d], hi = bounds[d + 1];
+        if (hi > lo) STEP_CUDA(cudaMemcpy(h_x_result + lo, cme213_shard_vector(R[d].shard, 0) + lo, (size_t)(hi - lo) * 8, cudaMemcpyDeviceToHost));
+    }
+#undef STEP
+#undef STEP_CUDA
+    cleanup();
+    return CME213_OK;
+}
+
 CME213_API int cme213_pagerank_iterate_host(const uint32_t *h_graph_indices, const uint32_t *h_graph_edges,
                                             const float *h_nodes_input, float *h_nodes_result,
                                             const float *h_inv_edges_per_node, int nr_iterations, int num_elements,

@@ -15,3 +15,33 @@ int cme213_internal_pagerank_propagate_w(cme213_ctx *ctx, const uint32_t *d_grap
                                          const uint32_t *d_graph_edges, const float *d_nodes_in, const float *d_w_in,
                                          float *d_nodes_out, float *d_w_out, const float *d_inv, int array_length,
                                          void *stream);
+
+// ---- row-sharded iterate (sharded.cu drives it, the protocol runs inside spmv_csr.cu's stream kernel) --------------
+// Every rank keeps a small block of 64-bit words in its own memory: how many of its boundary CTAs have finished (per
+// side, counted up for ever), a status word, and one flag per neighbour that the NEIGHBOUR writes: "the halo rows of
+// my first `flag` passes have landed in your vector".  A boundary CTA of pass p first waits until the neighbour's flag
+// says p-1 (its rows of the previous pass are here, and -- because only boundary rows read ghost entries -- it has also
+// finished reading what this pass is about to overwrite), computes, stores its rows locally and into the neighbour's
+// vector, and the last boundary CTA of a side raises this rank's flag in the neighbour's memory to p.  The pass
+// number is not a kernel argument (a CUDA graph would freeze it): it is finished-CTAs / CTAs-per-side.
+struct ShardSync {
+    double *peer_lo, *peer_hi;                 // neighbours' output vectors, shifted like y (null = no neighbour)
+    int64_t push_lo_end, push_hi_begin;        // rows < push_lo_end go to peer_lo, rows >= push_hi_begin to peer_hi
+    int64_t side_lo_end, side_hi_begin;        // boundary rows of each side (they wait and are counted): the rows pushed or the rows
+                                               // that read ghost entries, whichever reaches further
+    unsigned long long *cnt_lo, *cnt_hi;       // local: boundary CTAs finished so far, per side
+    const unsigned long long *flag_lo, *flag_hi;   // local, written by the neighbours
+    unsigned long long *peer_flag_lo, *peer_flag_hi;   // this rank's flag word in each neighbour's memory
+    unsigned long long *status;                // local: set to 1 when a wait gave up (a neighbour died or never launched)
+    unsigned nb_lo, nb_hi;                     // boundary CTAs per side
+    long long timeout_cycles;
+};
+// x[dst] rows of this shard = A_shard x[src], halo rows pushed to the neighbours and flags raised as described above.
+// d_y / the peers are shifted so that index r is the shard's local row r; one kernel launch.
+int cme213_internal_spmv_csr_f64_shard(cme213_ctx *ctx, int64_t rows_local, const int32_t *d_row_ptr, const int32_t *d_col,
+                                       const double *d_val, const double *d_x, double *d_y, const ShardSync &sync,
+                                       cudaStream_t st);
+// y[r] += sum_j val[j] x[col[j]] (the remote-column block of a split shard; different rounding order than the unsplit row)
+int cme213_internal_spmv_csr_f64_acc(cme213_ctx *ctx, int64_t rows_local, const int32_t *d_row_ptr, const int32_t *d_col,
+                                     const double *d_val, const double *d_x, double *d_y, cudaStream_t st);
+int cme213_internal_shard_block_rows(void);

@@ -21,6 +21,7 @@
 // holds with zero slack.
 #include "internal.cuh"
 #include <stdlib.h>
+#include <type_traits>
 
 namespace {
 using namespace cme213;
@@ -30,7 +31,8 @@ __device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(
 __device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
 __device__ __forceinline__ double add_rn(double a, double b) { return __dadd_rn(a, b); }
 
-enum Mode { MODE_CSR = 0, MODE_PAGERANK = 1, MODE_PAGERANK_W = 2 };
+enum Mode { MODE_CSR = 0, MODE_PAGERANK = 1, MODE_PAGERANK_W = 2, MODE_CSR_ACC = 3 };   // ACC: y += A x (remote-column block of a sharded matrix)
+__host__ __device__ constexpr bool is_csr(int m) { return m == MODE_CSR || m == MODE_CSR_ACC; }
 
 template <typename T> struct Args {
     const int32_t *row_ptr;
@@ -48,22 +50,40 @@ template <typename T> struct Args {
     int64_t push_lo_end, push_hi_begin;
 };
 
+// ---- row-sharded iterate: the exchange protocol that lives inside the SpMV kernel (sharded.cu drives it) -----------
+// (struct ShardSync and the description of the protocol are in internal.cuh)
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __noinline__ void shard_wait(const unsigned long long *flag, unsigned long long want, const ShardSync &s) {
+    const long long t0 = clock64();
+    while (ld_acquire_sys(flag) < want) {
+        if (clock64() - t0 > s.timeout_cycles) { atomicExch(s.status, 1ull); break; }   // never hang the GPU: give up, flag it
+        __nanosleep(64);
+    }
+}
+
 template <typename T, int MODE>
 __device__ __forceinline__ T product(const Args<T> &a, T v, int c) {
-    if (MODE == MODE_CSR) return mul_rn(v, __ldg(a.x + c));
+    if (is_csr(MODE)) return mul_rn(v, __ldg(a.x + c));
     if (MODE == MODE_PAGERANK) return mul_rn(__ldg(a.x + c), __ldg(a.inv + c));
     return __ldg(a.x + c);
 }
 // same, with the gathered entries marked evict-last in L2 (stream kernel)
 template <typename T, int MODE>
 __device__ __forceinline__ T product_keep(const Args<T> &a, T v, int c, uint64_t pol) {
-    if (MODE == MODE_CSR) return mul_rn(v, ld_keep(a.x + c, pol));
+    if (is_csr(MODE)) return mul_rn(v, ld_keep(a.x + c, pol));
     if (MODE == MODE_PAGERANK) return mul_rn(ld_keep(a.x + c, pol), ld_keep(a.inv + c, pol));
     return ld_keep(a.x + c, pol);
 }
 template <typename T, int MODE>
 __device__ __forceinline__ void epilogue(const Args<T> &a, int64_t r, T sum) {
-    if (MODE == MODE_CSR) {
+    if (is_csr(MODE)) {
         st_stream(a.y + r, sum);
         // fused exchange: the halo rows go straight into the neighbours' memory over NVLink while the rest of the
         // launch is still computing (plain stores: peer addresses bypass the local L2)
@@ -86,7 +106,7 @@ csr_scalar_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
     T sum = T(0);
     const int e = a.row_ptr[r + 1];
     for (int j = a.row_ptr[r]; j < e; j++) {
-        const T v = MODE == MODE_CSR ? a.val[j] : T(0);
+        const T v = is_csr(MODE) ? a.val[j] : T(0);
         sum = add_rn(sum, product<T, MODE>(a, v, a.col[j]));
     }
     epilogue<T, MODE>(a, r, sum);
@@ -131,6 +151,8 @@ template <typename T, int MODE>
 __device__ __forceinline__ void epilogue_lean(const Args<T> &a, int64_t r, T sum) {
     if (MODE == MODE_CSR) {
         st_stream(a.y + r, sum);
+    } else if (MODE == MODE_CSR_ACC) {
+        a.y[r] = add_rn(a.y[r], sum);
     } else {
         const T out = add_rn(a.base, mul_rn(T(0.5), sum));
         a.y[r] = out;
@@ -141,17 +163,37 @@ __device__ __forceinline__ void epilogue_lean(const Args<T> &a, int64_t r, T sum
 // The plain fast path: rows in index order.  Deliberately minimal -- it compiles to 32 registers
 // (8 CTAs of 256 threads per SM); the feature-complete kernel below (block lists, padded products) needs 38-40
 // and measured 5-30 % slower on the same inputs, so it only runs when one of its features is asked for.
-template <typename T, int MODE, int THREADS, int TILE, bool PADDED>
+struct NoSync {};
+template <typename T, int MODE, int THREADS, int TILE, bool PADDED, bool SHARD = false>
 __global__ void __launch_bounds__(THREADS)
-csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
+csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename std::conditional<SHARD, ShardSync, NoSync>::type sync) {
     static_assert(TILE % (4 * THREADS) == 0, "tile must be a whole number of 4-wide vectors per thread");
     constexpr int PAD = 128 / (int)sizeof(T);   // PADDED: one pad element per 128 bytes (see the kernel below)
     auto pidx = [](int j) { return PADDED ? j + j / PAD : j; };
     __shared__ __align__(16) T prod[PADDED ? TILE + TILE / PAD : TILE];
     const int tid = threadIdx.x;
-    const int64_t r0 = row_begin + (int64_t)blockIdx.x * THREADS;
+    int64_t blk = blockIdx.x;
+    bool side_lo = false, side_hi = false;
+    if constexpr (SHARD) {
+        // boundary CTAs first (they are what the neighbours wait for): a rotation puts the last nb_hi row blocks in
+        // front, the first nb_lo follow, then the interior in row order.  Only boundary rows read ghost entries.
+        blk -= sync.nb_hi;
+        if (blk < 0) blk += gridDim.x;
+    }
+    const int64_t r0 = row_begin + blk * THREADS;
     const int64_t r = r0 + tid;
     const int64_t rl = r0 + THREADS < row_end ? r0 + THREADS : row_end;
+    if constexpr (SHARD) {
+        side_lo = sync.peer_lo != nullptr && r0 < sync.side_lo_end;
+        side_hi = sync.peer_hi != nullptr && rl > sync.side_hi_begin;
+        if (side_lo || side_hi) {
+            if (tid == 0) {
+                if (side_lo) shard_wait(sync.flag_lo, *(volatile unsigned long long *)sync.cnt_lo / sync.nb_lo, sync);
+                if (side_hi) shard_wait(sync.flag_hi, *(volatile unsigned long long *)sync.cnt_hi / sync.nb_hi, sync);
+            }
+            __syncthreads();
+        }
+    }
     int rs = 0, re = 0;
     if (r < row_end) {
         rs = a.row_ptr[r];
@@ -167,7 +209,7 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
             if (j + 4 <= b1) {
                 const int4 c = ld_stream(reinterpret_cast<const int4 *>(a.col + j));
                 V4<T> w;
-                if (MODE == MODE_CSR) w = V4<T>::load(a.val + j);
+                if (is_csr(MODE)) w = V4<T>::load(a.val + j);
                 else w = V4<T>{{T(0), T(0), T(0), T(0)}};
                 T p0 = product<T, MODE>(a, w.v[0], c.x);
                 T p1 = product<T, MODE>(a, w.v[1], c.y);
@@ -179,7 +221,7 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
 #pragma unroll
                 for (int t = 0; t < 4; t++)
                     if (j + t < b1) {
-                        const T vv = MODE == MODE_CSR ? a.val[j + t] : T(0);
+                        const T vv = is_csr(MODE) ? a.val[j + t] : T(0);
                         prod[pidx(o + t)] = product<T, MODE>(a, vv, a.col[j + t]);
                     }
             }
@@ -191,6 +233,28 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
         __syncthreads();
     }
     if (r < row_end) epilogue_lean<T, MODE>(a, r, sum);
+    if constexpr (SHARD) {
+        if (side_lo || side_hi) {
+            // the exchange, fused: halo rows go straight into the neighbour's vector over NVLink (peer addresses bypass
+            // the local L2), then the side's last CTA tells the neighbour that this pass has landed
+            if (r < row_end) {
+                if (side_lo && r < sync.push_lo_end) sync.peer_lo[r] = sum;
+                if (side_hi && r >= sync.push_hi_begin) sync.peer_hi[r] = sum;
+            }
+            __threadfence_system();
+            __syncthreads();
+            if (tid == 0) {
+                if (side_lo) {
+                    const unsigned long long done = atomicAdd(sync.cnt_lo, 1ull) + 1;
+                    if (done % sync.nb_lo == 0) { __threadfence_system(); st_release_sys(sync.peer_flag_lo, done / sync.nb_lo); }
+                }
+                if (side_hi) {
+                    const unsigned long long done = atomicAdd(sync.cnt_hi, 1ull) + 1;
+                    if (done % sync.nb_hi == 0) { __threadfence_system(); st_release_sys(sync.peer_flag_hi, done / sync.nb_hi); }
+                }
+            }
+        }
+    }
 }
 
 template <typename T, int MODE, int THREADS, int RPT, int TILE, bool PADDED, bool ORDERED = true, bool KEEP = true>
@@ -231,7 +295,7 @@ csr_stream_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
             if (j + 4 <= b1) {
                 const int4 c = ld_stream(reinterpret_cast<const int4 *>(a.col + j));
                 V4<T> w;
-                if (MODE == MODE_CSR) w = V4<T>::load(a.val + j);
+                if (is_csr(MODE)) w = V4<T>::load(a.val + j);
                 else w = V4<T>{{T(0), T(0), T(0), T(0)}};
                 T p0, p1, p2, p3;
                 if (KEEP) {
@@ -247,7 +311,7 @@ csr_stream_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
 #pragma unroll
                 for (int t = 0; t < 4; t++)
                     if (j + t < b1) {
-                        const T vv = MODE == MODE_CSR ? a.val[j + t] : T(0);
+                        const T vv = is_csr(MODE) ? a.val[j + t] : T(0);
                         prod[pidx(o + t)] = product<T, MODE>(a, vv, a.col[j + t]);
                     }
             }
@@ -299,7 +363,7 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
     const int lanes = (kernel >> 8) & 0xFF;
     bool padded = kind == CME213_CSR_STREAM_PADDED;
     if (padded) kind = CME213_CSR_STREAM;
-    if (kind == CME213_CSR_AUTO && MODE == MODE_CSR) {
+    if (kind == CME213_CSR_AUTO && is_csr(MODE)) {
         // inspector, once per (row_ptr, row range): mean row length decides between the two stream variants
         int rc = stream_variant_for(ctx, a.row_ptr, row_begin, row_end, st, &padded);
         if (rc) return rc;
@@ -313,7 +377,7 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
         csr_scalar_kernel<T, MODE><<<(unsigned)blocks, 256, 0, st>>>(a, row_begin, row_end);
         CME213_LAUNCHED(ctx, "csr_scalar_kernel");
     } else if (kind == CME213_CSR_VECTOR) {
-        if constexpr (MODE == MODE_CSR) {
+        if constexpr (is_csr(MODE)) {
             int G = lanes ? lanes : 8;
             if (G & (G - 1) || G < 2 || G > 32) { set_error("csr vector: lanes per row must be 2,4,8,16 or 32"); return CME213_ERR_INVALID; }
             const int64_t blocks = div_up(rows * G, 256);
@@ -340,8 +404,8 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
             else csr_stream_kernel<T, MODE, ORD_THREADS, 1, ORD_TILE, false, true><<<(unsigned)blocks, ORD_THREADS, 0, st>>>(a, row_begin, row_end);
         } else {
             const int64_t blocks = div_up(rows, THREADS);
-            if (padded) csr_stream_lean_kernel<T, MODE, THREADS, TILE, true><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end);
-            else csr_stream_lean_kernel<T, MODE, THREADS, TILE, false><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end);
+            if (padded) csr_stream_lean_kernel<T, MODE, THREADS, TILE, true><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end, NoSync());
+            else csr_stream_lean_kernel<T, MODE, THREADS, TILE, false><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end, NoSync());
         }
         CME213_LAUNCHED(ctx, "csr_stream_kernel");
     } else {
@@ -445,4 +509,32 @@ int cme213_internal_pagerank_propagate_w(cme213_ctx *ctx, const uint32_t *d_grap
     Args<float> a{(const int32_t *)d_graph_indices, (const int32_t *)d_graph_edges, nullptr, d_w_in, d_inv,
                   d_nodes_out, d_w_out, base, nullptr, nullptr, nullptr, 0, 0};
     return launch_csr<float, MODE_PAGERANK_W>(ctx, a, 0, array_length, CME213_CSR_STREAM, (cudaStream_t)stream);
+}
+
+// ---- internal entry points of the row-sharded iterate (sharded.cu) ---------------------------------------------------
+int cme213_internal_shard_block_rows(void) { return 128; }
+int cme213_internal_spmv_csr_f64_shard(cme213_ctx *ctx, int64_t rows_local, const int32_t *d_row_ptr, const int32_t *d_col,
+                                       const double *d_val, const double *d_x, double *d_y, const ShardSync &sync,
+                                       cudaStream_t st) {
+    if (rows_local <= 0) return CME213_OK;
+    DeviceGuard g(ctx->device);
+    Args<double> a{d_row_ptr, d_col, d_val, d_x, nullptr, d_y, nullptr, 0.0, nullptr, nullptr, nullptr, 0, 0};
+    constexpr int THREADS = 128, TILE = THREADS * 8;
+    const int64_t blocks = div_up(rows_local, THREADS);
+    if (blocks > 0x7FFFFFFFLL) { set_error("spmv_csr shard: too many rows"); return CME213_ERR_UNSUPPORTED; }
+    csr_stream_lean_kernel<double, MODE_CSR, THREADS, TILE, false, true><<<(unsigned)blocks, THREADS, 0, st>>>(a, 0, rows_local, sync);
+    CME213_LAUNCHED(ctx, "csr_stream_lean_kernel<shard>");
+    return CME213_OK;
+}
+int cme213_internal_spmv_csr_f64_acc(cme213_ctx *ctx, int64_t rows_local, const int32_t *d_row_ptr, const int32_t *d_col,
+                                     const double *d_val, const double *d_x, double *d_y, cudaStream_t st) {
+    if (rows_local <= 0) return CME213_OK;
+    DeviceGuard g(ctx->device);
+    Args<double> a{d_row_ptr, d_col, d_val, d_x, nullptr, d_y, nullptr, 0.0, nullptr, nullptr, nullptr, 0, 0};
+    constexpr int THREADS = 128, TILE = THREADS * 8;
+    const int64_t blocks = div_up(rows_local, THREADS);
+    if (blocks > 0x7FFFFFFFLL) { set_error("spmv_csr acc: too many rows"); return CME213_ERR_UNSUPPORTED; }
+    csr_stream_lean_kernel<double, MODE_CSR_ACC, THREADS, TILE, false><<<(unsigned)blocks, THREADS, 0, st>>>(a, 0, rows_local, NoSync());
+    CME213_LAUNCHED(ctx, "csr_stream_lean_kernel<acc>");
+    return CME213_OK;
 }

@@ -1,0 +1,96 @@
+// csr_iterate -- C++ driver of the row-sharded CSR iterate (config C5) on 1..8 GPUs of one box, one process.
+//
+//   csr_iterate [--gpus N] [--grid G] [--iters T] [--mode auto|halo|gather|split] [--check]
+//
+// Builds the 7-point Laplacian of a G^3 grid in CSR on the host (the matrix of the reference's stencil,
+// hw/hw2/programming/2dHeat.cu:361-366, as hw/hw5/programming/2dHeat.cpp distributes it in row stripes), runs T
+// passes x <- A x through cme213_csr_iterate_sharded_host_f64 -- host pointers in, host pointer out, the library owns
+// all device memory, exactly the contract of device_graph_iterate (hw/hw1/programming/pagerank.cu:85-143) -- and,
+// with --check, repeats them with the CPU loop and compares like the homework's main() does (pagerank.cu:209-239),
+// here bit for bit: row sharding keeps the order in which a row is summed.
+#include <omp.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <vector>
+#include "../../include/cme213_b200.h"
+
+static void cpu_pass(int64_t rows, const int32_t *ptr, const int32_t *col, const double *val, const double *x, double *y) {
+#pragma omp parallel for schedule(static)
+    for (int64_t r = 0; r < rows; r++) {
+        double s = 0.0;
+        for (int32_t e = ptr[r]; e < ptr[r + 1]; e++) s += val[e] * x[col[e]];   // slides/Lecture22.pdf slide 20
+        y[r] = s;
+    }
+}
+
+int main(int argc, char **argv) {
+    int gpus = 1, grid = 128, iters = 20, mode = CME213_SHARD_AUTO, check = 0;
+    for (int i = 1; i < argc; i++) {
+        if (!strcmp(argv[i], "--gpus") && i + 1 < argc) gpus = atoi(argv[++i]);
+        else if (!strcmp(argv[i], "--grid") && i + 1 < argc) grid = atoi(argv[++i]);
+        else if (!strcmp(argv[i], "--iters") && i + 1 < argc) iters = atoi(argv[++i]);
+        else if (!strcmp(argv[i], "--check")) check = 1;
+        else if (!strcmp(argv[i], "--mode") && i + 1 < argc) {
+            const char *m = argv[++i];
+            mode = !strcmp(m, "halo") ? CME213_SHARD_HALO : !strcmp(m, "gather") ? CME213_SHARD_GATHER
+                 : !strcmp(m, "split") ? CME213_SHARD_GATHER_SPLIT : CME213_SHARD_AUTO;
+        } else {
+            printf("usage: %s [--gpus N] [--grid G] [--iters T] [--mode auto|halo|gather|split] [--check]\n", argv[0]);
+            return 1;
+        }
+    }
+    if (gpus < 1 || grid < 2 || grid > 812 || iters < 0 || iters % 2) { printf("bad arguments (iters must be even, grid 2..812)\n"); return 1; }
+    const int64_t n = grid, plane = n * n, rows = n * n * n;
+    std::vector<int32_t> ptr((size_t)rows + 1);
+    ptr[0] = 0;
+    for (int64_t i = 0; i < rows; i++) {
+        const int64_t ix = i % n, iy = (i / n) % n, iz = i / plane;
+        ptr[(size_t)i + 1] = ptr[(size_t)i] + 1 + (iz > 0) + (iy > 0) + (ix > 0) + (ix < n - 1) + (iy < n - 1) + (iz < n - 1);
+    }
+    const int64_t nnz = ptr[(size_t)rows];
+    std::vector<int32_t> col((size_t)nnz);
+    std::vector<double> val((size_t)nnz), x((size_t)rows), y((size_t)rows);
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < rows; i++) {
+        const int64_t ix = i % n, iy = (i / n) % n, iz = i / plane;
+        int64_t e = ptr[(size_t)i];
+        if (iz > 0) { col[e] = (int32_t)(i - plane); val[e++] = -1.0; }
+        if (iy > 0) { col[e] = (int32_t)(i - n); val[e++] = -1.0; }
+        if (ix > 0) { col[e] = (int32_t)(i - 1); val[e++] = -1.0; }
+        col[e] = (int32_t)i; val[e++] = 6.0;
+        if (ix < n - 1) { col[e] = (int32_t)(i + 1); val[e++] = -1.0; }
+        if (iy < n - 1) { col[e] = (int32_t)(i + n); val[e++] = -1.0; }
+        if (iz < n - 1) { col[e] = (int32_t)(i + plane); val[e++] = -1.0; }
+        x[(size_t)i] = 0.05 * ((double)((uint32_t)(i * 2654435761u) >> 8) * (1.0 / 8388608.0) - 1.0);   // (-0.05, 0.05): 20 passes stay finite
+    }
+    float ms = 0.f;
+    int rc = cme213_csr_iterate_sharded_host_f64(gpus, rows, nnz, ptr.data(), col.data(), val.data(), x.data(), y.data(), iters, mode, &ms);
+    if (rc) { printf("cme213_csr_iterate_sharded_host_f64 failed: %s\n", cme213_last_error()); return 1; }
+    const double bytes = (double)nnz * 12 + (double)(rows + 1) * 4 + (double)rows * 16;
+    printf("gpu sharded csr iterate (%d GPUs) took %.3f ms for %d iterations\n", gpus, ms, iters);   // the timer line of mp1-util.h:37
+    if (iters > 0) printf("%.3f ms per pass, %.1f GB/s, %.1f GFLOP/s (rows %lld, nnz %lld)\n", ms / iters, bytes * iters / (ms * 1e-3) / 1e9,
+                          2.0 * nnz * iters / (ms * 1e-3) / 1e9, (long long)rows, (long long)nnz);
+    if (check) {
+        std::vector<double> a(x), b((size_t)rows);
+        for (int it = 0; it < iters; it += 2) {
+            cpu_pass(rows, ptr.data(), col.data(), val.data(), a.data(), b.data());
+            cpu_pass(rows, ptr.data(), col.data(), val.data(), b.data(), a.data());
+        }
+        int64_t diff = 0;
+        double worst = 0.0;
+        for (int64_t i = 0; i < rows; i++) {
+            if (memcmp(&a[(size_t)i], &y[(size_t)i], 8)) diff++;
+            const double d = a[(size_t)i] - y[(size_t)i], m = a[(size_t)i] < 0 ? -a[(size_t)i] : a[(size_t)i];
+            const double rel = (d < 0 ? -d : d) / (m > 1e-300 ? m : 1e-300);
+            worst = rel > worst ? rel : worst;
+        }
+        printf("check against the CPU loop: %lld of %lld elements differ bitwise, worst relative difference %.3e\n", (long long)diff,
+               (long long)rows, worst);
+        if (mode != CME213_SHARD_GATHER_SPLIT && diff) { printf("Test FAILED\n"); return 2; }
+        if (worst > 1e-9) { printf("Test FAILED\n"); return 2; }
+        printf("Test PASSED\n");
+    }
+    return 0;
+}

@@ -32,6 +32,79 @@ The iteration skeleton is the ping-pong loop of hw/hw1/programming/pagerank.cu:5
 import math
 
 
+def partition_rows(lib, rows, world, h_row_ptr=None, align=128):
+    """Row-block bounds (world + 1 entries) from the C ABI: balanced by nonzeros when the host row pointers (numpy
+    int32) are given, ceil(rows/world) rows each otherwise; rounded to `align` rows."""
+    import ctypes as C
+    out = (C.c_int64 * (world + 1))()
+    p = None if h_row_ptr is None else C.c_void_p(h_row_ptr.ctypes.data)
+    if lib.cme213_partition_rows(rows, world, p, align, out):
+        raise RuntimeError(lib.cme213_last_error().decode())
+    return list(out)
+
+
+class Shard:
+    """One rank's cme213_shard (csrc/sharded.cu): the row-sharded iterate behind the C ABI.  This class only moves the
+    export handles between the ranks (torch.distributed, any backend) and wraps the two device vectors; partition,
+    exchange protocol, kernels and ordering all live in the library -- a C++ host does the same with MPI or a pipe."""
+
+    def __init__(self, ctx, dist, rank, world, rows, bounds, d_row_ptr, d_col, d_val, mode=0):
+        import ctypes as C
+        import torch
+        self.ctx, self.lib, self.rank, self.world, self.rows = ctx, ctx.lib, rank, world, rows
+        self.keep = (d_row_ptr, d_col, d_val)
+        b = (C.c_int64 * (world + 1))(*bounds)
+        h = C.c_void_p()
+        self._check(self.lib.cme213_shard_create_f64(ctx.h, rank, world, rows, b, C.c_void_p(d_row_ptr.data_ptr()),
+                                                     C.c_void_p(d_col.data_ptr()), C.c_void_p(d_val.data_ptr()), mode, C.byref(h)))
+        self.h = h
+        self.lo, self.hi = bounds[rank], bounds[rank + 1]
+        if world > 1:
+            n = self.lib.cme213_shard_handle_bytes()
+            blob = C.create_string_buffer(n)
+            rc = self.lib.cme213_shard_export(self.h, blob)
+            mine = None if rc else blob.raw
+            err = self.lib.cme213_last_error().decode() if rc else None
+            everyone = [None] * world
+            dist.all_gather_object(everyone, mine)          # always reached: no rank is left waiting
+            if any(e is None for e in everyone):
+                raise RuntimeError(err or "a peer could not export its shard")
+            rc = self.lib.cme213_shard_connect(self.h, C.create_string_buffer(b"".join(everyone), n * world))
+            err = self.lib.cme213_last_error().decode() if rc else None
+            oks = [None] * world
+            dist.all_gather_object(oks, 0 if rc else 1)     # every rank learns whether all of them connected
+            if not all(oks):
+                raise RuntimeError(err or "a peer could not connect")
+        self.mode = int(self.lib.cme213_shard_mode(self.h))
+        self.comm_bytes_per_step = int(self.lib.cme213_shard_comm_bytes_per_step(self.h))
+        self.x = [torch.as_tensor(_RawCuda(self.lib.cme213_shard_vector(self.h, w), rows, "<f8"), device="cuda") for w in (0, 1)]
+
+    def _check(self, rc):
+        if rc:
+            raise RuntimeError("cme213 error %d: %s" % (rc, self.lib.cme213_last_error().decode()))
+
+    def _stream(self, stream):
+        import ctypes as C
+        import torch
+        st = torch.cuda.current_stream() if stream is None else stream
+        return C.c_void_p(st.cuda_stream)
+
+    def step(self, src, stream=None):
+        self._check(self.lib.cme213_shard_step(self.h, src, self._stream(stream)))
+
+    def iterate(self, nr_iterations, stream=None):
+        self._check(self.lib.cme213_shard_iterate(self.h, nr_iterations, self._stream(stream)))
+
+    def finish(self, stream=None):
+        self._check(self.lib.cme213_shard_finish(self.h, self._stream(stream)))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.x = None
+            self.lib.cme213_shard_destroy(self.h)
+            self.h = None
+
+
 def row_partition(rows, world):
     """[begin, end) of every rank: ceil(rows/world) rows each, the last ranks take what is left."""
     per = -(-rows // world)

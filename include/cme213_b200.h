@@ -36,6 +36,7 @@ extern "C" {
 #define CME213_ERR_CUDA (-2)        /* a CUDA runtime call or kernel launch failed */
 #define CME213_ERR_ALLOC (-3)       /* device or host allocation failed */
 #define CME213_ERR_UNSUPPORTED (-4) /* size beyond a documented limit */
+#define CME213_ERR_TIMEOUT (-5)     /* multi-GPU: a rank gave up waiting for a neighbour (cme213_shard_finish) */
 
 /* CSR kernel selection (cme213_spmv_csr_*).  reference: slides/Lecture22.pdf slides 20-26,
  * refs/Bell Tech Report 2008.pdf Figs. 20, 22. */
@@ -184,6 +185,63 @@ int cme213_ipc_handle_bytes(void);
 int cme213_ipc_export(const void *d_ptr, void *handle_out);
 int cme213_ipc_open(const void *handle, void **d_out);
 int cme213_ipc_close(void *d_ptr);
+
+/* ---- row-sharded iterate across the GPUs of one box (config C5) ------------------------------------------
+ * x <- A x repeated, A split into contiguous row blocks, one cme213_shard per GPU -- in one process
+ * (cme213_shard_connect_local) or one process per GPU (cme213_shard_export + cme213_shard_connect; the handles
+ * travel by any means the host has: MPI, torch.distributed, a pipe).  No NCCL and no host synchronisation on the
+ * data path; the ranks only have to run the same number of passes.
+ * reference: the 1-D stripe decomposition and the overlapped halo exchange of the reference's only distributed
+ * code, hw/hw5/programming/2dHeat.cpp:284-306 (decomposition), :696-723 (asyncComputation), :503-547 (exchange);
+ * the iteration itself is the ping-pong loop of hw/hw1/programming/pagerank.cu:59-67,128-132.
+ * Exchange modes: */
+#define CME213_SHARD_AUTO 0          /* HALO when every rank's columns stay inside its two neighbours' rows, else GATHER */
+#define CME213_SHARD_HALO 1          /* ONE kernel launch per pass: boundary rows first, stored into the neighbours' vectors
+                                        over NVLink by the kernel itself, ordered by flags in peer memory */
+#define CME213_SHARD_GATHER 2        /* any matrix: SpMV, then every rank copies its slice into every peer's vector */
+#define CME213_SHARD_GATHER_SPLIT 3  /* same exchange overlapped with the next pass's local-column block; the split
+                                        changes the summation order of a row (reduction-order tolerance, not bitwise);
+                                        uses a second stream of its own, so its steps cannot be stream-captured */
+/* HALO and GATHER leave the order in which a row is summed untouched: results are bitwise equal to one GPU. */
+typedef struct cme213_shard cme213_shard;
+/* Row block bounds (world + 1 entries, bounds[0] = 0, bounds[world] = num_rows) balanced by nonzeros when the HOST
+ * row pointers are given (NULL: ceil(rows/world) rows each as in 2dHeat.cpp:284-306), rounded to `align` rows. */
+int cme213_partition_rows(int64_t num_rows, int world, const int32_t *h_row_ptr, int64_t align, int64_t *bounds_out);
+/* One rank's part: rows [bounds[rank], bounds[rank+1]) as CSR with row pointers rebased to 0 and GLOBAL column
+ * indices (the arrays stay the caller's).  Allocates the two full-length ping-pong vectors and a small flag block
+ * (all exportable), and finds the ghost rows the block reads (synchronises). */
+int cme213_shard_create_f64(cme213_ctx *ctx, int rank, int world, int64_t num_rows_total, const int64_t *bounds,
+                            const int32_t *d_row_ptr_local, const int32_t *d_col, const double *d_val, int mode,
+                            cme213_shard **out);
+int cme213_shard_destroy(cme213_shard *shard);
+/* One process per GPU: every rank exports a handle of cme213_shard_handle_bytes() bytes, gathers everybody's
+ * handles in rank order and connects.  One process: pass all shards in rank order (peer access is enabled). */
+int cme213_shard_handle_bytes(void);
+int cme213_shard_export(cme213_shard *shard, void *handle_out);
+int cme213_shard_connect(cme213_shard *shard, const void *handles_of_all_ranks);
+int cme213_shard_connect_local(cme213_shard *const *shards_in_rank_order, int world);
+int cme213_shard_mode(const cme213_shard *shard);                       /* the mode in use after connecting */
+int cme213_shard_rows(const cme213_shard *shard, int64_t *row_begin, int64_t *row_end);
+int64_t cme213_shard_comm_bytes_per_step(const cme213_shard *shard);    /* bytes this rank sends per pass */
+/* Full-length vector 0 or 1 (device pointer).  Before the first step vector `src` must hold x on every rank --
+ * at least the rank's own rows and the ghost rows it reads.  Own rows of the result are [row_begin, row_end). */
+double *cme213_shard_vector(cme213_shard *shard, int which);
+/* vector[1-src] = A vector[src] for this rank's rows, exchange included; only enqueues work.  Every rank must
+ * call it the same number of times with the same src sequence.  The pass number lives in device memory, so a
+ * HALO / GATHER step can be captured into a CUDA graph and replayed. */
+int cme213_shard_step(cme213_shard *shard, int src, void *stream);
+/* nr_iterations (even) steps 0->1, 1->0, ...: the result ends in vector 0. */
+int cme213_shard_iterate(cme213_shard *shard, int nr_iterations, void *stream);
+/* Synchronises the stream and reports CME213_ERR_TIMEOUT if a wait for a neighbour gave up (~20 s).  Peers may
+ * still be writing GHOST rows of this rank's vectors afterwards: put a barrier of your own between finish and
+ * cme213_shard_destroy or a read of ghost rows. */
+int cme213_shard_finish(cme213_shard *shard, void *stream);
+/* Host-pointer twin for a C++ driver (one process, num_gpus devices 0..num_gpus-1): partitions by nonzeros, uploads
+ * each row block, runs nr_iterations (even) passes and gathers the result.  kernel_ms_out = the passes alone
+ * (max over the GPUs).  The sharded counterpart of cme213_csr_iterate_host_f64 / device_graph_iterate. */
+int cme213_csr_iterate_sharded_host_f64(int num_gpus, int64_t num_rows, int64_t nnz, const int32_t *h_row_ptr,
+                                        const int32_t *h_col, const double *h_val, const double *h_x_input,
+                                        double *h_x_result, int nr_iterations, int mode, float *kernel_ms_out);
 
 /* PageRank propagate: out[i] = 0.5f/N + 0.5f * sum_j in[e[j]] * inv[e[j]].
  * reference: hw/hw1/programming/pagerank.cu:45-56 (CPU), :70-83 (GPU). */

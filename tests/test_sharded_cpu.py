@@ -175,3 +175,19 @@ def test_fused_exchange_logic_matches_single_process(world, grid):
         p.join(120)
         assert p.exitcode == 0
     assert out.get(), "fused exchange result differs from the single-process oracle"
+
+
+def test_partition_rows_host_function():
+    """cme213_partition_rows is host code: bounds by nonzeros (binary search on the row pointers) or by rows."""
+    import ctypes as C
+    lib = pkg().load()
+    b = (C.c_int64 * 5)()
+    assert lib.cme213_partition_rows(1000, 4, None, 1, b) == 0 and list(b) == [0, 250, 500, 750, 1000]
+    assert lib.cme213_partition_rows(10, 4, None, 1, b) == 0 and list(b) == [0, 3, 6, 9, 10]      # ceil(rows/P) each, the rest to the last
+    lens = np.array([100] * 10 + [1] * 990)
+    ptr = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    assert lib.cme213_partition_rows(1000, 2, C.c_void_p(ptr.ctypes.data), 1, b) == 0
+    assert b[0] == 0 and b[2] == 1000 and abs(int(ptr[b[1]]) - int(ptr[-1]) // 2) <= 100
+    assert lib.cme213_partition_rows(1000, 3, C.c_void_p(ptr.ctypes.data), 128, b) == 0
+    assert all(v % 128 == 0 or v == 1000 for v in list(b)[:4]) and list(b)[:4] == sorted(list(b)[:4])
+    assert lib.cme213_partition_rows(-1, 2, None, 1, b) != 0
