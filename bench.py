@@ -157,10 +157,82 @@ def make_vectors(sh, ctx, torch, dist, rank, world, rows, halo, exchange):
     return xa, xb, None, exchange
 
 
+def make_c5_shard(ctx, torch, args, rank, world, dist):
+    """N > 1 through the C ABI's own sharded iterate (csrc/sharded.cu): one kernel launch per pass, halo rows stored into
+    the neighbours' vectors by that kernel, passes ordered by flags in peer memory -- no NCCL on the data path.  Python
+    only carries the export handles between the ranks and replays one CUDA graph per pass direction."""
+    import ctypes as C
+    sh = importlib.import_module(PKG + ".sharded")
+    g = args.grid
+    rows = g * g * g
+    bounds = sh.partition_rows(ctx.lib, rows, world, None, 256)       # the stencil's nonzeros are spread evenly: equal rows
+    lo, hi = bounds[rank], bounds[rank + 1]
+    nloc = hi - lo
+    nnz = C.c_int64()
+    d_ptr = i32(nloc + 1, torch)
+    ctx.call("cme213_gen_laplace3d_f64", g, g, g, lo, hi, d_ptr, None, None, C.byref(nnz))
+    d_col = i32(nnz.value, torch)
+    d_val = torch.empty(nnz.value, dtype=torch.float64, device="cuda")
+    ctx.call("cme213_gen_laplace3d_f64", g, g, g, lo, hi, d_ptr, d_col, d_val, C.byref(nnz))
+    shard = sh.Shard(ctx, dist, rank, world, rows, bounds, d_ptr, d_col, d_val, mode={"flags": 0, "gather": 2, "split": 3}[args.exchange])
+    xa, xb = shard.x
+    ctx.call("cme213_fill_uniform_f64", xa, rows, 9)
+    xa.mul_(0.05)
+    xb.zero_()
+    torch.cuda.synchronize()
+    dist.barrier()
+    state = {"src": 0}
+    graphs = None
+    if args.graph and shard.mode != 3:
+        shard.step(0); shard.step(1)             # eager pair first: kernels loaded, nothing left to set up inside the capture
+        shard.finish()
+        dist.barrier()
+        graphs = []
+        for src in (0, 1):
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr):
+                shard.step(src)
+            graphs.append(gr)
+        # the capture itself launches nothing, but keep every rank's pass counters in step: nothing to do
+        torch.cuda.synchronize()
+        dist.barrier()
+
+    def step():
+        if graphs is not None:
+            graphs[state["src"]].replay()
+        else:
+            shard.step(state["src"])
+        state["src"] = 1 - state["src"]
+
+    def kernel_step():   # the SpMV kernel alone on this rank's rows (roofline leg)
+        ctx.call("cme213_spmv_csr_f64", 0, nloc, d_ptr, d_col, d_val, xa, xb.data_ptr() + lo * 8, args.csr_kernel,
+                 stream=torch.cuda.current_stream())
+
+    modes = {1: "flags (halo rows stored into the neighbours' vectors by the SpMV kernel, ordered by flags in peer memory)",
+             2: "gather (peer copies of the whole slice to every rank)", 3: "gather_split (local-column block overlapped with the peer copies)"}
+    nnz_total = 7 * rows - 6 * g * g
+    alg = nnz_total * 12 + (rows + 1) * 4 + rows * 8 * 2
+    local_alg = nnz.value * 12 + (nloc + 1) * 4 + nloc * 8 * 2
+    return dict(step=step, alg_bytes=alg, local_alg_bytes=local_alg, flops=2 * nnz_total, kernel="csr_stream_lean_kernel<double>",
+                launches_per_step=1 if shard.mode == 1 else 3, kernel_step=kernel_step,
+                meta={"workload": C5_WORKLOAD % g, "sharding": "rows split over %d GPU(s)" % world,
+                      "rows": rows, "nnz": nnz_total, "exchange": modes[shard.mode], "comm_bytes_per_rank_per_step": shard.comm_bytes_per_step,
+                      "launch": "one CUDA graph per pass direction (1 kernel node each); C ABI cme213_shard_step" if graphs is not None else "eager cme213_shard_step",
+                      "cta_order": "boundary row blocks first, then row order",
+                      "l2": "working set %.1f GB per pass >> 126 MB L2" % (alg / 1e9)},
+                keep=(d_ptr, d_col, d_val, graphs), shard_obj=shard, state=state, shard=(lo, hi, d_ptr, d_col, d_val, nnz.value), ctx=ctx)
+
+
 def make_c5(ctx, torch, args, rank, world, dist):
     import ctypes as C
     pkg = importlib.import_module(PKG)
     sh = pkg.sharded if hasattr(pkg, "sharded") else importlib.import_module(PKG + ".sharded")
+    if world > 1 and args.exchange in ("flags", "gather", "split"):
+        try:
+            return make_c5_shard(ctx, torch, args, rank, world, dist)
+        except RuntimeError as e:   # raised on every rank together (Shard gathers the outcome): e.g. CUDA IPC refused
+            log("[bench] rank %d: C-ABI sharded iterate unavailable (%s); falling back to the NCCL-ordered fused exchange" % (rank, e))
+            args.exchange = "fused"
     g = args.grid
     rows = g * g * g
     lo, hi = sh.row_partition(rows, world)[rank]
@@ -193,8 +265,9 @@ def make_c5(ctx, torch, args, rank, world, dist):
     nnz_total = 7 * rows - 6 * g * g
     alg = nnz_total * 12 + (rows + 1) * 4 + rows * 8 * 2
     local_alg = nnz.value * 12 + (nloc + 1) * 4 + nloc * 8 * 2
+    kernel_step = lambda: it.spmv(it.lo, it.hi, it.x[0], it.x[1])
     return dict(step=step, alg_bytes=alg, local_alg_bytes=local_alg, flops=2 * nnz_total, kernel="csr_stream_lean_kernel<double>",
-                launches_per_step=1 if it.mode not in ("halo", "p2p", "fused") else 2,
+                launches_per_step=1 if it.mode not in ("halo", "p2p", "fused") else 2, kernel_step=kernel_step, state=state,
                 meta={"workload": C5_WORKLOAD % g, "sharding": "rows split over %d GPU(s)" % world,
                       "rows": rows, "nnz": nnz_total, "exchange": it.mode, "comm_bytes_per_rank_per_step": it.comm_bytes_per_step,
                       "launch": ("CUDA graph of two passes (kernels + NCCL %s)" % ({"p2p": "send/recv", "fused": "1-element all-reduce; halo pushed by the kernel"}.get(it.mode, "all-gather"))) if replay is not None else "eager",
@@ -781,6 +854,32 @@ def e2e_c5_sharded(torch, pkg, wl, args, rank, world, dist, iters):
     h_ptr, h_col, h_val = d_ptr.cpu().pin_memory(), d_col.cpu().pin_memory(), d_val.cpu().pin_memory()
     h_x = (torch.rand(rows, dtype=torch.float64) * 1e-3).pin_memory()
     h_y = torch.empty(hi - lo, dtype=torch.float64).pin_memory()
+    if "shard_obj" in wl:
+        # the C ABI's sharded iterate: the row block is uploaded into the arrays the shard was created on
+        shard = wl["shard_obj"]
+
+        def call():
+            d_ptr.copy_(h_ptr, non_blocking=True); d_col.copy_(h_col, non_blocking=True); d_val.copy_(h_val, non_blocking=True)
+            shard.x[0].copy_(h_x, non_blocking=True)
+            shard.iterate(iters)
+            h_y.copy_(shard.x[0][lo:hi], non_blocking=True)
+            shard.finish()
+
+        call()
+        calls = max(1, min(args.steps, 3))
+        dist.barrier(); torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(calls):
+            call()
+        dist.barrier()
+        el = time.perf_counter() - t0
+        t = torch.tensor([el], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        el = float(t.item())
+        h2d = h_ptr.numel() * 4 + h_col.numel() * 4 + h_val.numel() * 8 + rows * 8
+        return {"value": wl["alg_bytes"] * iters * calls / el / 1e9, "unit": "GB/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": (hi - lo) * 8,
+                "call": "per rank: pinned host row block + x -> device, cme213_shard_iterate(%d), result slice -> host" % iters,
+                "calls_timed": calls, "ms_per_call": el / calls * 1e3, "bytes_are": "per rank"}
     # device buffers of the call (allocated once: the host-pointer API keeps its workspace between calls)
     e_ptr, e_col, e_val = torch.empty_like(d_ptr), torch.empty_like(d_col), torch.empty_like(d_val)
     xa, xb, peers, exchange = make_vectors(sh, ctx, torch, dist, rank, world, rows, g * g, args.exchange)
@@ -812,6 +911,61 @@ def e2e_c5_sharded(torch, pkg, wl, args, rank, world, dist, iters):
             "calls_timed": calls, "ms_per_call": el / calls * 1e3, "bytes_are": "per rank"}
 
 
+def parity_c5(torch, ctx, wl, args, rank, world, dist, passes=6):
+    """N > 1, outside the timed region: the same `passes` iterations once through the sharded path and once on rank 0
+    ALONE over the whole matrix (single-GPU kernel), compared bit for bit.  Row sharding does not change the order in
+    which a row is summed, so anything but equality is a bug in the exchange."""
+    import ctypes as C
+    g = args.grid
+    rows = g ** 3
+    lo, hi = wl["shard"][0], wl["shard"][1]
+    shard = wl.get("shard_obj")
+    x0, x1 = (shard.x if shard is not None else wl["iterate"].x)
+    torch.cuda.synchronize()
+    dist.barrier()
+    ctx.call("cme213_fill_uniform_f64", x0, rows, 9)
+    x0.mul_(0.05)
+    x1.zero_()
+    torch.cuda.synchronize()
+    dist.barrier()
+    if shard is not None:
+        shard.iterate(passes)
+        shard.finish()
+        mode = wl["meta"]["exchange"].split(" ")[0]
+    else:
+        wl["iterate"].iterate(passes)
+        torch.cuda.synchronize()
+        mode = wl["iterate"].mode
+    dist.barrier()
+    sizes = [0] * world
+    dist.all_gather_object(sizes, hi - lo)
+    pieces = [torch.empty(n, dtype=torch.float64, device="cuda") for n in sizes]
+    dist.all_gather(pieces, x0[lo:hi].contiguous())
+    ok = None
+    if rank == 0:
+        got = torch.cat(pieces)
+        del pieces
+        nnz = C.c_int64()
+        p = i32(rows + 1, torch)
+        ctx.call("cme213_gen_laplace3d_f64", g, g, g, 0, rows, p, None, None, C.byref(nnz))
+        c, v = i32(nnz.value, torch), torch.empty(nnz.value, dtype=torch.float64, device="cuda")
+        ctx.call("cme213_gen_laplace3d_f64", g, g, g, 0, rows, p, c, v, C.byref(nnz))
+        a = torch.empty(rows, dtype=torch.float64, device="cuda")
+        ctx.call("cme213_fill_uniform_f64", a, rows, 9)
+        a.mul_(0.05)
+        b = torch.empty_like(a)
+        for _ in range(passes // 2):
+            ctx.call("cme213_spmv_csr_f64", 0, rows, p, c, v, a, b, 0)
+            ctx.call("cme213_spmv_csr_f64", 0, rows, p, c, v, b, a, 0)
+        torch.cuda.synchronize()
+        ok = bool(torch.equal(got, a))
+        del p, c, v, a, b, got
+        torch.cuda.empty_cache()
+    dist.barrier()
+    return {"bitwise_equal_to_1gpu": ok, "mode": mode, "passes": passes, "rows_compared": rows,
+            "how": "rank 0 recomputes the passes alone on the whole matrix with the single-GPU kernel; torch.equal on the gathered vector"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -820,8 +974,8 @@ def main():
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--workload", default="c5")
     ap.add_argument("--grid", type=int, default=512)
-    ap.add_argument("--exchange", default="fused", choices=["fused", "p2p", "halo", "full"],
-                    help="N>1: fused = the boundary launch stores the halo planes into the neighbours' vectors over peer memory (falls back to p2p when CUDA IPC or the shape does not allow it); p2p = NCCL send/recv of the halo planes between neighbours; halo = one all-gather of every rank's boundary planes; full = all-gather of the whole vector")
+    ap.add_argument("--exchange", default="flags", choices=["flags", "gather", "split", "fused", "p2p", "halo", "full"],
+                    help="N>1: flags (default) = the C ABI's sharded iterate: ONE launch per pass, the kernel stores the halo rows into the neighbours' vectors and the passes are ordered by flags in peer memory (no NCCL on the data path); gather / split = its whole-vector modes for general matrices.  The others are the round-1 torch.distributed paths, kept as fallbacks: fused = the boundary launch stores the halo planes into the neighbours' vectors over peer memory (falls back to p2p when CUDA IPC or the shape does not allow it); p2p = NCCL send/recv of the halo planes between neighbours; halo = one all-gather of every rank's boundary planes; full = all-gather of the whole vector")
     ap.add_argument("--csr-kernel", type=int, default=0)
     ap.add_argument("--graph", type=int, default=1, help="N>1: replay a CUDA graph of two passes instead of launching eagerly")
     ap.add_argument("--order-strip", type=int, default=0, help="C5: CTA order = z fastest inside strips of this many grid lines (0 = row order)")
@@ -831,6 +985,7 @@ def main():
     ap.add_argument("--extras", type=int, default=1, help="also time the other single-GPU configs (N=1 only)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="N>1: skip the bitwise comparison with rank 0's single-GPU recomputation")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
 
@@ -855,8 +1010,8 @@ def main():
     peak, peak_kind = measured_peak()
 
     wl = build_workload(args.workload, ctx, torch, args, rank, world, dist)
-    if world > 1 and args.workload == "c5" and args.graph:
-        args.steps += args.steps % 2      # a graph replay is a pair of passes
+    if world > 1 and args.workload == "c5" and args.graph and "shard_obj" not in wl:
+        args.steps += args.steps % 2      # NCCL fallback modes: a graph replay is a pair of passes
         args.warmup += args.warmup % 2
     torch.cuda.synchronize()
     sampler = ClockSampler(local)
@@ -875,10 +1030,7 @@ def main():
     # average duration, timed alone with CUDA events on its launch stream
     roof = None
     if args.workload == "c5":
-        it = wl["iterate"]
-        xin, xout = it.x[0], it.x[1]
-        kstep = lambda: it.spmv(it.lo, it.hi, xin, xout)
-        kms = time_steps(torch, kstep, args.steps, 3) / args.steps
+        kms = time_steps(torch, wl["kernel_step"], args.steps, 3) / args.steps
         ach = wl["local_alg_bytes"] / (kms * 1e-3) / 1e9
     else:
         kms = ms_step
@@ -897,6 +1049,9 @@ def main():
            "data": "synthetic", "config": wl["meta"], "gflops": wl["flops"] / (ms_step * 1e-3) / 1e9,
            "roofline": roof, "gpu_launches": launches, "clocks": clocks}
 
+    if args.workload == "c5" and world > 1 and not args.no_parity:
+        par = parity_c5(torch, ctx, wl, args, rank, world, dist)
+        out["parity"] = par
     if args.workload == "c5" and not args.no_e2e:
         e = e2e_c5(torch, pkg, wl, args, rank, world, dist)
         if e is not None:

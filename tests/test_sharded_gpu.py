@@ -86,7 +86,7 @@ def test_general_matrix_gather_modes(cme, mode):
     y = np.empty_like(x)
     P = lambda a: C.c_void_p(a.ctypes.data)
     rc = lib.cme213_csr_iterate_sharded_host_f64(2, rows, len(col), P(ptr), P(col), P(val), P(x), P(y), 2, HALO, None)
-    assert rc == cme.capi.ERR_UNSUPPORTED              # asked for HALO on a matrix it cannot serve: refused, not wrong
+    assert rc == cme.capi.ERR_UNSUPPORTED, lib.cme213_last_error()   # asked for HALO on a matrix it cannot serve: refused, not wrong
 
 
 def test_skewed_rows_are_balanced_by_nonzeros_and_stay_bitwise(cme):
