@@ -12,7 +12,8 @@ LIB_PATH = os.path.join(HERE, "libcme213_b200.so")
 OK = 0
 ERR_INVALID, ERR_CUDA, ERR_ALLOC, ERR_UNSUPPORTED, ERR_TIMEOUT = -1, -2, -3, -4, -5
 SHARD_AUTO, SHARD_HALO, SHARD_GATHER, SHARD_GATHER_SPLIT = 0, 1, 2, 3
-CSR_AUTO, CSR_SCALAR, CSR_VECTOR, CSR_STREAM, CSR_STREAM_PADDED = 0, 1, 2, 3, 4
+CSR_AUTO, CSR_SCALAR, CSR_VECTOR, CSR_STREAM, CSR_STREAM_PADDED, CSR_STREAM_KEEP, CSR_BINNED = 0, 1, 2, 3, 4, 5, 6
+FORMAT_CSR, FORMAT_ELL, FORMAT_HYB = 0, 1, 2
 
 
 def csr_vector(lanes):
@@ -54,6 +55,16 @@ PROTOTYPES = {
     "cme213_mul_gather_segscan_f64": (_i, [_p, _p, _p, _p, _p, _p, _i64, _p]),
     "cme213_spmv_csr_f32": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _i, _p]),
     "cme213_spmv_csr_f64": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _i, _p]),
+    "cme213_csr_plan_create": (_i, [_p, _i64, _i64, _i64, _p, _i, _p, C.POINTER(_p)]),
+    "cme213_csr_plan_destroy": (_i, [_p]),
+    "cme213_csr_plan_kernel": (_i, [_p]),
+    "cme213_csr_plan_describe": (C.c_char_p, [_p]),
+    "cme213_spmv_csr_plan_f32": (_i, [_p, _p, _p, _p, _p, _p, _p, _p]),
+    "cme213_spmv_csr_plan_f64": (_i, [_p, _p, _p, _p, _p, _p, _p, _p]),
+    "cme213_spmv_pick_format": (_i, [_p, _i64, _p, _p, _p]),
+    "cme213_spmv_hyb_csrtail_f32": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "cme213_spmv_hyb_csrtail_f64": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "cme213_csr_tail_row_ptr": (_i, [_p, _i64, _p, _i, _p, _pi64, _p]),
     "cme213_spmv_csr_block_rows": (_i, []),
     "cme213_spmv_csr_f32_ordered": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _p, _i64, _p]),
     "cme213_spmv_csr_f64_ordered": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _p, _i64, _p]),
@@ -178,6 +189,11 @@ def ptr(t):
     if hasattr(t, "ctypes"):
         return C.c_void_p(t.ctypes.data)
     raise TypeError("cannot take the address of %r" % type(t))
+
+
+class FormatChoice(C.Structure):
+    _fields_ = [("format", C.c_int), ("K", C.c_int), ("max_row", C.c_int), ("mean_row", C.c_double),
+                ("ell_padding_ratio", C.c_double), ("tail_fraction", C.c_double), ("cost_vs_csr", C.c_double)]
 
 
 class Context:

@@ -19,7 +19,7 @@ struct cme213_ctx {
     int64_t launches;  // kernels launched through this context
     // CSR AUTO decisions (spmv_csr.cu), remembered per (row_ptr, row range)
     static constexpr int CSR_CACHE = 16;
-    struct CsrChoice { const int32_t *row_ptr; int64_t row_begin, row_end; bool padded; };
+    struct CsrChoice { const int32_t *row_ptr; int64_t row_begin, row_end; cme213_csr_plan *plan; };   // plans owned by the context
     CsrChoice csr_cache[CSR_CACHE];
     unsigned csr_cache_next;
 };

@@ -11,7 +11,7 @@
 namespace {
 using namespace cme213;
 
-constexpr int HIST_BINS = 4096;
+constexpr int HIST_BINS = CME213_HIST_BINS;
 
 __global__ void row_length_hist_kernel(int64_t num_rows, const int32_t *__restrict__ row_ptr,
                                        unsigned long long *hist, int *max_len) {
@@ -144,15 +144,10 @@ int csr_to_ell_impl(cme213_ctx *ctx, int64_t num_rows, int64_t num_cols, const i
 
 CME213_API int64_t cme213_ell_pitch(int64_t num_rows) { return (num_rows + 63) & ~(int64_t)63; }
 
-CME213_API int cme213_hyb_pick_k(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr, int *K_out,
-                                 int *max_len_out, void *stream) {
-    CME213_CHECK_CTX(ctx);
-    if (num_rows < 0 || !K_out || (num_rows > 0 && !d_row_ptr)) { set_error("hyb_pick_k: bad arguments"); return CME213_ERR_INVALID; }
-    *K_out = 0;
-    if (max_len_out) *max_len_out = 0;
-    if (num_rows == 0) return CME213_OK;
-    DeviceGuard g(ctx->device);
-    cudaStream_t st = (cudaStream_t)stream;
+// Row-length histogram of rows [0, num_rows) of d_row_ptr (bin HIST_BINS-1 collects everything longer) and the longest
+// row; synchronises the stream.  Shared by the HYB split rule, the CSR dispatcher and the format chooser (csr_plan.cu).
+int cme213_internal_row_length_hist(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr, unsigned long long *h_hist,
+                                    int *max_len_out, cudaStream_t st) {
     void *ws = nullptr;
     const size_t bytes = HIST_BINS * 8 + 256;
     int rc = workspace(ctx, bytes, &ws, st);
@@ -163,11 +158,25 @@ CME213_API int cme213_hyb_pick_k(cme213_ctx *ctx, int64_t num_rows, const int32_
     int blocks = (int)(div_up(num_rows, 256) < (int64_t)ctx->sm_count * 8 ? div_up(num_rows, 256) : (int64_t)ctx->sm_count * 8);
     row_length_hist_kernel<<<blocks, 256, 0, st>>>(num_rows, d_row_ptr, d_hist, d_max);
     CME213_LAUNCHED(ctx, "row_length_hist_kernel");
+    CME213_CUDA(cudaMemcpyAsync(h_hist, d_hist, HIST_BINS * 8, cudaMemcpyDeviceToHost, st));
+    CME213_CUDA(cudaMemcpyAsync(max_len_out, d_max, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CME213_CUDA(cudaStreamSynchronize(st));
+    return CME213_OK;
+}
+
+CME213_API int cme213_hyb_pick_k(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr, int *K_out,
+                                 int *max_len_out, void *stream) {
+    CME213_CHECK_CTX(ctx);
+    if (num_rows < 0 || !K_out || (num_rows > 0 && !d_row_ptr)) { set_error("hyb_pick_k: bad arguments"); return CME213_ERR_INVALID; }
+    *K_out = 0;
+    if (max_len_out) *max_len_out = 0;
+    if (num_rows == 0) return CME213_OK;
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
     std::vector<unsigned long long> hist(HIST_BINS);
     int max_len = 0;
-    CME213_CUDA(cudaMemcpyAsync(hist.data(), d_hist, HIST_BINS * 8, cudaMemcpyDeviceToHost, st));
-    CME213_CUDA(cudaMemcpyAsync(&max_len, d_max, sizeof(int), cudaMemcpyDeviceToHost, st));
-    CME213_CUDA(cudaStreamSynchronize(st));
+    int rc = cme213_internal_row_length_hist(ctx, num_rows, d_row_ptr, hist.data(), &max_len, st);
+    if (rc) return rc;
     // SC09 section 3.5: add the K-th ELL column while at least max(4096, M/3) rows have >= K entries.
     const unsigned long long thresh = (unsigned long long)(num_rows / 3 > 4096 ? num_rows / 3 : 4096);
     unsigned long long ge = 0;  // rows with length >= l, walking l downward
@@ -224,6 +233,32 @@ static int csr_to_coo_tail_impl(cme213_ctx *ctx, int64_t num_rows, const int32_t
         tail_fill_kernel<T><<<(unsigned)div_up(num_rows * 32, 256), 256, 0, st>>>(num_rows, d_row_ptr, d_col, d_val, K, d_count,
                                                                                      d_coo_row, d_coo_col, d_coo_val);
         CME213_LAUNCHED(ctx, "tail_fill_kernel");
+    }
+    return CME213_OK;
+}
+
+// Row pointers of the tail (entries at in-row position >= K) as a CSR matrix of its own: tail_ptr = exclusive scan of
+// max(len - K, 0).  Its column / value arrays are the d_coo_col / d_coo_val of cme213_csr_to_coo_tail_* (same order).
+CME213_API int cme213_csr_tail_row_ptr(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr, int K,
+                                       int32_t *d_tail_ptr, int64_t *tail_nnz_out, void *stream) {
+    CME213_CHECK_CTX(ctx);
+    if (num_rows < 0 || K < 0 || !d_tail_ptr || (num_rows > 0 && !d_row_ptr)) { set_error("csr_tail_row_ptr: bad arguments"); return CME213_ERR_INVALID; }
+    if (tail_nnz_out) *tail_nnz_out = 0;
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t n = num_rows + 1;
+    void *ws = nullptr;
+    int rc = workspace(ctx, cme213_internal_scan_u32_scratch_bytes(n), &ws, st);
+    if (rc) return rc;
+    tail_count_kernel<<<(unsigned)div_up(n, 256), 256, 0, st>>>(num_rows, d_row_ptr, K, (uint32_t *)d_tail_ptr);
+    CME213_LAUNCHED(ctx, "tail_count_kernel");
+    rc = cme213_internal_exclusive_scan_u32(ctx, (uint32_t *)d_tail_ptr, (uint32_t *)d_tail_ptr, n, ws, stream);
+    if (rc) return rc;
+    if (tail_nnz_out) {
+        uint32_t total = 0;
+        CME213_CUDA(cudaMemcpyAsync(&total, d_tail_ptr + num_rows, 4, cudaMemcpyDeviceToHost, st));
+        CME213_CUDA(cudaStreamSynchronize(st));
+        *tail_nnz_out = (int64_t)total;
     }
     return CME213_OK;
 }

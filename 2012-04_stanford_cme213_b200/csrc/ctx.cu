@@ -82,6 +82,7 @@ CME213_API int cme213_ctx_create(int device, cme213_ctx **out) {
 CME213_API int cme213_ctx_destroy(cme213_ctx *ctx) {
     if (!ctx) return CME213_OK;
     cme213::DeviceGuard g(ctx->device);
+    for (int i = 0; i < cme213_ctx::CSR_CACHE; i++) cme213_csr_plan_destroy(ctx->csr_cache[i].plan);
     if (ctx->ws) cudaFree(ctx->ws);
     if (ctx->ws_event) cudaEventDestroy(ctx->ws_event);
     free(ctx);

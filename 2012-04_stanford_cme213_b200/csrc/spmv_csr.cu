@@ -21,7 +21,9 @@
 // holds with zero slack.
 #include "internal.cuh"
 #include <stdlib.h>
+#include <string.h>
 #include <type_traits>
+#include <vector>
 
 namespace {
 using namespace cme213;
@@ -31,7 +33,7 @@ __device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(
 __device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
 __device__ __forceinline__ double add_rn(double a, double b) { return __dadd_rn(a, b); }
 
-enum Mode { MODE_CSR = 0, MODE_PAGERANK = 1, MODE_PAGERANK_W = 2, MODE_CSR_ACC = 3 };   // ACC: y += A x (remote-column block of a sharded matrix)
+enum Mode { MODE_CSR = 0, MODE_PAGERANK = 1, MODE_PAGERANK_W = 2, MODE_CSR_ACC = 3 };   // ACC: y[r] = y[r] + e1 + e2 + ... (HYB tail, remote-column block of a sharded matrix)
 __host__ __device__ constexpr bool is_csr(int m) { return m == MODE_CSR || m == MODE_CSR_ACC; }
 
 template <typename T> struct Args {
@@ -152,7 +154,7 @@ __device__ __forceinline__ void epilogue_lean(const Args<T> &a, int64_t r, T sum
     if (MODE == MODE_CSR) {
         st_stream(a.y + r, sum);
     } else if (MODE == MODE_CSR_ACC) {
-        a.y[r] = add_rn(a.y[r], sum);
+        a.y[r] = sum;   // the sum started from y[r] (below): y + e1 + e2 + ... left to right, as if the row had never been split
     } else {
         const T out = add_rn(a.base, mul_rn(T(0.5), sum));
         a.y[r] = out;
@@ -164,7 +166,7 @@ __device__ __forceinline__ void epilogue_lean(const Args<T> &a, int64_t r, T sum
 // (8 CTAs of 256 threads per SM); the feature-complete kernel below (block lists, padded products) needs 38-40
 // and measured 5-30 % slower on the same inputs, so it only runs when one of its features is asked for.
 struct NoSync {};
-template <typename T, int MODE, int THREADS, int TILE, bool PADDED, bool SHARD = false>
+template <typename T, int MODE, int THREADS, int TILE, bool PADDED, bool SHARD = false, bool KEEP = false>
 __global__ void __launch_bounds__(THREADS)
 csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename std::conditional<SHARD, ShardSync, NoSync>::type sync) {
     static_assert(TILE % (4 * THREADS) == 0, "tile must be a whole number of 4-wide vectors per thread");
@@ -201,6 +203,8 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename s
     }
     const int b0 = __ldg(a.row_ptr + r0), b1 = __ldg(a.row_ptr + rl);  // this CTA's nonzero range
     T sum = T(0);
+    if (MODE == MODE_CSR_ACC && re > rs) sum = a.y[r];
+    [[maybe_unused]] const uint64_t keep = KEEP ? l2_policy_evict_last() : 0;
     for (int base = b0 & ~3; base < b1; base += TILE) {
 #pragma unroll
         for (int v = 0; v < TILE / (4 * THREADS); v++) {
@@ -211,10 +215,14 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename s
                 V4<T> w;
                 if (is_csr(MODE)) w = V4<T>::load(a.val + j);
                 else w = V4<T>{{T(0), T(0), T(0), T(0)}};
-                T p0 = product<T, MODE>(a, w.v[0], c.x);
-                T p1 = product<T, MODE>(a, w.v[1], c.y);
-                T p2 = product<T, MODE>(a, w.v[2], c.z);
-                T p3 = product<T, MODE>(a, w.v[3], c.w);
+                T p0, p1, p2, p3;
+                if constexpr (KEEP) {   // x entries marked evict-last in L2: for vectors that fit L2 but are gathered at random
+                    p0 = product_keep<T, MODE>(a, w.v[0], c.x, keep); p1 = product_keep<T, MODE>(a, w.v[1], c.y, keep);
+                    p2 = product_keep<T, MODE>(a, w.v[2], c.z, keep); p3 = product_keep<T, MODE>(a, w.v[3], c.w, keep);
+                } else {
+                    p0 = product<T, MODE>(a, w.v[0], c.x); p1 = product<T, MODE>(a, w.v[1], c.y);
+                    p2 = product<T, MODE>(a, w.v[2], c.z); p3 = product<T, MODE>(a, w.v[3], c.w);
+                }
                 const int po = pidx(o);
                 prod[po + 0] = p0; prod[po + 1] = p1; prod[po + 2] = p2; prod[po + 3] = p3;
             } else {
@@ -232,7 +240,7 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename s
         for (int j = lo; j < hi; j++) sum = add_rn(sum, prod[pidx(j - base)]);
         __syncthreads();
     }
-    if (r < row_end) epilogue_lean<T, MODE>(a, r, sum);
+    if (r < row_end && (MODE != MODE_CSR_ACC || re > rs)) epilogue_lean<T, MODE>(a, r, sum);   // ACC: rows without entries keep their y untouched
     if constexpr (SHARD) {
         if (side_lo || side_hi) {
             // the exchange, fused: halo rows go straight into the neighbour's vector over NVLink (peer addresses bypass
@@ -332,25 +340,150 @@ csr_stream_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
     }
 }
 
-// AUTO: rows whose common length is a multiple of 8 make the per-row sums of the stream kernel collide on shared
-// memory banks; pick the padded variant for them.  The decision needs three row_ptr entries from the device, so it is
-// taken once per (row_ptr, range) and remembered in the context (the first call on a new matrix synchronises the
-// stream; callers that must not synchronise pass CME213_CSR_STREAM or CME213_CSR_STREAM_PADDED explicitly).
-static int stream_variant_for(cme213_ctx *ctx, const int32_t *row_ptr, int64_t row_begin, int64_t row_end,
-                              cudaStream_t st, bool *padded) {
+// ---- dispatcher ------------------------------------------------------------------------------------------------------
+// The reference material states three CSR shapes and their regimes (slides/Lecture22.pdf slides 20/21/25; Bell TR 2008
+// Figs. 20, 22: one thread per row loses coalescing as rows grow, one warp per row wastes lanes on short rows; the student's
+// own finding that a warp per segment regresses on short segments, hw_final paper/Final_Report_DongBang_Tsai.tex:228).
+// A plan looks at the row-length histogram ONCE (one small kernel + one synchronisation), picks the kernel and, for
+// skewed matrices, splits the 256-row blocks into a short and a long list; every SpMV through the plan is launch-only.
+// Thresholds: profiles/r02_csr_kernel_sweep.csv.
+}  // namespace
+
+struct cme213_csr_plan {
+    int device = 0;
+    int64_t row_begin = 0, row_end = 0, num_cols = 0, nnz = 0;
+    int elem_bytes = 4;
+    int kernel = CME213_CSR_STREAM;       // CME213_CSR_* (| lanes << 8) or CME213_CSR_BINNED
+    int long_lanes = 32;
+    double mean = 0, long_nnz_fraction = 0;
+    int max_len = 0;
+    int32_t *d_short = nullptr, *d_long = nullptr;   // BINNED: 256-row block numbers (counted from row_begin)
+    int64_t n_short = 0, n_long = 0;
+    char text[320] = "";
+};
+
+namespace {
+constexpr int PLAN_BLOCK_ROWS = 256;       // = cme213_spmv_csr_block_rows()
+constexpr int PLAN_LONG_ROW = 96;          // a row this long is better served by a warp than by one thread of the stream kernel
+constexpr double PLAN_VECTOR_MEAN = 48.0;  // mean row length from which CSR-vector wins on the whole matrix
+constexpr double PLAN_BINNED_FRACTION = 0.20;   // share of the nonzeros in long rows that makes a split launch worth it
+
+__global__ void plan_block_class_kernel(int64_t nblocks, int64_t rows, const int32_t *__restrict__ row_ptr, int thresh_nnz,
+                                        uint32_t *is_long) {
+    const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b > nblocks) return;
+    uint32_t v = 0;
+    if (b < nblocks) {
+        const int64_t r0 = b * PLAN_BLOCK_ROWS, r1 = r0 + PLAN_BLOCK_ROWS < rows ? r0 + PLAN_BLOCK_ROWS : rows;
+        v = (row_ptr[r1] - row_ptr[r0]) >= thresh_nnz ? 1u : 0u;
+    }
+    is_long[b] = v;   // entry nblocks = 0: its scan value is the number of long blocks
+}
+// stream compaction on the scan (slides/Lecture16.pdf slides 3-13): both lists at once
+__global__ void plan_block_lists_kernel(int64_t nblocks, const uint32_t *__restrict__ is_long, const uint32_t *__restrict__ excl,
+                                        int32_t *long_list, int32_t *short_list) {
+    const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= nblocks) return;
+    if (is_long[b]) long_list[excl[b]] = (int32_t)b; else short_list[b - excl[b]] = (int32_t)b;
+}
+
+// CSR-vector over a list of 256-row blocks: CTA c works on part c % G of block list[c / G] (256 / G rows, G lanes each)
+template <typename T, int G>
+__global__ void __launch_bounds__(256)
+csr_vector_blocks_kernel(Args<T> a, int64_t row_begin, int64_t row_end, const int32_t *__restrict__ list) {
+    const int64_t blk = __ldg(list + blockIdx.x / G);
+    const int64_t r = row_begin + blk * PLAN_BLOCK_ROWS + (int64_t)(blockIdx.x % G) * (256 / G) + threadIdx.x / G;
+    const int sub = threadIdx.x % G;
+    T sum = T(0);
+    if (r < row_end) {
+        const int e = a.row_ptr[r + 1];
+        for (int j = a.row_ptr[r] + sub; j < e; j += G) sum += ld_stream(a.val + j) * __ldg(a.x + ld_stream(a.col + j));
+    }
+#pragma unroll
+    for (int d = G / 2; d > 0; d >>= 1) sum += __shfl_down_sync(0xFFFFFFFFu, sum, d, G);
+    if (r < row_end && sub == 0) a.y[r] = sum;
+}
+
+int vector_lanes_for(double mean) { return mean >= 24 ? 32 : mean >= 12 ? 16 : mean >= 6 ? 8 : mean >= 3 ? 4 : 2; }
+
+int plan_build(cme213_ctx *ctx, cme213_csr_plan *p, const int32_t *d_row_ptr, cudaStream_t st) {
+    const int64_t rows = p->row_end - p->row_begin;
+    const int32_t *ptr = d_row_ptr + p->row_begin;
+    std::vector<unsigned long long> hist(CME213_HIST_BINS);
+    int rc = cme213_internal_row_length_hist(ctx, rows, ptr, hist.data(), &p->max_len, st);
+    if (rc) return rc;
+    unsigned long long nnz = 0, long_nnz = 0, nonempty_bins = 0;
+    int only_len = -1;
+    for (int l = 0; l < CME213_HIST_BINS; l++) {
+        if (!hist[l]) continue;
+        nonempty_bins++;
+        only_len = l;
+        nnz += hist[l] * (unsigned long long)l;     // the last bin undercounts rows longer than 4095: fine for a ratio
+        if (l >= PLAN_LONG_ROW) long_nnz += hist[l] * (unsigned long long)l;
+    }
+    p->nnz = (int64_t)nnz;
+    p->mean = rows ? (double)nnz / (double)rows : 0.0;
+    p->long_nnz_fraction = nnz ? (double)long_nnz / (double)nnz : 0.0;
+    const size_t x_bytes = (size_t)p->num_cols * (size_t)p->elem_bytes;
+    if (nonempty_bins == 1 && only_len >= 8 && only_len % 8 == 0 && only_len < PLAN_VECTOR_MEAN) {
+        // every row has 8, 16, 32 ... entries: the per-row sums of the stream kernel would walk shared memory with a
+        // power-of-two stride; the padded variant removes the bank conflicts (0.43 -> 0.77 of peak on 16 per row)
+        p->kernel = CME213_CSR_STREAM_PADDED;
+    } else if (p->mean >= PLAN_VECTOR_MEAN) {
+        p->kernel = CME213_CSR_VECTOR | (32 << 8);
+    } else if (p->long_nnz_fraction >= PLAN_BINNED_FRACTION && rows >= 4 * PLAN_BLOCK_ROWS) {
+        p->kernel = CME213_CSR_BINNED;
+    } else {
+        // x larger than what L1 holds, smaller than L2: keep it there against the matrix streaming through
+        p->kernel = (x_bytes >= ((size_t)8 << 20) && x_bytes <= ((size_t)96 << 20)) ? CME213_CSR_STREAM_KEEP : CME213_CSR_STREAM;
+    }
+    if (p->kernel == CME213_CSR_BINNED) {
+        const int64_t nblocks = div_up(rows, PLAN_BLOCK_ROWS);
+        const int64_t n = nblocks + 1;
+        uint32_t *d_flag = nullptr, *d_excl = nullptr;
+        CME213_CUDA(cudaMalloc(&d_flag, (size_t)n * 4));
+        CME213_CUDA(cudaMalloc(&d_excl, (size_t)n * 4));
+        CME213_CUDA(cudaMalloc(&p->d_short, (size_t)nblocks * 4));
+        CME213_CUDA(cudaMalloc(&p->d_long, (size_t)nblocks * 4));
+        plan_block_class_kernel<<<(unsigned)div_up(n, 256), 256, 0, st>>>(nblocks, rows, ptr, PLAN_BLOCK_ROWS * 32, d_flag);
+        CME213_LAUNCHED(ctx, "plan_block_class_kernel");
+        rc = cme213_exclusive_scan_u32(ctx, d_flag, d_excl, n, st);
+        if (rc) return rc;
+        plan_block_lists_kernel<<<(unsigned)div_up(nblocks, 256), 256, 0, st>>>(nblocks, d_flag, d_excl, p->d_long, p->d_short);
+        CME213_LAUNCHED(ctx, "plan_block_lists_kernel");
+        uint32_t nl = 0;
+        CME213_CUDA(cudaMemcpyAsync(&nl, d_excl + nblocks, 4, cudaMemcpyDeviceToHost, st));
+        CME213_CUDA(cudaStreamSynchronize(st));
+        cudaFree(d_flag);
+        cudaFree(d_excl);
+        p->n_long = nl;
+        p->n_short = nblocks - nl;
+        if (p->n_long == 0) p->kernel = CME213_CSR_STREAM;         // long rows spread too thinly to fill a block
+        else if (p->n_short == 0) p->kernel = CME213_CSR_VECTOR | (32 << 8);
+    }
+    const char *names[] = {"auto", "scalar", "vector", "stream", "stream-padded", "stream-keep", "binned"};
+    const int kind = p->kernel & 0xFF;
+    snprintf(p->text, sizeof(p->text), "%s%s: rows %lld, mean row %.2f, longest %d, %.1f%% of the nonzeros in rows >= %d%s", names[kind],
+             kind == CME213_CSR_VECTOR ? " (32 lanes)" : "", (long long)rows, p->mean, p->max_len, 100.0 * p->long_nnz_fraction, PLAN_LONG_ROW,
+             kind == CME213_CSR_BINNED ? "; short blocks -> stream, long blocks -> vector(32)" : "");
+    return CME213_OK;
+}
+
+// the plan for (row_ptr, range), from the context's cache or built now (first call: synchronises)
+int plan_for(cme213_ctx *ctx, const int32_t *row_ptr, int64_t row_begin, int64_t row_end, int64_t num_cols, int elem_bytes,
+             cudaStream_t st, cme213_csr_plan **out) {
     for (int i = 0; i < cme213_ctx::CSR_CACHE; i++) {
         const auto &e = ctx->csr_cache[i];
-        if (e.row_ptr == row_ptr && e.row_begin == row_begin && e.row_end == row_end) { *padded = e.padded; return CME213_OK; }
+        if (e.plan && e.row_ptr == row_ptr && e.row_begin == row_begin && e.row_end == row_end) { *out = e.plan; return CME213_OK; }
     }
-    int32_t h[2] = {0, 0};
-    CME213_CUDA(cudaMemcpyAsync(&h[0], row_ptr + row_begin, 4, cudaMemcpyDeviceToHost, st));
-    CME213_CUDA(cudaMemcpyAsync(&h[1], row_ptr + row_end, 4, cudaMemcpyDeviceToHost, st));
-    CME213_CUDA(cudaStreamSynchronize(st));
-    const double mean = (double)(h[1] - h[0]) / (double)(row_end - row_begin);
-    const long m = (long)(mean + 0.5);
-    *padded = m >= 8 && m % 8 == 0 && (mean - (double)m < 0.01 && (double)m - mean < 0.01);
+    cme213_csr_plan *p = new cme213_csr_plan();
+    p->device = ctx->device; p->row_begin = row_begin; p->row_end = row_end; p->num_cols = num_cols; p->elem_bytes = elem_bytes;
+    int rc = plan_build(ctx, p, row_ptr, st);
+    if (rc) { cme213_csr_plan_destroy(p); return rc; }
     auto &e = ctx->csr_cache[ctx->csr_cache_next++ % cme213_ctx::CSR_CACHE];
-    e.row_ptr = row_ptr; e.row_begin = row_begin; e.row_end = row_end; e.padded = *padded;
+    cme213_csr_plan_destroy(e.plan);
+    e.row_ptr = row_ptr; e.row_begin = row_begin; e.row_end = row_end; e.plan = p;
+    *out = p;
     return CME213_OK;
 }
 
@@ -361,15 +494,11 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
     if (rows <= 0) return CME213_OK;
     int kind = kernel & 0xFF;
     const int lanes = (kernel >> 8) & 0xFF;
-    bool padded = kind == CME213_CSR_STREAM_PADDED;
-    if (padded) kind = CME213_CSR_STREAM;
-    if (kind == CME213_CSR_AUTO && is_csr(MODE)) {
-        // inspector, once per (row_ptr, row range): mean row length decides between the two stream variants
-        int rc = stream_variant_for(ctx, a.row_ptr, row_begin, row_end, st, &padded);
-        if (rc) return rc;
-    }
+    const bool padded = kind == CME213_CSR_STREAM_PADDED;
+    const bool keep = kind == CME213_CSR_STREAM_KEEP;
+    if (padded || keep) kind = CME213_CSR_STREAM;
     const bool vec_ok = aligned16(a.col) && (MODE != MODE_CSR || aligned16(a.val));
-    if (kind == CME213_CSR_AUTO) kind = CME213_CSR_STREAM;
+    if (kind == CME213_CSR_AUTO) kind = CME213_CSR_STREAM;   // (CSR products resolve AUTO through a plan before they get here)
     if (kind == CME213_CSR_STREAM && !vec_ok) kind = CME213_CSR_SCALAR;
     if (kind == CME213_CSR_VECTOR && MODE != MODE_CSR) kind = CME213_CSR_STREAM;
     if (kind == CME213_CSR_SCALAR) {
@@ -405,6 +534,7 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
         } else {
             const int64_t blocks = div_up(rows, THREADS);
             if (padded) csr_stream_lean_kernel<T, MODE, THREADS, TILE, true><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end, NoSync());
+            else if (keep) csr_stream_lean_kernel<T, MODE, THREADS, TILE, false, false, true><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end, NoSync());
             else csr_stream_lean_kernel<T, MODE, THREADS, TILE, false><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end, NoSync());
         }
         CME213_LAUNCHED(ctx, "csr_stream_kernel");
@@ -416,6 +546,27 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
 }
 
 template <typename T> struct Push { T *peer_lo = nullptr, *peer_hi = nullptr; int64_t lo_end = 0, hi_begin = 0; };
+
+// One SpMV as the plan says: launches only, no synchronisation.
+template <typename T>
+int run_plan(cme213_ctx *ctx, const cme213_csr_plan *p, Args<T> a, cudaStream_t st) {
+    const int kind = p->kernel & 0xFF;
+    if (kind != CME213_CSR_BINNED) return launch_csr<T, MODE_CSR>(ctx, a, p->row_begin, p->row_end, p->kernel, st);
+    if (!(aligned16(a.col) && aligned16(a.val))) return launch_csr<T, MODE_CSR>(ctx, a, p->row_begin, p->row_end, CME213_CSR_SCALAR, st);
+    if (p->n_short > 0) {
+        Args<T> b = a;
+        b.order = p->d_short;
+        int rc = launch_csr<T, MODE_CSR>(ctx, b, p->row_begin, p->row_end, CME213_CSR_STREAM, st, p->n_short);
+        if (rc) return rc;
+    }
+    if (p->n_long > 0) {
+        const int64_t blocks = p->n_long * 32;
+        if (blocks > 0x7FFFFFFFLL) { set_error("csr plan: too many long blocks"); return CME213_ERR_UNSUPPORTED; }
+        csr_vector_blocks_kernel<T, 32><<<(unsigned)blocks, 256, 0, st>>>(a, p->row_begin, p->row_end, p->d_long);
+        CME213_LAUNCHED(ctx, "csr_vector_blocks_kernel");
+    }
+    return CME213_OK;
+}
 
 template <typename T>
 int spmv_csr_impl(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, const int32_t *d_row_ptr, const int32_t *d_col,
@@ -429,6 +580,15 @@ int spmv_csr_impl(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, const int
     Args<T> a{d_row_ptr, d_col, d_val, d_x, nullptr, d_y, nullptr, T(0), d_order, push.peer_lo, push.peer_hi, push.lo_end, push.hi_begin};
     if (d_order && !(aligned16(d_col) && aligned16(d_val))) { set_error("spmv_csr ordered: col/val must be 16-byte aligned"); return CME213_ERR_INVALID; }
     if (d_order && (num_blocks < 0 || num_blocks > div_up(row_end - row_begin, 256))) { set_error("spmv_csr ordered: bad num_blocks"); return CME213_ERR_INVALID; }
+    if (!d_order && (kernel & 0xFF) == CME213_CSR_AUTO) {
+        // AUTO = the dispatcher: the plan of this (row_ptr, row range) is built on the first call (one synchronisation)
+        // and kept in the context.  The matrix is taken to be about square for the x-residency rule (no column count here;
+        // cme213_csr_plan_create takes one).
+        cme213_csr_plan *plan = nullptr;
+        int rc = plan_for(ctx, d_row_ptr, row_begin, row_end, row_end, (int)sizeof(T), (cudaStream_t)stream, &plan);
+        if (rc) return rc;
+        return run_plan<T>(ctx, plan, a, (cudaStream_t)stream);
+    }
     return launch_csr<T, MODE_CSR>(ctx, a, row_begin, row_end, d_order ? CME213_CSR_STREAM : kernel, (cudaStream_t)stream,
                                    d_order ? num_blocks : -1);
 }
@@ -511,6 +671,102 @@ int cme213_internal_pagerank_propagate_w(cme213_ctx *ctx, const uint32_t *d_grap
     return launch_csr<float, MODE_PAGERANK_W>(ctx, a, 0, array_length, CME213_CSR_STREAM, (cudaStream_t)stream);
 }
 
+// ---- plans: the dispatcher as an object (inspect once, then launch-only) ----------------------------------------------
+CME213_API int cme213_csr_plan_create(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, int64_t num_cols,
+                                      const int32_t *d_row_ptr, int elem_bytes, void *stream, cme213_csr_plan **out) {
+    CME213_CHECK_CTX(ctx);
+    if (!out) { set_error("csr_plan_create: null out pointer"); return CME213_ERR_INVALID; }
+    *out = nullptr;
+    if (row_begin < 0 || row_end < row_begin || num_cols < 0 || (elem_bytes != 4 && elem_bytes != 8) || (row_end > row_begin && !d_row_ptr)) {
+        set_error("csr_plan_create: bad arguments");
+        return CME213_ERR_INVALID;
+    }
+    DeviceGuard g(ctx->device);
+    cme213_csr_plan *p = new cme213_csr_plan();
+    p->device = ctx->device; p->row_begin = row_begin; p->row_end = row_end; p->num_cols = num_cols; p->elem_bytes = elem_bytes;
+    if (row_end > row_begin) {
+        int rc = plan_build(ctx, p, d_row_ptr, (cudaStream_t)stream);
+        if (rc) { cme213_csr_plan_destroy(p); return rc; }
+    }
+    *out = p;
+    return CME213_OK;
+}
+CME213_API int cme213_csr_plan_destroy(cme213_csr_plan *p) {
+    if (!p) return CME213_OK;
+    DeviceGuard g(p->device);
+    if (p->d_short) cudaFree(p->d_short);
+    if (p->d_long) cudaFree(p->d_long);
+    delete p;
+    return CME213_OK;
+}
+CME213_API int cme213_csr_plan_kernel(const cme213_csr_plan *p) { return p ? p->kernel : CME213_ERR_INVALID; }
+CME213_API const char *cme213_csr_plan_describe(const cme213_csr_plan *p) { return p ? p->text : ""; }
+CME213_API int cme213_spmv_csr_plan_f32(cme213_ctx *ctx, const cme213_csr_plan *plan, const int32_t *d_row_ptr, const int32_t *d_col,
+                                        const float *d_val, const float *d_x, float *d_y, void *stream) {
+    CME213_CHECK_CTX(ctx);
+    if (!plan || plan->elem_bytes != 4) { set_error("spmv_csr_plan_f32: no plan, or a plan made for 8-byte values"); return CME213_ERR_INVALID; }
+    if (plan->row_end == plan->row_begin) return CME213_OK;
+    if (!d_row_ptr || !d_col || !d_val || !d_x || !d_y) { set_error("spmv_csr_plan: null pointer"); return CME213_ERR_INVALID; }
+    DeviceGuard g(ctx->device);
+    Args<float> a{d_row_ptr, d_col, d_val, d_x, nullptr, d_y, nullptr, 0.f, nullptr, nullptr, nullptr, 0, 0};
+    return run_plan<float>(ctx, plan, a, (cudaStream_t)stream);
+}
+CME213_API int cme213_spmv_csr_plan_f64(cme213_ctx *ctx, const cme213_csr_plan *plan, const int32_t *d_row_ptr, const int32_t *d_col,
+                                        const double *d_val, const double *d_x, double *d_y, void *stream) {
+    CME213_CHECK_CTX(ctx);
+    if (!plan || plan->elem_bytes != 8) { set_error("spmv_csr_plan_f64: no plan, or a plan made for 4-byte values"); return CME213_ERR_INVALID; }
+    if (plan->row_end == plan->row_begin) return CME213_OK;
+    if (!d_row_ptr || !d_col || !d_val || !d_x || !d_y) { set_error("spmv_csr_plan: null pointer"); return CME213_ERR_INVALID; }
+    DeviceGuard g(ctx->device);
+    Args<double> a{d_row_ptr, d_col, d_val, d_x, nullptr, d_y, nullptr, 0.0, nullptr, nullptr, nullptr, 0, 0};
+    return run_plan<double>(ctx, plan, a, (cudaStream_t)stream);
+}
+
+// Format choice from the same histogram.  Costs are in "ELL slots": an ELL slot (padded or not) costs 1, an entry that goes
+// through the CSR stream kernel (the whole matrix as CSR, or the tail of HYB) costs PICK_CSR_COST -- the ratio of the two
+// kernels' gather rates on this GPU (profiles/r02_notes.md).  ELL when padding to the longest row is cheaper than CSR;
+// else HYB with the K that minimises K*rows + cost*tail(K) (Bell & Garland's rule, SC09 section 3.5, is this with
+// cost 3 and a floor of 4096 rows) when that beats CSR; else CSR.
+CME213_API int cme213_spmv_pick_format(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr, cme213_format_choice *out,
+                                       void *stream) {
+    CME213_CHECK_CTX(ctx);
+    if (!out || num_rows < 0 || (num_rows > 0 && !d_row_ptr)) { set_error("spmv_pick_format: bad arguments"); return CME213_ERR_INVALID; }
+    memset(out, 0, sizeof(*out));
+    if (num_rows == 0) return CME213_OK;
+    DeviceGuard g(ctx->device);
+    std::vector<unsigned long long> hist(CME213_HIST_BINS);
+    int max_len = 0;
+    int rc = cme213_internal_row_length_hist(ctx, num_rows, d_row_ptr, hist.data(), &max_len, (cudaStream_t)stream);
+    if (rc) return rc;
+    constexpr double PICK_CSR_COST = 1.6;
+    double nnz = 0;
+    for (int l = 0; l < CME213_HIST_BINS; l++) nnz += (double)hist[l] * l;
+    const double M = (double)num_rows, csr_cost = PICK_CSR_COST * nnz;
+    // walk K upward: tail(K) = nnz - sum_{k<=K} rows_ge(k)
+    double rows_ge = M - (double)hist[0], tail = nnz, best_cost = csr_cost;
+    int best_K = 0;
+    for (int K = 1; K < CME213_HIST_BINS && K <= max_len; K++) {
+        tail -= rows_ge;                      // column K holds one entry of every row with >= K entries
+        const double cost = (double)K * M + PICK_CSR_COST * tail;
+        if (cost < best_cost) { best_cost = cost; best_K = K; }
+        rows_ge -= (double)hist[K];
+    }
+    out->mean_row = nnz / M;
+    out->max_row = max_len;
+    out->ell_padding_ratio = nnz > 0 ? (double)max_len * M / nnz : 0.0;
+    if (max_len < CME213_HIST_BINS - 1 && (double)max_len * M <= csr_cost) {
+        out->format = CME213_FORMAT_ELL; out->K = max_len; out->tail_fraction = 0.0;
+    } else if (best_K > 0) {
+        double t = nnz, ge = M - (double)hist[0];
+        for (int K = 1; K <= best_K; K++) { t -= ge; ge -= (double)hist[K]; }
+        out->format = CME213_FORMAT_HYB; out->K = best_K; out->tail_fraction = nnz > 0 ? t / nnz : 0.0;
+    } else {
+        out->format = CME213_FORMAT_CSR; out->K = 0; out->tail_fraction = 1.0;
+    }
+    out->cost_vs_csr = csr_cost > 0 ? (out->format == CME213_FORMAT_ELL ? (double)max_len * M : best_cost) / csr_cost : 1.0;
+    return CME213_OK;
+}
+
 // ---- internal entry points of the row-sharded iterate (sharded.cu) ---------------------------------------------------
 int cme213_internal_shard_block_rows(void) { return 128; }
 int cme213_internal_spmv_csr_f64_shard(cme213_ctx *ctx, int64_t rows_local, const int32_t *d_row_ptr, const int32_t *d_col,
@@ -526,15 +782,30 @@ int cme213_internal_spmv_csr_f64_shard(cme213_ctx *ctx, int64_t rows_local, cons
     CME213_LAUNCHED(ctx, "csr_stream_lean_kernel<shard>");
     return CME213_OK;
 }
-int cme213_internal_spmv_csr_f64_acc(cme213_ctx *ctx, int64_t rows_local, const int32_t *d_row_ptr, const int32_t *d_col,
-                                     const double *d_val, const double *d_x, double *d_y, cudaStream_t st) {
+template <typename T>
+static int spmv_csr_acc(cme213_ctx *ctx, int64_t rows_local, const int32_t *d_row_ptr, const int32_t *d_col, const T *d_val,
+                        const T *d_x, T *d_y, bool keep, cudaStream_t st) {
     if (rows_local <= 0) return CME213_OK;
     DeviceGuard g(ctx->device);
-    Args<double> a{d_row_ptr, d_col, d_val, d_x, nullptr, d_y, nullptr, 0.0, nullptr, nullptr, nullptr, 0, 0};
-    constexpr int THREADS = 128, TILE = THREADS * 8;
+    if (!(aligned16(d_col) && aligned16(d_val))) { set_error("spmv_csr acc: col/val must be 16-byte aligned"); return CME213_ERR_INVALID; }
+    Args<T> a{d_row_ptr, d_col, d_val, d_x, nullptr, d_y, nullptr, T(0), nullptr, nullptr, nullptr, 0, 0};
+    constexpr int THREADS = sizeof(T) == 8 ? 128 : 256, TILE = THREADS * 8;
     const int64_t blocks = div_up(rows_local, THREADS);
     if (blocks > 0x7FFFFFFFLL) { set_error("spmv_csr acc: too many rows"); return CME213_ERR_UNSUPPORTED; }
-    csr_stream_lean_kernel<double, MODE_CSR_ACC, THREADS, TILE, false><<<(unsigned)blocks, THREADS, 0, st>>>(a, 0, rows_local, NoSync());
+    if (keep) csr_stream_lean_kernel<T, MODE_CSR_ACC, THREADS, TILE, false, false, true><<<(unsigned)blocks, THREADS, 0, st>>>(a, 0, rows_local, NoSync());
+    else csr_stream_lean_kernel<T, MODE_CSR_ACC, THREADS, TILE, false><<<(unsigned)blocks, THREADS, 0, st>>>(a, 0, rows_local, NoSync());
     CME213_LAUNCHED(ctx, "csr_stream_lean_kernel<acc>");
     return CME213_OK;
+}
+int cme213_internal_spmv_csr_f64_acc(cme213_ctx *ctx, int64_t rows_local, const int32_t *d_row_ptr, const int32_t *d_col,
+                                     const double *d_val, const double *d_x, double *d_y, cudaStream_t st) {
+    return spmv_csr_acc<double>(ctx, rows_local, d_row_ptr, d_col, d_val, d_x, d_y, false, st);
+}
+int cme213_internal_spmv_csr_f64_acc_keep(cme213_ctx *ctx, int64_t rows_local, const int32_t *d_row_ptr, const int32_t *d_col,
+                                          const double *d_val, const double *d_x, double *d_y, cudaStream_t st) {
+    return spmv_csr_acc<double>(ctx, rows_local, d_row_ptr, d_col, d_val, d_x, d_y, true, st);
+}
+int cme213_internal_spmv_csr_f32_acc_keep(cme213_ctx *ctx, int64_t rows_local, const int32_t *d_row_ptr, const int32_t *d_col,
+                                          const float *d_val, const float *d_x, float *d_y, cudaStream_t st) {
+    return spmv_csr_acc<float>(ctx, rows_local, d_row_ptr, d_col, d_val, d_x, d_y, true, st);
 }

@@ -503,7 +503,14 @@ def make_powerlaw(ctx, torch, args, fmt):
                     keep=(d_ptr, d_col, d_val, x, y))
     K, maxlen = C.c_int(), C.c_int()
     ctx.call("cme213_hyb_pick_k", rows, d_ptr, C.byref(K), C.byref(maxlen))
-    Kell = maxlen.value if fmt == "ell" else K.value
+    choice = pkg.capi.FormatChoice()
+    ctx.call("cme213_spmv_pick_format", rows, d_ptr, C.byref(choice))
+    meta["pick_format"] = {"format": ["CSR", "ELL", "HYB"][choice.format], "K": choice.K, "tail_fraction": choice.tail_fraction,
+                           "ell_padding_ratio": choice.ell_padding_ratio, "cost_vs_csr": choice.cost_vs_csr}
+    if fmt == "hyb":      # HYB as the library recommends it: the chooser's K (or --hyb-k), tail kept as CSR
+        Kell = args.hyb_k if args.hyb_k > 0 else (choice.K if choice.format == 2 else K.value)
+    else:
+        Kell = maxlen.value if fmt == "ell" else K.value
     pitch = int(pkg.load().cme213_ell_pitch(rows))
     e_idx, e_val = i32(Kell * pitch, torch), torch.empty(Kell * pitch, dtype=torch.float32, device="cuda")
     ctx.call("cme213_csr_to_ell_f32", rows, rows, d_ptr, d_col, d_val, Kell, pitch, e_idx, e_val)
@@ -515,6 +522,23 @@ def make_powerlaw(ctx, torch, args, fmt):
         meta["workload"] = "C4: ELL SpMV fp32, %s, %d rows (K = max row length)" % (name, rows)
         return dict(step=step, alg_bytes=alg, flops=2 * nnz.value, kernel="ell_v4_kernel<float>", launches_per_step=1, meta=meta,
                     keep=(e_idx, e_val, x, y))
+    if fmt == "hyb":
+        t_p = i32(rows + 1, torch)
+        tail = C.c_int64()
+        ctx.call("cme213_csr_tail_row_ptr", rows, d_ptr, Kell, t_p, C.byref(tail))
+        n = max(tail.value, 4)
+        t_r, t_c, t_v = i32(n, torch), i32(n, torch), torch.empty(n, dtype=torch.float32, device="cuda")
+        if tail.value:
+            ctx.call("cme213_csr_to_coo_tail_f32", rows, d_ptr, d_col, d_val, Kell, None, t_r, t_c, t_v)
+        del d_col, d_val, t_r
+        meta.update({"tail_nnz": tail.value, "hyb_actual_bytes": Kell * pitch * 8 + tail.value * 8 + (rows + 1) * 4})
+
+        def step():
+            ctx.call("cme213_spmv_hyb_csrtail_f32", rows, pitch, Kell, e_idx, e_val, t_p if tail.value else None, t_c, t_v, x, y,
+                     stream=torch.cuda.current_stream())
+        meta["workload"] = "C4: HYB SpMV fp32 (ELL K=%d + tail as CSR), %s, %d rows" % (Kell, name, rows)
+        return dict(step=step, alg_bytes=alg, flops=2 * nnz.value, kernel="ell_v4_kernel<float> + csr_stream_lean_kernel<float,acc>",
+                    launches_per_step=2 if tail.value else 1, meta=meta, keep=(e_idx, e_val, t_p, t_c, t_v, x, y))
     tail = C.c_int64()
     ctx.call("cme213_csr_to_coo_tail_f32", rows, d_ptr, d_col, d_val, Kell, C.byref(tail), None, None, None)
     t_r, t_c, t_v = i32(max(tail.value, 4), torch), i32(max(tail.value, 4), torch), torch.empty(max(tail.value, 4), dtype=torch.float32, device="cuda")
@@ -525,7 +549,7 @@ def make_powerlaw(ctx, torch, args, fmt):
 
     def step():
         ctx.call("cme213_spmv_hyb_f32", rows, pitch, Kell, e_idx, e_val, tail.value, t_r, t_c, t_v, x, y, stream=torch.cuda.current_stream())
-    meta["workload"] = "C4: HYB SpMV fp32 (ELL K=%d + COO tail), %s, %d rows" % (Kell, name, rows)
+    meta["workload"] = "C4: HYB SpMV fp32 (ELL K=%d by the SC09 rule + COO tail by segmented reduction), %s, %d rows" % (Kell, name, rows)
     return dict(step=step, alg_bytes=alg, flops=2 * nnz.value, kernel="ell_v4_kernel<float> + lookback_scan_kernel<coo>",
                 launches_per_step=2 if tail.value else 1, meta=meta, keep=(e_idx, e_val, t_r, t_c, t_v, x, y))
 
@@ -574,11 +598,11 @@ def build_workload(name, ctx, torch, args, rank=0, world=1, dist=None):
         return make_transpose(ctx, torch, args, 32)
     if name == "transpose64":
         return make_transpose(ctx, torch, args, 64)
-    if name in ("ell", "hyb"):
+    if name in ("ell", "hyb", "hyb_coo"):
         return make_powerlaw(ctx, torch, args, name)
     if name == "csr_powerlaw":
         return make_powerlaw(ctx, torch, args, "csr")
-    if name in ("ell_window", "hyb_window", "csr_window", "ell_regular_window", "csr_regular_window"):
+    if name in ("ell_window", "hyb_window", "hyb_coo_window", "csr_window", "ell_regular_window", "csr_regular_window"):
         # same row lengths, columns drawn inside a 4,096-wide band around the diagonal (the locality of the FEM
         # matrices in the final project's benchmark set): the x gathers then hit in L1/L2 and the format kernels show
         # their streaming rate instead of the random-gather ceiling
@@ -586,7 +610,7 @@ def build_workload(name, ctx, torch, args, rank=0, world=1, dist=None):
         a2 = copy.copy(args)
         a2.window = 1 << 12
         a2.regular = 1 if "regular" in name else 0
-        return make_powerlaw(ctx, torch, a2, name.split("_")[0])
+        return make_powerlaw(ctx, torch, a2, "hyb_coo" if name.startswith("hyb_coo") else name.split("_")[0])
     if name == "pagerank":
         return make_pagerank(ctx, torch, args)
     raise SystemExit("unknown workload " + name)
@@ -982,6 +1006,7 @@ def main():
     ap.add_argument("--powerlaw-rows", type=int, default=1 << 24)
     ap.add_argument("--window", type=int, default=0)
     ap.add_argument("--regular", type=int, default=0)
+    ap.add_argument("--hyb-k", type=int, default=0, help="hyb workload: ELL width (0 = cme213_spmv_pick_format's choice)")
     ap.add_argument("--extras", type=int, default=1, help="also time the other single-GPU configs (N=1 only)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -1067,8 +1092,8 @@ def main():
         others = []
         del wl
         torch.cuda.empty_cache()
-        names = ["scan", "segscan", "radixsort", "dia", "stencil", "fp", "transpose32", "transpose64", "c1", "ell", "hyb", "csr_powerlaw",
-                 "ell_window", "hyb_window", "csr_window", "ell_regular_window", "csr_regular_window", "pagerank"]
+        names = ["scan", "segscan", "radixsort", "dia", "stencil", "fp", "transpose32", "transpose64", "c1", "ell", "hyb", "hyb_coo", "csr_powerlaw",
+                 "ell_window", "hyb_window", "hyb_coo_window", "csr_window", "ell_regular_window", "csr_regular_window", "pagerank"]
         for name in names:
             try:
                 w = build_workload(name, ctx, torch, args)

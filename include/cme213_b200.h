@@ -44,10 +44,14 @@ extern "C" {
 #define CME213_CSR_SCALAR 1 /* one thread per row, sequential sum: bit-identical to the CPU loop */
 #define CME213_CSR_VECTOR 2 /* 2..32 lanes per row, warp-shuffle reduction */
 #define CME213_CSR_STREAM 3 /* block streams its nonzeros through shared memory, then one thread per row sums sequentially: bit-identical to the CPU loop */
+#define CME213_CSR_STREAM_KEEP 5   /* CSR_STREAM with the x gathers marked evict-last in L2: x fits L2 but is gathered at random while the matrix streams by */
 #define CME213_CSR_STREAM_PADDED 4 /* same, shared-memory products padded against bank conflicts: for matrices whose rows all have 8, 16, 32 ... entries.
                                       AUTO picks between 3 and 4 from the mean row length (one small device read per new matrix). */
 
+#define CME213_CSR_BINNED 6 /* plans only: 256-row blocks split into a short list (stream kernel) and a long list (vector kernel) */
+
 typedef struct cme213_ctx cme213_ctx;
+typedef struct cme213_csr_plan cme213_csr_plan;
 
 /* ---- context ---------------------------------------------------------- */
 /* Binds to a CUDA device and owns a scratch workspace that grows on demand
@@ -151,6 +155,44 @@ int cme213_spmv_csr_f32(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, con
 int cme213_spmv_csr_f64(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, const int32_t *d_row_ptr,
                         const int32_t *d_col, const double *d_val, const double *d_x, double *d_y, int kernel,
                         void *stream);
+
+/* The dispatcher as an object.  CME213_CSR_AUTO in the calls above builds (first call on a matrix: one small kernel and
+ * ONE synchronisation) and caches such a plan per (row_ptr, row range); a caller that must never synchronise -- a timed
+ * loop, a stream capture -- creates the plan during set-up and multiplies through it.  The plan reads the row-length
+ * histogram and picks: stream (short / irregular rows), stream-padded (all rows 8, 16, 32 ... long), stream-keep
+ * (x between L1 and L2 size), vector with 32 lanes (long rows: mean >= 48), or BINNED for skewed matrices (>= 20 % of
+ * the nonzeros in rows >= 96 long): the 256-row blocks are split by stream compaction into a short list for the stream
+ * kernel and a long list for the vector kernel, two launches.  stream / scalar / padded / keep keep the CPU loop's
+ * summation order (bit-identical); vector and the long blocks of BINNED sum in another order (reduction-order bound).
+ * reference: slides/Lecture22.pdf slides 20, 21, 25; refs/Bell Tech Report 2008.pdf Figs. 20, 22 and section 5;
+ * hw/hw_final/programming/paper/Final_Report_DongBang_Tsai.tex:228 (warp-per-segment regresses on short segments). */
+int cme213_csr_plan_create(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, int64_t num_cols, const int32_t *d_row_ptr,
+                           int elem_bytes, void *stream, cme213_csr_plan **out);
+int cme213_csr_plan_destroy(cme213_csr_plan *plan);
+int cme213_csr_plan_kernel(const cme213_csr_plan *plan);           /* CME213_CSR_* (| lanes << 8) */
+const char *cme213_csr_plan_describe(const cme213_csr_plan *plan); /* one line: choice and the statistics behind it */
+int cme213_spmv_csr_plan_f32(cme213_ctx *ctx, const cme213_csr_plan *plan, const int32_t *d_row_ptr, const int32_t *d_col,
+                             const float *d_val, const float *d_x, float *d_y, void *stream);
+int cme213_spmv_csr_plan_f64(cme213_ctx *ctx, const cme213_csr_plan *plan, const int32_t *d_row_ptr, const int32_t *d_col,
+                             const double *d_val, const double *d_x, double *d_y, void *stream);
+/* Which FORMAT to convert a CSR matrix to, from the same histogram (synchronises): ELL when padding every row to the
+ * longest costs less than running the matrix as CSR, else HYB with the split width K that minimises
+ * K * rows + c * tail(K) when that beats CSR, else CSR.  c = 1.6: the measured ratio between the gather rates of the
+ * ELL kernel and of the CSR stream kernel that serves the tail.  reference: refs/Bell SC 2009.pdf section 3.5 (the
+ * same rule with c = 3 and a 4096-row floor: cme213_hyb_pick_k), Table 1 and Fig. 9. */
+#define CME213_FORMAT_CSR 0
+#define CME213_FORMAT_ELL 1
+#define CME213_FORMAT_HYB 2
+typedef struct cme213_format_choice {
+    int format;               /* CME213_FORMAT_* */
+    int K;                    /* ELL width (ELL: the longest row; HYB: the split) */
+    int max_row;
+    double mean_row;
+    double ell_padding_ratio; /* max_row * rows / nnz */
+    double tail_fraction;     /* share of the nonzeros left to the HYB tail */
+    double cost_vs_csr;       /* modelled cost of the choice relative to plain CSR (< 1: the conversion pays) */
+} cme213_format_choice;
+int cme213_spmv_pick_format(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr, cme213_format_choice *out, void *stream);
 
 /* Same result (bit for bit), with the caller choosing WHICH blocks of cme213_spmv_csr_block_rows() consecutive
  * rows one launch computes and in what order: CTA b (b < num_blocks) computes block number d_block_order[b],
@@ -272,7 +314,23 @@ int cme213_spmv_hyb_f64(cme213_ctx *ctx, int64_t num_rows, int64_t pitch, int K,
                         const double *d_ell_val, int64_t coo_nnz, const int32_t *d_coo_row,
                         const int32_t *d_coo_col, const double *d_coo_val, const double *d_x, double *d_y, void *stream);
 
+/* HYB with the tail as a CSR matrix of its own instead of COO triplets: d_tail_ptr from cme213_csr_tail_row_ptr, its
+ * column / value arrays are the d_coo_col / d_coo_val of cme213_csr_to_coo_tail_* (same order).  The tail runs through
+ * the CSR stream kernel in accumulate mode (8 bytes per entry instead of COO's 12, coalesced update of y for the rows
+ * that have a tail).  Rows are summed ELL columns first, then the tail in order: bit-identical to the CPU loop.
+ * d_tail_ptr == NULL: no tail.  reference: refs/Bell SC 2009.pdf section 3.5 (the split); the tail kernel is the CSR shape of
+ * slides/Lecture22.pdf slide 20. */
+int cme213_spmv_hyb_csrtail_f32(cme213_ctx *ctx, int64_t num_rows, int64_t pitch, int K, const int32_t *d_ell_idx,
+                                const float *d_ell_val, const int32_t *d_tail_ptr, const int32_t *d_tail_col,
+                                const float *d_tail_val, const float *d_x, float *d_y, void *stream);
+int cme213_spmv_hyb_csrtail_f64(cme213_ctx *ctx, int64_t num_rows, int64_t pitch, int K, const int32_t *d_ell_idx,
+                                const double *d_ell_val, const int32_t *d_tail_ptr, const int32_t *d_tail_col,
+                                const double *d_tail_val, const double *d_x, double *d_y, void *stream);
+
 /* ---- format conversion on the device ----------------------------------- */
+/* Row pointers (num_rows + 1) of the tail left after an ELL(K) split: exclusive scan of max(len - K, 0). */
+int cme213_csr_tail_row_ptr(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr, int K, int32_t *d_tail_ptr,
+                            int64_t *tail_nnz_out, void *stream);
 /* HYB split width: largest K such that at least max(4096, num_rows/3) rows have >= K entries.
  * Synchronises `stream`.  reference: refs/Bell SC 2009.pdf p.5 section 3.5. */
 int cme213_hyb_pick_k(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr, int *K_out, int *max_len_out,

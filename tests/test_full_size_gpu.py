@@ -178,3 +178,46 @@ def test_c5_csr_dia_matrix_free_512_cubed(ctx, cme):
     assert torch.equal(y_dia, y_csr)
     del d_dat, y_dia, y_mf, y_csr
     _free(torch)
+
+
+def test_c4_hyb_with_csr_tail_16mi_rows_bit_identical_to_csr(ctx, cme):
+    """Config C4 at full size through the format chooser: cme213_spmv_pick_format picks HYB and its K for the power-law
+    matrix, the tail runs as a CSR matrix of its own, and the product equals CSR-stream's bit for bit over all 16 Mi rows."""
+    import torch
+    rows = 1 << 24
+    lib = cme.load()
+    d_ptr = torch.empty(rows + 1, dtype=torch.int32, device="cuda")
+    nnz = C.c_int64()
+    ctx.call("cme213_gen_powerlaw_lengths", rows, 4, 265, 100, 256, 6, d_ptr, C.byref(nnz))
+    d_col = torch.empty(nnz.value, dtype=torch.int32, device="cuda")
+    d_val = torch.empty(nnz.value, dtype=torch.float32, device="cuda")
+    ctx.call("cme213_gen_random_csr_fill_f32", rows, rows, d_ptr, 0, 7, d_col, d_val)
+    d_x = torch.empty(rows, dtype=torch.float32, device="cuda")
+    ctx.call("cme213_fill_uniform_f32", d_x, rows, 8)
+    choice = cme.capi.FormatChoice()
+    ctx.call("cme213_spmv_pick_format", rows, d_ptr, C.byref(choice))
+    assert choice.format == cme.capi.FORMAT_HYB and 1 <= choice.K <= 32 and choice.cost_vs_csr < 1.0
+    K = choice.K
+    pitch = int(lib.cme213_ell_pitch(rows))
+    e_idx = torch.empty(K * pitch, dtype=torch.int32, device="cuda")
+    e_val = torch.empty(K * pitch, dtype=torch.float32, device="cuda")
+    ctx.call("cme213_csr_to_ell_f32", rows, rows, d_ptr, d_col, d_val, K, pitch, e_idx, e_val)
+    t_p = torch.empty(rows + 1, dtype=torch.int32, device="cuda")
+    tail = C.c_int64()
+    ctx.call("cme213_csr_tail_row_ptr", rows, d_ptr, K, t_p, C.byref(tail))
+    assert abs(tail.value / nnz.value - choice.tail_fraction) < 1e-6
+    t_r = torch.empty(tail.value, dtype=torch.int32, device="cuda")
+    t_c = torch.empty(tail.value, dtype=torch.int32, device="cuda")
+    t_v = torch.empty(tail.value, dtype=torch.float32, device="cuda")
+    ctx.call("cme213_csr_to_coo_tail_f32", rows, d_ptr, d_col, d_val, K, None, t_r, t_c, t_v)
+    del t_r
+    y_csr = torch.empty(rows, dtype=torch.float32, device="cuda")
+    ctx.call("cme213_spmv_csr_f32", 0, rows, d_ptr, d_col, d_val, d_x, y_csr, STREAM)
+    y = torch.full((rows,), -7.0, dtype=torch.float32, device="cuda")
+    ctx.call("cme213_spmv_hyb_csrtail_f32", rows, pitch, K, e_idx, e_val, t_p, t_c, t_v, d_x, y)
+    y_auto = torch.empty_like(y)
+    ctx.call("cme213_spmv_csr_f32", 0, rows, d_ptr, d_col, d_val, d_x, y_auto, 0)     # the dispatcher's choice for this matrix
+    torch.cuda.synchronize()
+    assert torch.equal(y, y_csr)
+    assert torch.equal(y_auto, y_csr)
+    _free(torch)
