@@ -106,3 +106,25 @@ def test_primitive_host_twins(cme):
         t = np.zeros((517, 333), dt)
         assert fn(P(a), P(t), 333, 517) == 0
         assert np.array_equal(t, a.T)
+
+
+@pytest.mark.parametrize("dtype,sfx", [(np.float64, "f64"), (np.float32, "f32")])
+def test_csr_matrix_stays_resident_between_iterate_calls(cme, dtype, sfx):
+    """Upload once, iterate many times with different x: only the vectors cross the bus on the later calls."""
+    lib = cme.load()
+    ptr, col, val = g.laplace3d(14, 9, 11, dtype=dtype)
+    n = 14 * 9 * 11
+    h = C.c_void_p()
+    assert getattr(lib, "cme213_csr_upload_host_" + sfx)(n, len(col), P(ptr), P(col), P(val), C.byref(h)) == 0
+    iterate = getattr(lib, "cme213_csr_iterate_" + sfx)
+    for seed, iters in ((1, 2), (2, 6), (3, 0)):
+        x = np.random.default_rng(seed).uniform(0, 0.2, n).astype(dtype)
+        out = np.full_like(x, -1)
+        ms = C.c_float(-1)
+        assert iterate(h, P(x), P(out), iters, C.byref(ms)) == 0, lib.cme213_last_error()
+        assert np.array_equal(out, oracle.csr_iterate(ptr, col, val, x, iters) if iters else x) and ms.value >= 0
+    assert iterate(h, P(x), P(out), 3, None) == cme.capi.ERR_INVALID                      # odd, as pagerank.cu:127 asserts
+    other = getattr(lib, "cme213_csr_iterate_" + ("f32" if sfx == "f64" else "f64"))
+    assert other(h, P(x), P(out), 2, None) == cme.capi.ERR_INVALID                       # wrong precision for this matrix
+    assert lib.cme213_csr_matrix_destroy(h) == 0
+    assert lib.cme213_csr_matrix_destroy(None) == 0
