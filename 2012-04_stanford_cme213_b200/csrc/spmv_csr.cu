@@ -20,6 +20,7 @@
 // code is built without FMA (x86-64 baseline), and its 10-ULP check (pagerank.cu:216-239) then
 // holds with zero slack.
 #include "internal.cuh"
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 #include <type_traits>
@@ -532,6 +533,24 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
             if (padded) csr_stream_kernel<T, MODE, ORD_THREADS, 1, ORD_TILE, true, true><<<(unsigned)blocks, ORD_THREADS, 0, st>>>(a, row_begin, row_end);
             else csr_stream_kernel<T, MODE, ORD_THREADS, 1, ORD_TILE, false, true><<<(unsigned)blocks, ORD_THREADS, 0, st>>>(a, row_begin, row_end);
         } else {
+#ifdef CME213_TUNING   // launch-shape sweep of the lean kernel: CME213_CSR_CFG="threads,tile,keep" (tuning builds only)
+            if (const char *cfg = getenv("CME213_CSR_CFG")) {
+                int T_ = 0, L_ = 0, K_ = 0;
+                sscanf(cfg, "%d,%d,%d", &T_, &L_, &K_);
+#define CME213_TRY_CSR(TH, TL) \
+                if (T_ == TH && L_ == TL) { \
+                    const int64_t nb = div_up(rows, TH); \
+                    if (K_) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, true><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); \
+                    else csr_stream_lean_kernel<T, MODE, TH, TL, false><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); \
+                    CME213_LAUNCHED(ctx, "csr_stream_lean_kernel(cfg)"); \
+                    return CME213_OK; \
+                }
+                CME213_TRY_CSR(64, 512) CME213_TRY_CSR(64, 1024) CME213_TRY_CSR(128, 1024) CME213_TRY_CSR(128, 1536) CME213_TRY_CSR(128, 2048)
+                CME213_TRY_CSR(256, 2048) CME213_TRY_CSR(256, 3072) CME213_TRY_CSR(256, 4096) CME213_TRY_CSR(512, 4096) CME213_TRY_CSR(512, 2048)
+                CME213_TRY_CSR(1024, 4096)
+#undef CME213_TRY_CSR
+            }
+#endif
             const int64_t blocks = div_up(rows, THREADS);
             if (padded) csr_stream_lean_kernel<T, MODE, THREADS, TILE, true><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end, NoSync());
             else if (keep) csr_stream_lean_kernel<T, MODE, THREADS, TILE, false, false, true><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end, NoSync());
