@@ -126,6 +126,7 @@ PROTOTYPES = {
     "cme213_fill_uniform_f64": (_i, [_p, _p, _i64, _u32, _p]),
     "cme213_fill_hash_u32": (_i, [_p, _p, _i64, _u32, _u32, _p]),
     "cme213_fill_random_flags": (_i, [_p, _p, _i64, _u32, _u32, _p]),
+    "cme213_probe_gather_f32": (_i, [_p, _p, _i64, _p, _i64, _u32, _p]),
     "device_graph_iterate": (None, [_p, _p, _p, _p, _p, _i, _i, _i]),
     "cme213_pagerank_iterate_host": (_i, [_p, _p, _p, _p, _p, _i, _i, _pf]),
     "cme213_csr_upload_host_f64": (_i, [_i64, _i64, _p, _p, _p, C.POINTER(_p)]),

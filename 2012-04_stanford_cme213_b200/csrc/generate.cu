@@ -352,3 +352,42 @@ CME213_API int cme213_gen_segment_offsets(cme213_ctx *ctx, int64_t n, int64_t nu
     return rc;
 }
 
+
+// ---- measurement aid: how fast can this GPU gather? --------------------------------------------------------------------
+// Every SpMV format here issues one data-dependent 4- or 8-byte load of x per nonzero.  When the columns are spread out,
+// each such load costs a whole 32-byte sector from L2 (or from HBM once x is larger than L2), so the rate of random
+// gathers -- not the HBM stream -- bounds the kernel.  This probe measures that ceiling with nothing else in the way:
+// 16 independent gathers per thread from hashed positions of x[0, q), one result stored per thread.
+namespace {
+__global__ void __launch_bounds__(256)
+probe_gather_kernel(const float *__restrict__ x, uint32_t q, float *__restrict__ out, int64_t threads_total, uint32_t seed) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= threads_total) return;
+    const uint64_t pol = l2_policy_evict_last();
+    float v[16];
+#pragma unroll
+    for (int j = 0; j < 16; j++) {
+        const uint32_t h = hash32(seed, (uint64_t)t * 16 + j);
+        v[j] = ld_keep(x + (uint32_t)(((uint64_t)h * q) >> 32), pol);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < 16; j++) s += v[j];
+    out[t] = s;
+}
+}  // namespace
+
+CME213_API int cme213_probe_gather_f32(cme213_ctx *ctx, const float *d_x, int64_t q, float *d_out, int64_t num_gathers,
+                                       uint32_t seed, void *stream) {
+    CME213_CHECK_CTX(ctx);
+    if (q < 1 || q > 0xFFFFFFFFLL || num_gathers < 0 || num_gathers % 16 || !d_x || (num_gathers > 0 && !d_out)) {
+        set_error("probe_gather_f32: bad arguments (num_gathers must be a multiple of 16)");
+        return CME213_ERR_INVALID;
+    }
+    if (num_gathers == 0) return CME213_OK;
+    DeviceGuard g(ctx->device);
+    const int64_t threads = num_gathers / 16;
+    probe_gather_kernel<<<(unsigned)div_up(threads, 256), 256, 0, (cudaStream_t)stream>>>(d_x, (uint32_t)q, d_out, threads, seed);
+    CME213_LAUNCHED(ctx, "probe_gather_kernel");
+    return CME213_OK;
+}

@@ -554,6 +554,22 @@ def make_powerlaw(ctx, torch, args, fmt):
                 launches_per_step=2 if tail.value else 1, meta=meta, keep=(e_idx, e_val, t_r, t_c, t_v, x, y))
 
 
+def make_gather(ctx, torch, args, q):
+    """The random-gather ceiling (cme213_probe_gather_f32): 2^28 gathers of 4 bytes from q floats."""
+    n = 1 << 28
+    x = torch.empty(q, dtype=torch.float32, device="cuda")
+    ctx.call("cme213_fill_uniform_f32", x, q, 8)
+    out = torch.empty(n // 16, dtype=torch.float32, device="cuda")
+
+    def step():
+        ctx.call("cme213_probe_gather_f32", x, q, out, n, 3, stream=torch.cuda.current_stream())
+
+    return dict(step=step, alg_bytes=n * 4 + n // 4, flops=n, kernel="probe_gather_kernel", launches_per_step=1,
+                meta={"workload": "gather ceiling: 2^28 random 4-byte gathers from %d floats (%.0f MB), 16 per thread" % (q, q * 4 / 1e6),
+                      "gathers": n, "sector_bytes_if_every_gather_is_one_l2_sector": n * 32, "l2": "x %s L2" % ("fits" if q * 4 < 100e6 else "exceeds")},
+                keep=(x, out))
+
+
 def make_pagerank(ctx, torch, args):
     import ctypes as C
     n, avg = 1 << 21, 8
@@ -613,6 +629,8 @@ def build_workload(name, ctx, torch, args, rank=0, world=1, dist=None):
         return make_powerlaw(ctx, torch, a2, "hyb_coo" if name.startswith("hyb_coo") else name.split("_")[0])
     if name == "pagerank":
         return make_pagerank(ctx, torch, args)
+    if name in ("gather_4mb", "gather_64mb", "gather_1gb"):
+        return make_gather(ctx, torch, args, {"gather_4mb": 1 << 20, "gather_64mb": 1 << 24, "gather_1gb": 1 << 28}[name])
     raise SystemExit("unknown workload " + name)
 
 
@@ -1115,12 +1133,15 @@ def main():
         del wl
         torch.cuda.empty_cache()
         names = ["scan", "segscan", "radixsort", "dia", "stencil", "fp", "transpose32", "transpose64", "c1", "ell", "hyb", "hyb_coo", "csr_powerlaw",
-                 "ell_window", "hyb_window", "hyb_coo_window", "csr_window", "ell_regular_window", "csr_regular_window", "pagerank"]
+                 "ell_window", "hyb_window", "hyb_coo_window", "csr_window", "ell_regular_window", "csr_regular_window", "pagerank",
+                 "gather_4mb", "gather_64mb", "gather_1gb"]
         for name in names:
             try:
                 w = build_workload(name, ctx, torch, args)
                 t = time_steps(torch, w["step"], args.steps, 3) / args.steps
                 gbs = w["alg_bytes"] / (t * 1e-3) / 1e9
+                if "gathers" in w["meta"]:
+                    w["meta"]["giga_gathers_per_s"] = w["meta"]["gathers"] / (t * 1e-3) / 1e9
                 others.append({"workload": w["meta"]["workload"], "ms": t, "gbs": gbs, "frac_of_measured_peak": gbs / peak,
                                "gflops": w["flops"] / (t * 1e-3) / 1e9, "kernel": w["kernel"],
                                "detail": {k: v for k, v in w["meta"].items() if k != "workload"}})

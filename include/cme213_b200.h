@@ -468,6 +468,12 @@ int cme213_fill_uniform_f64(cme213_ctx *ctx, double *d_out, int64_t n, uint32_t 
 int cme213_gen_segment_offsets(cme213_ctx *ctx, int64_t n, int64_t num_cuts, uint32_t seed, int32_t *d_s_out,
                                int64_t *p_out, void *stream);
 int cme213_fill_hash_u32(cme213_ctx *ctx, uint32_t *d_out, int64_t n, uint32_t seed, uint32_t modulus, void *stream);
+/* Measurement aid (bench.py --workload gather): d_out[t] = sum of 16 gathers of d_x at hashed positions in [0, q), for
+ * t < num_gathers / 16.  Its rate is the ceiling of every format's x gathers on matrices with scattered columns: one
+ * 32-byte L2 sector per gather.  No counterpart in the reference (its reports quote GB/s of the arrays only,
+ * hw/hw1/programming/PA1_Dong-Bang_Tsai.pdf p.3). */
+int cme213_probe_gather_f32(cme213_ctx *ctx, const float *d_x, int64_t q, float *d_out, int64_t num_gathers, uint32_t seed,
+                            void *stream);
 int cme213_fill_random_flags(cme213_ctx *ctx, uint32_t *d_flag_bits, int64_t n, uint32_t seed, uint32_t prob_num,
                              void *stream);
 
