@@ -140,12 +140,21 @@ template <> struct V4<float> {
         float4 t = ld_stream(reinterpret_cast<const float4 *>(p));
         return V4{{t.x, t.y, t.z, t.w}};
     }
+    __device__ static V4 load_first(const float *p, uint64_t pol) {
+        float4 t = ld_first(reinterpret_cast<const float4 *>(p), pol);
+        return V4{{t.x, t.y, t.z, t.w}};
+    }
 };
 template <> struct V4<double> {
     double v[4];
     __device__ static V4 load(const double *p) {
         double2 t0 = ld_stream(reinterpret_cast<const double2 *>(p));
         double2 t1 = ld_stream(reinterpret_cast<const double2 *>(p) + 1);
+        return V4{{t0.x, t0.y, t1.x, t1.y}};
+    }
+    __device__ static V4 load_first(const double *p, uint64_t pol) {
+        double2 t0 = ld_first(reinterpret_cast<const double2 *>(p), pol);
+        double2 t1 = ld_first(reinterpret_cast<const double2 *>(p) + 1, pol);
         return V4{{t0.x, t0.y, t1.x, t1.y}};
     }
 };
@@ -167,7 +176,9 @@ __device__ __forceinline__ void epilogue_lean(const Args<T> &a, int64_t r, T sum
 // (8 CTAs of 256 threads per SM); the feature-complete kernel below (block lists, padded products) needs 38-40
 // and measured 5-30 % slower on the same inputs, so it only runs when one of its features is asked for.
 struct NoSync {};
-template <typename T, int MODE, int THREADS, int TILE, bool PADDED, bool SHARD = false, bool KEEP = false>
+// KEEP: 0 = plain (.cs streams, default-policy gathers), 1 = x gathers evict-last, 2 = 1 + col/val with an explicit
+// evict-first policy and no L1 allocation (tuning builds only)
+template <typename T, int MODE, int THREADS, int TILE, bool PADDED, bool SHARD = false, int KEEP = 0>
 __global__ void __launch_bounds__(THREADS)
 csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename std::conditional<SHARD, ShardSync, NoSync>::type sync) {
     static_assert(TILE % (4 * THREADS) == 0, "tile must be a whole number of 4-wide vectors per thread");
@@ -206,18 +217,25 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename s
     T sum = T(0);
     if (MODE == MODE_CSR_ACC && re > rs) sum = a.y[r];
     [[maybe_unused]] const uint64_t keep = KEEP ? l2_policy_evict_last() : 0;
+    [[maybe_unused]] const uint64_t first = KEEP == 2 ? l2_policy_evict_first() : 0;
     for (int base = b0 & ~3; base < b1; base += TILE) {
 #pragma unroll
         for (int v = 0; v < TILE / (4 * THREADS); v++) {
             const int o = (v * THREADS + tid) * 4;
             const int j = base + o;
             if (j + 4 <= b1) {
-                const int4 c = ld_stream(reinterpret_cast<const int4 *>(a.col + j));
+                int4 c;
                 V4<T> w;
-                if (is_csr(MODE)) w = V4<T>::load(a.val + j);
-                else w = V4<T>{{T(0), T(0), T(0), T(0)}};
+                if constexpr (KEEP == 2) {
+                    c = ld_first(reinterpret_cast<const int4 *>(a.col + j), first);
+                    w = V4<T>::load_first(a.val + j, first);
+                } else {
+                    c = ld_stream(reinterpret_cast<const int4 *>(a.col + j));
+                    if (is_csr(MODE)) w = V4<T>::load(a.val + j);
+                    else w = V4<T>{{T(0), T(0), T(0), T(0)}};
+                }
                 T p0, p1, p2, p3;
-                if constexpr (KEEP) {   // x entries marked evict-last in L2: for vectors that fit L2 but are gathered at random
+                if constexpr (KEEP != 0) {   // x entries marked evict-last in L2: for vectors that fit L2 but are gathered at random
                     p0 = product_keep<T, MODE>(a, w.v[0], c.x, keep); p1 = product_keep<T, MODE>(a, w.v[1], c.y, keep);
                     p2 = product_keep<T, MODE>(a, w.v[2], c.z, keep); p3 = product_keep<T, MODE>(a, w.v[3], c.w, keep);
                 } else {
@@ -540,7 +558,8 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
 #define CME213_TRY_CSR(TH, TL) \
                 if (T_ == TH && L_ == TL) { \
                     const int64_t nb = div_up(rows, TH); \
-                    if (K_) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, true><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); \
+                    if (K_ == 2) { if constexpr (MODE == MODE_CSR) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, 2><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); } \
+                    else if (K_) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, 1><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); \
                     else csr_stream_lean_kernel<T, MODE, TH, TL, false><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); \
                     CME213_LAUNCHED(ctx, "csr_stream_lean_kernel(cfg)"); \
                     return CME213_OK; \
@@ -553,7 +572,7 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
 #endif
             const int64_t blocks = div_up(rows, THREADS);
             if (padded) csr_stream_lean_kernel<T, MODE, THREADS, TILE, true><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end, NoSync());
-            else if (keep) csr_stream_lean_kernel<T, MODE, THREADS, TILE, false, false, true><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end, NoSync());
+            else if (keep) csr_stream_lean_kernel<T, MODE, THREADS, TILE, false, false, 1><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end, NoSync());
             else csr_stream_lean_kernel<T, MODE, THREADS, TILE, false><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end, NoSync());
         }
         CME213_LAUNCHED(ctx, "csr_stream_kernel");
@@ -811,7 +830,7 @@ static int spmv_csr_acc(cme213_ctx *ctx, int64_t rows_local, const int32_t *d_ro
     constexpr int THREADS = sizeof(T) == 8 ? 128 : 256, TILE = THREADS * 8;
     const int64_t blocks = div_up(rows_local, THREADS);
     if (blocks > 0x7FFFFFFFLL) { set_error("spmv_csr acc: too many rows"); return CME213_ERR_UNSUPPORTED; }
-    if (keep) csr_stream_lean_kernel<T, MODE_CSR_ACC, THREADS, TILE, false, false, true><<<(unsigned)blocks, THREADS, 0, st>>>(a, 0, rows_local, NoSync());
+    if (keep) csr_stream_lean_kernel<T, MODE_CSR_ACC, THREADS, TILE, false, false, 1><<<(unsigned)blocks, THREADS, 0, st>>>(a, 0, rows_local, NoSync());
     else csr_stream_lean_kernel<T, MODE_CSR_ACC, THREADS, TILE, false><<<(unsigned)blocks, THREADS, 0, st>>>(a, 0, rows_local, NoSync());
     CME213_LAUNCHED(ctx, "csr_stream_lean_kernel<acc>");
     return CME213_OK;
