@@ -54,6 +54,10 @@ PROTOTYPES = {
     "cme213_segscan_exclusive_f32": (_i, [_p, _p, _p, _p, _i64, _p]),
     "cme213_mul_gather_segscan_f32": (_i, [_p, _p, _p, _p, _p, _p, _i64, _p]),
     "cme213_mul_gather_segscan_f64": (_i, [_p, _p, _p, _p, _p, _p, _i64, _p]),
+    "cme213_gather_f32": (_i, [_p, _p, _p, _p, _i64, _p]),
+    "cme213_gather_f64": (_i, [_p, _p, _p, _p, _i64, _p]),
+    "cme213_mul_segscan_f32": (_i, [_p, _p, _p, _p, _p, _i64, _p]),
+    "cme213_mul_segscan_f64": (_i, [_p, _p, _p, _p, _p, _i64, _p]),
     "cme213_spmv_csr_f32": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _i, _p]),
     "cme213_spmv_csr_f64": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _i, _p]),
     "cme213_csr_plan_create": (_i, [_p, _i64, _i64, _i64, _p, _i, _p, C.POINTER(_p)]),

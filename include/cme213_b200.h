@@ -148,6 +148,17 @@ int cme213_mul_gather_segscan_f32(cme213_ctx *ctx, const float *d_a, const int32
 int cme213_mul_gather_segscan_f64(cme213_ctx *ctx, const double *d_a, const int32_t *d_k, const double *d_x,
                                   const uint32_t *d_flag_bits, double *d_b, int64_t n, void *stream);
 
+/* The same step with the gather hoisted out of the iteration: xx[i] = x[k[i]] once (cme213_gather_*), then
+ * b = inclusive segmented sum of a[i]*xx[i] per iteration -- pure streaming, no random access.  The rounded product and
+ * the segmented sum are those of the fused step; only the tiling of the scan differs (same tolerance).  d_b == d_a allowed.
+ * reference: hw/hw_final/programming/fp.cu:124-125 (xx = x[k] flattened once), :139-149 / :174-180 (multiply, scan). */
+int cme213_gather_f32(cme213_ctx *ctx, const float *d_x, const int32_t *d_k, float *d_xx, int64_t n, void *stream);
+int cme213_gather_f64(cme213_ctx *ctx, const double *d_x, const int32_t *d_k, double *d_xx, int64_t n, void *stream);
+int cme213_mul_segscan_f32(cme213_ctx *ctx, const float *d_a, const float *d_xx, const uint32_t *d_flag_bits, float *d_b,
+                           int64_t n, void *stream);
+int cme213_mul_segscan_f64(cme213_ctx *ctx, const double *d_a, const double *d_xx, const uint32_t *d_flag_bits, double *d_b,
+                           int64_t n, void *stream);
+
 /* ---- CSR SpMV ---------------------------------------------------------- */
 /* y[r] = sum_j val[j] * x[col[j]], j in [row_ptr[r], row_ptr[r+1]), for rows r in [row_begin, row_end).
  * row_ptr, y are indexed by r itself (not r - row_begin) so a caller can split one matrix into
