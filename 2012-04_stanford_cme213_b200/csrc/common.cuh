@@ -91,6 +91,30 @@ __device__ __forceinline__ double ld_keep(const double *p, uint64_t pol) {
     return v;
 }
 
+// Streamed (read-once) data with an explicit evict-first L2 policy instead of the .cs qualifier.
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ int4 ld_first(const int4 *p, uint64_t pol) {
+    int4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.s32 {%0,%1,%2,%3}, [%4], %5;"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p), "l"(pol));
+    return v;
+}
+__device__ __forceinline__ float4 ld_first(const float4 *p, uint64_t pol) {
+    float4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.f32 {%0,%1,%2,%3}, [%4], %5;"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p), "l"(pol));
+    return v;
+}
+__device__ __forceinline__ double2 ld_first(const double2 *p, uint64_t pol) {
+    double2 v;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.f64 {%0,%1}, [%2], %3;" : "=d"(v.x), "=d"(v.y) : "l"(p), "l"(pol));
+    return v;
+}
+
 __device__ __forceinline__ uint32_t hash32(uint32_t seed, uint64_t idx) {
     // counter-based hash (two rounds of a 32-bit finaliser over a 64-bit counter); restated in
     // numpy by oracle/generators.py so tests can rebuild any generated input bit for bit.

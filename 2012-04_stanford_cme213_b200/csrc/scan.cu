@@ -90,6 +90,93 @@ struct PlainPolicy {
     }
 };
 
+// ---- final project step with the gather hoisted: v = a[i] * xx[i], inclusive segmented sum ------------------------
+// x[k[i]] is the same in every one of the N iterations (only a changes: a <- b), which the reference exploits by
+// flattening xx = x[k] once (fp.cu:124-125, on the host).  Here the flattening runs once on the device inside the timed
+// region (cme213_gather_*), and the remaining work per iteration is pure streaming: two value streams and the flag
+// words in, one value stream out, through the bulk-copy pipeline -- no random gather, so no L2-sector bound.
+template <typename T_>
+struct MulPolicy {
+    using T = T_;
+    using Aux = NoAux;
+    static constexpr int IPV = 16 / sizeof(T);
+    static constexpr bool SEG = true;
+    static constexpr bool BULK = true;
+    static constexpr bool INCLUSIVE_OUT = true;
+    using V16T = typename V16<T_>::type;
+    static constexpr int NIN = 3;   // a, xx, head-flag words
+    __host__ __device__ static constexpr int tile_bytes(int s, int tile_items) { return s < 2 ? tile_items * (int)sizeof(T) : tile_items / 8; }
+    const T *a;
+    const T *xx;
+    const uint32_t *flag_bits;
+    T *b;
+    __host__ __device__ T *out_ptr() const { return b; }
+    __host__ __device__ const void *in_ptr(int s) const { return s == 0 ? (const void *)a : s == 1 ? (const void *)xx : (const void *)flag_bits; }
+
+    __device__ void load_smem(const unsigned char *const (&sin)[NIN], int vec, int, int64_t, int64_t, T (&v)[IPV],
+                              unsigned &head, Aux &) const {
+        typename V16<T>::type av = *reinterpret_cast<const typename V16<T>::type *>(sin[0] + (size_t)vec * 16);
+        typename V16<T>::type xv = *reinterpret_cast<const typename V16<T>::type *>(sin[1] + (size_t)vec * 16);
+        const T *ae = reinterpret_cast<const T *>(&av), *xe = reinterpret_cast<const T *>(&xv);
+#pragma unroll
+        for (int j = 0; j < IPV; j++) v[j] = mul_rn(ae[j], xe[j]);
+        head = head_bits<IPV>(reinterpret_cast<const uint32_t *>(sin[2]), (int64_t)vec * IPV);
+    }
+    __device__ void load(int64_t idx, int64_t n, bool fast, T (&v)[IPV], unsigned &head, Aux &) const {
+        head = 0;
+        if (fast) {
+            typename V16<T>::type av = ld_stream(reinterpret_cast<const typename V16<T>::type *>(a + idx));
+            typename V16<T>::type xv = ld_stream(reinterpret_cast<const typename V16<T>::type *>(xx + idx));
+            const T *ae = reinterpret_cast<const T *>(&av), *xe = reinterpret_cast<const T *>(&xv);
+#pragma unroll
+            for (int j = 0; j < IPV; j++) v[j] = mul_rn(ae[j], xe[j]);
+            head = head_bits<IPV>(flag_bits, idx);
+        } else {
+#pragma unroll
+            for (int j = 0; j < IPV; j++) {
+                v[j] = T(0);
+                if (idx + j < n) {
+                    v[j] = mul_rn(a[idx + j], xx[idx + j]);
+                    head |= ((flag_bits[(idx + j) >> 5] >> (unsigned)((idx + j) & 31)) & 1u) << j;
+                }
+            }
+        }
+    }
+    __device__ void store(int64_t idx, int64_t n, bool fast, const T (&incl)[IPV], const T (&)[IPV], const Aux &) const {
+        if (fast) {
+            typename V16<T>::type o;
+            T *e = reinterpret_cast<T *>(&o);
+#pragma unroll
+            for (int j = 0; j < IPV; j++) e[j] = incl[j];
+            st_stream(reinterpret_cast<typename V16<T>::type *>(b + idx), o);
+        } else {
+#pragma unroll
+            for (int j = 0; j < IPV; j++)
+                if (idx + j < n) b[idx + j] = incl[j];
+        }
+    }
+};
+
+// xx[i] = x[k[i]]: four consecutive indices per thread (one 128-bit load of k, one 128-bit store of xx), x gathers evict-last
+template <typename T>
+__global__ void __launch_bounds__(256) gather_kernel(const T *__restrict__ x, const int32_t *__restrict__ k, T *__restrict__ xx, int64_t n, int vec_ok) {
+    const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i >= n) return;
+    const uint64_t pol = l2_policy_evict_last();
+    if (vec_ok && i + 4 <= n) {
+        const int4 kv = ld_stream(reinterpret_cast<const int4 *>(k + i));
+        const T v0 = ld_keep(x + kv.x, pol), v1 = ld_keep(x + kv.y, pol), v2 = ld_keep(x + kv.z, pol), v3 = ld_keep(x + kv.w, pol);
+        if constexpr (sizeof(T) == 4) {
+            st_stream(reinterpret_cast<float4 *>(xx + i), make_float4(v0, v1, v2, v3));
+        } else {
+            st_stream(reinterpret_cast<double2 *>(xx + i), make_double2(v0, v1));
+            st_stream(reinterpret_cast<double2 *>(xx + i) + 1, make_double2(v2, v3));
+        }
+    } else {
+        for (int j = 0; j < 4 && i + j < n; j++) xx[i + j] = __ldg(x + k[i + j]);
+    }
+}
+
 // ---- final project step: v = a[i] * x[k[i]], inclusive segmented sum ------------------------------
 template <typename T_>
 struct MulGatherPolicy {
@@ -273,7 +360,12 @@ int run(cme213_ctx *ctx, const P &p, int64_t n, bool vec_ok, void *stream, const
             cudaStream_t st = (cudaStream_t)stream;
             if (vec_ok && n >= ((int64_t)1 << 20)) {
 #define CME213_TRY_BLOCKED(T, V, S, D) if (T_ == T && V_ == V && S_ == -(S) && D_ == D) return scan::launch_bulk<P, T, V, S, 5, true, D>(ctx, p, n, st, name, nullptr, 0);
-                CME213_TRY_BLOCKED(1024, 3, 4, 2) CME213_TRY_BLOCKED(896, 5, 3, 1) CME213_TRY_BLOCKED(640, 5, 4, 2)
+                if constexpr (P::NIN >= 3) {   // two value streams per tile: smaller tiles
+                    CME213_TRY_BLOCKED(640, 3, 3, 1) CME213_TRY_BLOCKED(640, 2, 4, 2) CME213_TRY_BLOCKED(768, 2, 4, 2) CME213_TRY_BLOCKED(512, 3, 4, 2)
+                    CME213_TRY_BLOCKED(1024, 2, 3, 1) CME213_TRY_BLOCKED(896, 2, 3, 1)
+                } else {
+                    CME213_TRY_BLOCKED(1024, 3, 4, 2) CME213_TRY_BLOCKED(896, 5, 3, 1) CME213_TRY_BLOCKED(640, 5, 4, 2)
+                }
 #undef CME213_TRY_BLOCKED
             }
         }
@@ -367,6 +459,42 @@ CME213_API int cme213_mul_gather_segscan_f64(cme213_ctx *ctx, const double *d_a,
                                              const double *d_x, const uint32_t *d_flag_bits, double *d_b, int64_t n,
                                              void *stream) {
     return mul_gather_impl<double>(ctx, d_a, d_k, d_x, d_flag_bits, d_b, n, stream, "mul_gather_segscan_f64");
+}
+
+template <typename T>
+static int mul_segscan_impl(cme213_ctx *ctx, const T *d_a, const T *d_xx, const uint32_t *d_flag_bits, T *d_b, int64_t n, void *stream,
+                            const char *name) {
+    CME213_CHECK_CTX(ctx);
+    if (n < 0 || (n > 0 && (!d_a || !d_xx || !d_flag_bits || !d_b))) { set_error("%s: bad arguments", name); return CME213_ERR_INVALID; }
+    if (n == 0) return CME213_OK;
+    MulPolicy<T> p{d_a, d_xx, d_flag_bits, d_b};
+    return run(ctx, p, n, aligned16(d_a) && aligned16(d_xx) && aligned16(d_b) && aligned16(d_flag_bits), stream, name);
+}
+CME213_API int cme213_mul_segscan_f32(cme213_ctx *ctx, const float *d_a, const float *d_xx, const uint32_t *d_flag_bits, float *d_b,
+                                      int64_t n, void *stream) {
+    return mul_segscan_impl<float>(ctx, d_a, d_xx, d_flag_bits, d_b, n, stream, "mul_segscan_f32");
+}
+CME213_API int cme213_mul_segscan_f64(cme213_ctx *ctx, const double *d_a, const double *d_xx, const uint32_t *d_flag_bits, double *d_b,
+                                      int64_t n, void *stream) {
+    return mul_segscan_impl<double>(ctx, d_a, d_xx, d_flag_bits, d_b, n, stream, "mul_segscan_f64");
+}
+template <typename T>
+static int gather_impl(cme213_ctx *ctx, const T *d_x, const int32_t *d_k, T *d_xx, int64_t n, void *stream) {
+    CME213_CHECK_CTX(ctx);
+    if (n < 0 || (n > 0 && (!d_x || !d_k || !d_xx))) { set_error("gather: bad arguments"); return CME213_ERR_INVALID; }
+    if (n == 0) return CME213_OK;
+    DeviceGuard g(ctx->device);
+    const int64_t blocks = div_up(div_up(n, 4), 256);
+    if (blocks > 0x7FFFFFFFLL) { set_error("gather: n too large"); return CME213_ERR_UNSUPPORTED; }
+    gather_kernel<T><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(d_x, d_k, d_xx, n, (aligned16(d_k) && aligned16(d_xx)) ? 1 : 0);
+    CME213_LAUNCHED(ctx, "gather_kernel");
+    return CME213_OK;
+}
+CME213_API int cme213_gather_f32(cme213_ctx *ctx, const float *d_x, const int32_t *d_k, float *d_xx, int64_t n, void *stream) {
+    return gather_impl<float>(ctx, d_x, d_k, d_xx, n, stream);
+}
+CME213_API int cme213_gather_f64(cme213_ctx *ctx, const double *d_x, const int32_t *d_k, double *d_xx, int64_t n, void *stream) {
+    return gather_impl<double>(ctx, d_x, d_k, d_xx, n, stream);
 }
 
 template <typename T>

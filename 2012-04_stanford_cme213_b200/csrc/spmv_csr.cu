@@ -140,12 +140,21 @@ template <> struct V4<float> {
         float4 t = ld_stream(reinterpret_cast<const float4 *>(p));
         return V4{{t.x, t.y, t.z, t.w}};
     }
+    __device__ static V4 load_first(const float *p, uint64_t pol) {
+        float4 t = ld_first(reinterpret_cast<const float4 *>(p), pol);
+        return V4{{t.x, t.y, t.z, t.w}};
+    }
 };
 template <> struct V4<double> {
     double v[4];
     __device__ static V4 load(const double *p) {
         double2 t0 = ld_stream(reinterpret_cast<const double2 *>(p));
         double2 t1 = ld_stream(reinterpret_cast<const double2 *>(p) + 1);
+        return V4{{t0.x, t0.y, t1.x, t1.y}};
+    }
+    __device__ static V4 load_first(const double *p, uint64_t pol) {
+        double2 t0 = ld_first(reinterpret_cast<const double2 *>(p), pol);
+        double2 t1 = ld_first(reinterpret_cast<const double2 *>(p) + 1, pol);
         return V4{{t0.x, t0.y, t1.x, t1.y}};
     }
 };
@@ -167,7 +176,9 @@ __device__ __forceinline__ void epilogue_lean(const Args<T> &a, int64_t r, T sum
 // (8 CTAs of 256 threads per SM); the feature-complete kernel below (block lists, padded products) needs 38-40
 // and measured 5-30 % slower on the same inputs, so it only runs when one of its features is asked for.
 struct NoSync {};
-template <typename T, int MODE, int THREADS, int TILE, bool PADDED, bool SHARD = false, bool KEEP = false>
+// KEEP: 0 = plain (.cs streams, default-policy gathers), 1 = x gathers evict-last, 2 = 1 + col/val with an explicit
+// evict-first policy and no L1 allocation (tuning builds only)
+template <typename T, int MODE, int THREADS, int TILE, bool PADDED, bool SHARD = false, int KEEP = 0>
 __global__ void __launch_bounds__(THREADS)
 csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename std::conditional<SHARD, ShardSync, NoSync>::type sync) {
     static_assert(TILE % (4 * THREADS) == 0, "tile must be a whole number of 4-wide vectors per thread");
@@ -206,18 +217,25 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename s
     T sum = T(0);
     if (MODE == MODE_CSR_ACC && re > rs) sum = a.y[r];
     [[maybe_unused]] const uint64_t keep = KEEP ? l2_policy_evict_last() : 0;
+    [[maybe_unused]] const uint64_t first = KEEP == 2 ? l2_policy_evict_first() : 0;
     for (int base = b0 & ~3; base < b1; base += TILE) {
 #pragma unroll
         for (int v = 0; v < TILE / (4 * THREADS); v++) {
             const int o = (v * THREADS + tid) * 4;
             const int j = base + o;
             if (j + 4 <= b1) {
-                const int4 c = ld_stream(reinterpret_cast<const int4 *>(a.col + j));
+                int4 c;
                 V4<T> w;
-                if (is_csr(MODE)) w = V4<T>::load(a.val + j);
-                else w = V4<T>{{T(0), T(0), T(0), T(0)}};
+                if constexpr (KEEP == 2) {
+                    c = ld_first(reinterpret_cast<const int4 *>(a.col + j), first);
+                    w = V4<T>::load_first(a.val + j, first);
+                } else {
+                    c = ld_stream(reinterpret_cast<const int4 *>(a.col + j));
+                    if (is_csr(MODE)) w = V4<T>::load(a.val + j);
+                    else w = V4<T>{{T(0), T(0), T(0), T(0)}};
+                }
                 T p0, p1, p2, p3;
-                if constexpr (KEEP) {   // x entries marked evict-last in L2: for vectors that fit L2 but are gathered at random
+                if constexpr (KEEP != 0) {   // x entries marked evict-last in L2: for vectors that fit L2 but are gathered at random
                     p0 = product_keep<T, MODE>(a, w.v[0], c.x, keep); p1 = product_keep<T, MODE>(a, w.v[1], c.y, keep);
                     p2 = product_keep<T, MODE>(a, w.v[2], c.z, keep); p3 = product_keep<T, MODE>(a, w.v[3], c.w, keep);
                 } else {
@@ -263,6 +281,86 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename s
                 }
             }
         }
+    }
+}
+
+// Persistent, software-pipelined form of the lean kernel.  The lean kernel's CTA goes through three dependent round trips
+// to memory (row pointers -> col/val -> x) before it can sum, and hides them only by having many CTAs resident; on a
+// matrix of a few waves (config C1: 4096 CTAs, 3.5 waves) there is nothing to hide them behind.  Here a CTA walks over
+// row blocks b, b + grid, b + 2 grid, ... and keeps three blocks in flight: the row pointers of block i+2, the col/val
+// vectors of block i+1 (in registers) and the gathers / sums of block i, with two product buffers so that one barrier per
+// block is enough.  Same products, same order: bit-identical to the CPU loop.  Blocks with more than TILE nonzeros fall
+// back to the multi-pass loop inside the same kernel.
+template <typename T, int THREADS, int TILE>
+__global__ void __launch_bounds__(THREADS)
+csr_stream_pipe_kernel(Args<T> a, int64_t row_begin, int64_t row_end, int64_t nblocks) {
+    constexpr int V = TILE / (4 * THREADS);
+    static_assert(TILE % (4 * THREADS) == 0 && V >= 1, "tile = whole 4-wide vectors per thread");
+    __shared__ __align__(16) T prod[2][TILE];
+    const int tid = threadIdx.x;
+    const int64_t G = gridDim.x;
+    struct Ptr { int rs, re, b0, b1; };
+    struct Vec { int4 c[V]; V4<T> w[V]; };
+    auto load_ptr = [&](int64_t blk) {
+        Ptr p{0, 0, 0, 0};
+        if (blk < nblocks) {
+            const int64_t r0 = row_begin + blk * THREADS, r = r0 + tid, rl = r0 + THREADS < row_end ? r0 + THREADS : row_end;
+            if (r < row_end) { p.rs = a.row_ptr[r]; p.re = a.row_ptr[r + 1]; }
+            p.b0 = __ldg(a.row_ptr + r0);
+            p.b1 = __ldg(a.row_ptr + rl);
+        }
+        return p;
+    };
+    auto load_vec = [&](const Ptr &p, Vec &v) {   // the first TILE entries of the block, whole vectors only
+        const int base = p.b0 & ~3;
+#pragma unroll
+        for (int k = 0; k < V; k++) {
+            const int j = base + (k * THREADS + tid) * 4;
+            if (j + 4 <= p.b1) {
+                v.c[k] = ld_stream(reinterpret_cast<const int4 *>(a.col + j));
+                v.w[k] = V4<T>::load(a.val + j);
+            }
+        }
+    };
+    int64_t blk = blockIdx.x;
+    Ptr p0 = load_ptr(blk), p1 = load_ptr(blk + G);
+    Vec v0, v1;
+    load_vec(p0, v0);
+    for (int it = 0; blk < nblocks; blk += G, it++) {
+        const Ptr p2 = load_ptr(blk + 2 * G);          // block i+2: row pointers
+        load_vec(p1, v1);                              // block i+1: col / val (p1 arrived during the previous iteration)
+        T *pr = prod[it & 1];
+        const int64_t r = row_begin + blk * THREADS + tid;
+        T sum = T(0);
+        bool first = true;
+        for (int base = p0.b0 & ~3; base < p0.b1; base += TILE, first = false) {
+            if (!first) __syncthreads();               // rare multi-pass block: the previous pass's products are being summed
+#pragma unroll
+            for (int k = 0; k < V; k++) {
+                const int o = (k * THREADS + tid) * 4;
+                const int j = base + o;
+                if (j + 4 <= p0.b1) {
+                    int4 c;
+                    V4<T> w;
+                    if (first) { c = v0.c[k]; w = v0.w[k]; }
+                    else { c = ld_stream(reinterpret_cast<const int4 *>(a.col + j)); w = V4<T>::load(a.val + j); }
+                    pr[o + 0] = mul_rn(w.v[0], __ldg(a.x + c.x));
+                    pr[o + 1] = mul_rn(w.v[1], __ldg(a.x + c.y));
+                    pr[o + 2] = mul_rn(w.v[2], __ldg(a.x + c.z));
+                    pr[o + 3] = mul_rn(w.v[3], __ldg(a.x + c.w));
+                } else {
+#pragma unroll
+                    for (int t = 0; t < 4; t++)
+                        if (j + t < p0.b1) pr[o + t] = mul_rn(a.val[j + t], __ldg(a.x + a.col[j + t]));
+                }
+            }
+            __syncthreads();
+            const int lo = p0.rs > base ? p0.rs : base;
+            const int hi = p0.re < base + TILE ? p0.re : base + TILE;
+            for (int j = lo; j < hi; j++) sum = add_rn(sum, pr[j - base]);
+        }
+        if (r < row_end) st_stream(a.y + r, sum);
+        p0 = p1; p1 = p2; v0 = v1;
     }
 }
 
@@ -358,6 +456,8 @@ struct cme213_csr_plan {
     int long_lanes = 32;
     double mean = 0, long_nnz_fraction = 0;
     int max_len = 0;
+    double long_block_nnz_fraction = 0;
+    bool ordered_only = false;            // CME213_CSR_AUTO_ORDERED: only kernels that keep the CPU loop's summation order
     int32_t *d_short = nullptr, *d_long = nullptr;   // BINNED: 256-row block numbers (counted from row_begin)
     int64_t n_short = 0, n_long = 0;
     char text[320] = "";
@@ -365,18 +465,31 @@ struct cme213_csr_plan {
 
 namespace {
 constexpr int PLAN_BLOCK_ROWS = 256;       // = cme213_spmv_csr_block_rows()
-constexpr int PLAN_LONG_ROW = 96;          // a row this long is better served by a warp than by one thread of the stream kernel
-constexpr double PLAN_VECTOR_MEAN = 48.0;  // mean row length from which CSR-vector wins on the whole matrix
-constexpr double PLAN_BINNED_FRACTION = 0.20;   // share of the nonzeros in long rows that makes a split launch worth it
+// Thresholds read from profiles/r02_csr_kernel_sweep.csv (134 M nonzeros per matrix, uniform and banded columns):
+//   rows of 1-2 entries: one thread per row is already coalesced enough and skips the shared-memory round trip (scalar 0.59 ms
+//     vs stream 0.66 on 2 per row);
+//   every row 8, 16, ... 128 long: stream-padded (0.24-0.26 ms where plain stream needs 0.33-0.66 and the best vector 0.23-0.30);
+//   mean >= 96 (or regular rows beyond 128): vector, 16 lanes below a mean of 128, 32 above (256 per row: 0.16 ms vs stream 0.72);
+//   otherwise stream.  Evict-last x gathers measured exactly like plain stream on every matrix: not used.
+//   BINNED only when whole 256-row blocks are long (>= 32 per row on average) and hold >= 30 % of the nonzeros: the block-list
+//   kernels cost ~10 % more than the plain one, which scattered long rows (the power-law matrix) do not pay back.
+constexpr double PLAN_SCALAR_MEAN = 2.5;
+constexpr double PLAN_VECTOR_MEAN = 96.0;
+constexpr int PLAN_PADDED_MAX = 128;
+constexpr int PLAN_LONG_ROW = 96;          // statistics only: share of the nonzeros in rows at least this long
+constexpr int PLAN_LONG_BLOCK_MEAN = 32;   // a 256-row block is "long" from this mean row length on
+constexpr double PLAN_BINNED_FRACTION = 0.30;
 
 __global__ void plan_block_class_kernel(int64_t nblocks, int64_t rows, const int32_t *__restrict__ row_ptr, int thresh_nnz,
-                                        uint32_t *is_long) {
+                                        uint32_t *is_long, unsigned long long *long_nnz) {
     const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (b > nblocks) return;
     uint32_t v = 0;
     if (b < nblocks) {
         const int64_t r0 = b * PLAN_BLOCK_ROWS, r1 = r0 + PLAN_BLOCK_ROWS < rows ? r0 + PLAN_BLOCK_ROWS : rows;
-        v = (row_ptr[r1] - row_ptr[r0]) >= thresh_nnz ? 1u : 0u;
+        const int cnt = row_ptr[r1] - row_ptr[r0];
+        v = cnt >= thresh_nnz ? 1u : 0u;
+        if (v) atomicAdd(long_nnz, (unsigned long long)cnt);
     }
     is_long[b] = v;   // entry nblocks = 0: its scan value is the number of long blocks
 }
@@ -425,28 +538,33 @@ int plan_build(cme213_ctx *ctx, cme213_csr_plan *p, const int32_t *d_row_ptr, cu
     p->nnz = (int64_t)nnz;
     p->mean = rows ? (double)nnz / (double)rows : 0.0;
     p->long_nnz_fraction = nnz ? (double)long_nnz / (double)nnz : 0.0;
-    const size_t x_bytes = (size_t)p->num_cols * (size_t)p->elem_bytes;
-    if (nonempty_bins == 1 && only_len >= 8 && only_len % 8 == 0 && only_len < PLAN_VECTOR_MEAN) {
+    const bool regular = nonempty_bins == 1;
+    const bool ordered_only = p->ordered_only;
+    bool try_binned = false;
+    if (regular && only_len >= 8 && only_len % 8 == 0 && (only_len <= PLAN_PADDED_MAX || ordered_only)) {
         // every row has 8, 16, 32 ... entries: the per-row sums of the stream kernel would walk shared memory with a
-        // power-of-two stride; the padded variant removes the bank conflicts (0.43 -> 0.77 of peak on 16 per row)
+        // power-of-two stride; the padded variant removes the bank conflicts
         p->kernel = CME213_CSR_STREAM_PADDED;
-    } else if (p->mean >= PLAN_VECTOR_MEAN) {
-        p->kernel = CME213_CSR_VECTOR | (32 << 8);
-    } else if (p->long_nnz_fraction >= PLAN_BINNED_FRACTION && rows >= 4 * PLAN_BLOCK_ROWS) {
-        p->kernel = CME213_CSR_BINNED;
+    } else if (p->mean <= PLAN_SCALAR_MEAN) {
+        p->kernel = CME213_CSR_SCALAR;
+    } else if (p->mean >= PLAN_VECTOR_MEAN && !ordered_only) {
+        p->kernel = CME213_CSR_VECTOR | ((p->mean >= 128 ? 32 : 16) << 8);
     } else {
-        // x larger than what L1 holds, smaller than L2: keep it there against the matrix streaming through
-        p->kernel = (x_bytes >= ((size_t)8 << 20) && x_bytes <= ((size_t)96 << 20)) ? CME213_CSR_STREAM_KEEP : CME213_CSR_STREAM;
+        p->kernel = CME213_CSR_STREAM;
+        try_binned = !ordered_only && p->long_nnz_fraction >= PLAN_BINNED_FRACTION && rows >= 4 * PLAN_BLOCK_ROWS;
     }
-    if (p->kernel == CME213_CSR_BINNED) {
+    if (try_binned) {
         const int64_t nblocks = div_up(rows, PLAN_BLOCK_ROWS);
         const int64_t n = nblocks + 1;
         uint32_t *d_flag = nullptr, *d_excl = nullptr;
+        unsigned long long *d_long_nnz = nullptr, h_long_nnz = 0;
         CME213_CUDA(cudaMalloc(&d_flag, (size_t)n * 4));
         CME213_CUDA(cudaMalloc(&d_excl, (size_t)n * 4));
+        CME213_CUDA(cudaMalloc(&d_long_nnz, 8));
+        CME213_CUDA(cudaMemsetAsync(d_long_nnz, 0, 8, st));
         CME213_CUDA(cudaMalloc(&p->d_short, (size_t)nblocks * 4));
         CME213_CUDA(cudaMalloc(&p->d_long, (size_t)nblocks * 4));
-        plan_block_class_kernel<<<(unsigned)div_up(n, 256), 256, 0, st>>>(nblocks, rows, ptr, PLAN_BLOCK_ROWS * 32, d_flag);
+        plan_block_class_kernel<<<(unsigned)div_up(n, 256), 256, 0, st>>>(nblocks, rows, ptr, PLAN_BLOCK_ROWS * PLAN_LONG_BLOCK_MEAN, d_flag, d_long_nnz);
         CME213_LAUNCHED(ctx, "plan_block_class_kernel");
         rc = cme213_exclusive_scan_u32(ctx, d_flag, d_excl, n, st);
         if (rc) return rc;
@@ -454,31 +572,43 @@ int plan_build(cme213_ctx *ctx, cme213_csr_plan *p, const int32_t *d_row_ptr, cu
         CME213_LAUNCHED(ctx, "plan_block_lists_kernel");
         uint32_t nl = 0;
         CME213_CUDA(cudaMemcpyAsync(&nl, d_excl + nblocks, 4, cudaMemcpyDeviceToHost, st));
+        CME213_CUDA(cudaMemcpyAsync(&h_long_nnz, d_long_nnz, 8, cudaMemcpyDeviceToHost, st));
         CME213_CUDA(cudaStreamSynchronize(st));
         cudaFree(d_flag);
         cudaFree(d_excl);
+        cudaFree(d_long_nnz);
         p->n_long = nl;
         p->n_short = nblocks - nl;
-        if (p->n_long == 0) p->kernel = CME213_CSR_STREAM;         // long rows spread too thinly to fill a block
-        else if (p->n_short == 0) p->kernel = CME213_CSR_VECTOR | (32 << 8);
+        p->long_block_nnz_fraction = nnz ? (double)h_long_nnz / (double)nnz : 0.0;
+        if (p->n_short == 0) p->kernel = CME213_CSR_VECTOR | (32 << 8);
+        else if (p->n_long > 0 && p->long_block_nnz_fraction >= PLAN_BINNED_FRACTION) p->kernel = CME213_CSR_BINNED;
+        if ((p->kernel & 0xFF) != CME213_CSR_BINNED) {   // long rows spread too thinly over the blocks: one plain launch is faster
+            cudaFree(p->d_short); cudaFree(p->d_long);
+            p->d_short = p->d_long = nullptr;
+        }
     }
-    const char *names[] = {"auto", "scalar", "vector", "stream", "stream-padded", "stream-keep", "binned"};
+    const char *names[] = {"auto", "scalar", "vector", "stream", "stream-padded", "stream-keep", "binned", "stream-pipe"};
     const int kind = p->kernel & 0xFF;
-    snprintf(p->text, sizeof(p->text), "%s%s: rows %lld, mean row %.2f, longest %d, %.1f%% of the nonzeros in rows >= %d%s", names[kind],
-             kind == CME213_CSR_VECTOR ? " (32 lanes)" : "", (long long)rows, p->mean, p->max_len, 100.0 * p->long_nnz_fraction, PLAN_LONG_ROW,
-             kind == CME213_CSR_BINNED ? "; short blocks -> stream, long blocks -> vector(32)" : "");
+    char lanes[24] = "";
+    if (kind == CME213_CSR_VECTOR) snprintf(lanes, sizeof(lanes), " (%d lanes)", (p->kernel >> 8) & 0xFF);
+    snprintf(p->text, sizeof(p->text), "%s%s%s: rows %lld, mean row %.2f, longest %d, %s, %.1f%% of the nonzeros in rows >= %d%s", names[kind], lanes,
+             ordered_only ? " [order-preserving kernels only]" : "", (long long)rows, p->mean, p->max_len,
+             regular ? "all rows equally long" : "irregular rows", 100.0 * p->long_nnz_fraction, PLAN_LONG_ROW,
+             kind == CME213_CSR_BINNED ? "; short 256-row blocks -> stream, long blocks -> vector(32)" : "");
     return CME213_OK;
 }
 
 // the plan for (row_ptr, range), from the context's cache or built now (first call: synchronises)
 int plan_for(cme213_ctx *ctx, const int32_t *row_ptr, int64_t row_begin, int64_t row_end, int64_t num_cols, int elem_bytes,
-             cudaStream_t st, cme213_csr_plan **out) {
+             bool ordered_only, cudaStream_t st, cme213_csr_plan **out) {
     for (int i = 0; i < cme213_ctx::CSR_CACHE; i++) {
         const auto &e = ctx->csr_cache[i];
-        if (e.plan && e.row_ptr == row_ptr && e.row_begin == row_begin && e.row_end == row_end) { *out = e.plan; return CME213_OK; }
+        if (e.plan && e.row_ptr == row_ptr && e.row_begin == row_begin && e.row_end == row_end && e.plan->ordered_only == ordered_only &&
+            e.plan->elem_bytes == elem_bytes) { *out = e.plan; return CME213_OK; }
     }
     cme213_csr_plan *p = new cme213_csr_plan();
     p->device = ctx->device; p->row_begin = row_begin; p->row_end = row_end; p->num_cols = num_cols; p->elem_bytes = elem_bytes;
+    p->ordered_only = ordered_only;
     int rc = plan_build(ctx, p, row_ptr, st);
     if (rc) { cme213_csr_plan_destroy(p); return rc; }
     auto &e = ctx->csr_cache[ctx->csr_cache_next++ % cme213_ctx::CSR_CACHE];
@@ -495,11 +625,33 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
     if (rows <= 0) return CME213_OK;
     int kind = kernel & 0xFF;
     const int lanes = (kernel >> 8) & 0xFF;
+    if (kind == CME213_CSR_STREAM_PIPE) {
+        if constexpr (MODE == MODE_CSR) {
+            if (a.order || !(aligned16(a.col) && aligned16(a.val))) { kind = CME213_CSR_STREAM; }
+            else {
+                constexpr int THREADS = sizeof(T) == 8 ? 128 : 256, TILE = THREADS * 8;
+                const int64_t nblocks = div_up(rows, THREADS);
+                static int per_sm_dev[64] = {0};
+                int &per_sm = per_sm_dev[ctx->device & 63];
+                if (per_sm == 0) {
+                    CME213_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, csr_stream_pipe_kernel<T, THREADS, TILE>, THREADS, 0));
+                    if (per_sm < 1) per_sm = 1;
+                }
+                int64_t grid = (int64_t)per_sm * ctx->sm_count;
+                if (grid > nblocks) grid = nblocks;
+                csr_stream_pipe_kernel<T, THREADS, TILE><<<(unsigned)grid, THREADS, 0, st>>>(a, row_begin, row_end, nblocks);
+                CME213_LAUNCHED(ctx, "csr_stream_pipe_kernel");
+                return CME213_OK;
+            }
+        } else {
+            kind = CME213_CSR_STREAM;
+        }
+    }
     const bool padded = kind == CME213_CSR_STREAM_PADDED;
     const bool keep = kind == CME213_CSR_STREAM_KEEP;
     if (padded || keep) kind = CME213_CSR_STREAM;
     const bool vec_ok = aligned16(a.col) && (MODE != MODE_CSR || aligned16(a.val));
-    if (kind == CME213_CSR_AUTO) kind = CME213_CSR_STREAM;   // (CSR products resolve AUTO through a plan before they get here)
+    if (kind == CME213_CSR_AUTO || kind == CME213_CSR_AUTO_ORDERED) kind = CME213_CSR_STREAM;   // (CSR products resolve AUTO through a plan before they get here)
     if (kind == CME213_CSR_STREAM && !vec_ok) kind = CME213_CSR_SCALAR;
     if (kind == CME213_CSR_VECTOR && MODE != MODE_CSR) kind = CME213_CSR_STREAM;
     if (kind == CME213_CSR_SCALAR) {
@@ -540,7 +692,8 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
 #define CME213_TRY_CSR(TH, TL) \
                 if (T_ == TH && L_ == TL) { \
                     const int64_t nb = div_up(rows, TH); \
-                    if (K_) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, true><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); \
+                    if (K_ == 2) { if constexpr (MODE == MODE_CSR) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, 2><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); } \
+                    else if (K_) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, 1><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); \
                     else csr_stream_lean_kernel<T, MODE, TH, TL, false><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); \
                     CME213_LAUNCHED(ctx, "csr_stream_lean_kernel(cfg)"); \
                     return CME213_OK; \
@@ -553,7 +706,7 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
 #endif
             const int64_t blocks = div_up(rows, THREADS);
             if (padded) csr_stream_lean_kernel<T, MODE, THREADS, TILE, true><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end, NoSync());
-            else if (keep) csr_stream_lean_kernel<T, MODE, THREADS, TILE, false, false, true><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end, NoSync());
+            else if (keep) csr_stream_lean_kernel<T, MODE, THREADS, TILE, false, false, 1><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end, NoSync());
             else csr_stream_lean_kernel<T, MODE, THREADS, TILE, false><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end, NoSync());
         }
         CME213_LAUNCHED(ctx, "csr_stream_kernel");
@@ -599,12 +752,12 @@ int spmv_csr_impl(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, const int
     Args<T> a{d_row_ptr, d_col, d_val, d_x, nullptr, d_y, nullptr, T(0), d_order, push.peer_lo, push.peer_hi, push.lo_end, push.hi_begin};
     if (d_order && !(aligned16(d_col) && aligned16(d_val))) { set_error("spmv_csr ordered: col/val must be 16-byte aligned"); return CME213_ERR_INVALID; }
     if (d_order && (num_blocks < 0 || num_blocks > div_up(row_end - row_begin, 256))) { set_error("spmv_csr ordered: bad num_blocks"); return CME213_ERR_INVALID; }
-    if (!d_order && (kernel & 0xFF) == CME213_CSR_AUTO) {
+    if (!d_order && ((kernel & 0xFF) == CME213_CSR_AUTO || (kernel & 0xFF) == CME213_CSR_AUTO_ORDERED)) {
         // AUTO = the dispatcher: the plan of this (row_ptr, row range) is built on the first call (one synchronisation)
         // and kept in the context.  The matrix is taken to be about square for the x-residency rule (no column count here;
         // cme213_csr_plan_create takes one).
         cme213_csr_plan *plan = nullptr;
-        int rc = plan_for(ctx, d_row_ptr, row_begin, row_end, row_end, (int)sizeof(T), (cudaStream_t)stream, &plan);
+        int rc = plan_for(ctx, d_row_ptr, row_begin, row_end, row_end, (int)sizeof(T), (kernel & 0xFF) == CME213_CSR_AUTO_ORDERED, (cudaStream_t)stream, &plan);
         if (rc) return rc;
         return run_plan<T>(ctx, plan, a, (cudaStream_t)stream);
     }
@@ -696,6 +849,8 @@ CME213_API int cme213_csr_plan_create(cme213_ctx *ctx, int64_t row_begin, int64_
     CME213_CHECK_CTX(ctx);
     if (!out) { set_error("csr_plan_create: null out pointer"); return CME213_ERR_INVALID; }
     *out = nullptr;
+    const bool ordered_only = (elem_bytes & CME213_PLAN_ORDERED) != 0;
+    elem_bytes &= ~CME213_PLAN_ORDERED;
     if (row_begin < 0 || row_end < row_begin || num_cols < 0 || (elem_bytes != 4 && elem_bytes != 8) || (row_end > row_begin && !d_row_ptr)) {
         set_error("csr_plan_create: bad arguments");
         return CME213_ERR_INVALID;
@@ -703,6 +858,7 @@ CME213_API int cme213_csr_plan_create(cme213_ctx *ctx, int64_t row_begin, int64_
     DeviceGuard g(ctx->device);
     cme213_csr_plan *p = new cme213_csr_plan();
     p->device = ctx->device; p->row_begin = row_begin; p->row_end = row_end; p->num_cols = num_cols; p->elem_bytes = elem_bytes;
+    p->ordered_only = ordered_only;
     if (row_end > row_begin) {
         int rc = plan_build(ctx, p, d_row_ptr, (cudaStream_t)stream);
         if (rc) { cme213_csr_plan_destroy(p); return rc; }
@@ -811,7 +967,7 @@ static int spmv_csr_acc(cme213_ctx *ctx, int64_t rows_local, const int32_t *d_ro
     constexpr int THREADS = sizeof(T) == 8 ? 128 : 256, TILE = THREADS * 8;
     const int64_t blocks = div_up(rows_local, THREADS);
     if (blocks > 0x7FFFFFFFLL) { set_error("spmv_csr acc: too many rows"); return CME213_ERR_UNSUPPORTED; }
-    if (keep) csr_stream_lean_kernel<T, MODE_CSR_ACC, THREADS, TILE, false, false, true><<<(unsigned)blocks, THREADS, 0, st>>>(a, 0, rows_local, NoSync());
+    if (keep) csr_stream_lean_kernel<T, MODE_CSR_ACC, THREADS, TILE, false, false, 1><<<(unsigned)blocks, THREADS, 0, st>>>(a, 0, rows_local, NoSync());
     else csr_stream_lean_kernel<T, MODE_CSR_ACC, THREADS, TILE, false><<<(unsigned)blocks, THREADS, 0, st>>>(a, 0, rows_local, NoSync());
     CME213_LAUNCHED(ctx, "csr_stream_lean_kernel<acc>");
     return CME213_OK;

@@ -460,6 +460,36 @@ def make_fp(ctx, torch, args):
                 keep=(a, a0, k, x, bits))
 
 
+def make_fp_iterate(ctx, torch, args):
+    """C2c as the final project runs it: N = 10 iterations a <- b on the same x.  x[k] is gathered once (inside the timed
+    step) and the ten iterations stream a and xx through the bulk pipeline; one bench step = the gather + 10 iterations."""
+    n, q, N = 1 << 28, 1 << 20, 10
+    a = torch.empty(n, dtype=torch.float32, device="cuda")
+    ctx.call("cme213_fill_uniform_f32", a, n, 4)
+    a0 = a.clone()
+    k = i32(n, torch)
+    ctx.call("cme213_fill_hash_u32", k, n, 6, q)
+    x = torch.empty(q, dtype=torch.float32, device="cuda")
+    ctx.call("cme213_fill_uniform_f32", x, q, 7)
+    xx = torch.empty_like(a)
+    bits = i32((n + 31) // 32, torch)
+    ctx.call("cme213_fill_random_flags", bits, n, 5, (1 << 32) // 64)
+
+    def step():
+        st = torch.cuda.current_stream()
+        ctx.call("cme213_gather_f32", x, k, xx, n, stream=st)
+        ctx.call("cme213_mul_segscan_f32", a0, xx, bits, a, n, stream=st)       # first iteration reads the pristine a
+        for _ in range(N - 1):
+            ctx.call("cme213_mul_segscan_f32", a, xx, bits, a, n, stream=st)
+
+    per_iter = 12 * n + n // 8
+    return dict(step=step, alg_bytes=N * per_iter + 8 * n + 4 * q, flops=2 * n * N, kernel="scan_bulk_blocked_kernel<mul>", launches_per_step=N + 1,
+                meta={"workload": "C2c iterated: final-project loop, N=10 iterations on n=2^28, q=2^20: x[k] gathered once, then a*xx + segscan streamed", "n": n,
+                      "iterations_per_step": N, "l2": "3.2 GB per iteration >> L2",
+                      "note": "ms is for the gather + 10 iterations; the fused single step (gather every iteration) is the C2c line above"},
+                keep=(a, a0, k, x, xx, bits))
+
+
 def make_transpose(ctx, torch, args, bits):
     n = 16384
     dt = torch.float32 if bits == 32 else torch.float64
@@ -610,6 +640,8 @@ def build_workload(name, ctx, torch, args, rank=0, world=1, dist=None):
         return make_stencil(ctx, torch, args)
     if name == "fp":
         return make_fp(ctx, torch, args)
+    if name == "fp_iterate":
+        return make_fp_iterate(ctx, torch, args)
     if name == "transpose32":
         return make_transpose(ctx, torch, args, 32)
     if name == "transpose64":
@@ -1132,7 +1164,7 @@ def main():
         others = []
         del wl
         torch.cuda.empty_cache()
-        names = ["scan", "segscan", "radixsort", "dia", "stencil", "fp", "transpose32", "transpose64", "c1", "ell", "hyb", "hyb_coo", "csr_powerlaw",
+        names = ["scan", "segscan", "radixsort", "dia", "stencil", "fp", "fp_iterate", "transpose32", "transpose64", "c1", "ell", "hyb", "hyb_coo", "csr_powerlaw",
                  "ell_window", "hyb_window", "hyb_coo_window", "csr_window", "ell_regular_window", "csr_regular_window", "pagerank",
                  "gather_4mb", "gather_64mb", "gather_1gb"]
         for name in names:

@@ -48,6 +48,11 @@ extern "C" {
 #define CME213_CSR_STREAM_PADDED 4 /* same, shared-memory products padded against bank conflicts: for matrices whose rows all have 8, 16, 32 ... entries.
                                       AUTO picks between 3 and 4 from the mean row length (one small device read per new matrix). */
 
+#define CME213_CSR_STREAM_PIPE 7 /* CSR_STREAM as a persistent, software-pipelined kernel (three row blocks in flight per CTA): for matrices of a
+                                    few waves, where the plain kernel has nothing to hide its three dependent round trips behind */
+#define CME213_CSR_AUTO_ORDERED 8 /* the dispatcher restricted to kernels that keep the CPU loop's summation order (scalar, stream, stream-padded):
+                                     bit-identical to the CPU loop on every matrix, at the price of long rows being summed by one thread */
+#define CME213_PLAN_ORDERED 0x100  /* OR into cme213_csr_plan_create's elem_bytes for the same restriction */
 #define CME213_CSR_BINNED 6 /* plans only: 256-row blocks split into a short list (stream kernel) and a long list (vector kernel) */
 
 typedef struct cme213_ctx cme213_ctx;
@@ -143,6 +148,17 @@ int cme213_mul_gather_segscan_f32(cme213_ctx *ctx, const float *d_a, const int32
 int cme213_mul_gather_segscan_f64(cme213_ctx *ctx, const double *d_a, const int32_t *d_k, const double *d_x,
                                   const uint32_t *d_flag_bits, double *d_b, int64_t n, void *stream);
 
+/* The same step with the gather hoisted out of the iteration: xx[i] = x[k[i]] once (cme213_gather_*), then
+ * b = inclusive segmented sum of a[i]*xx[i] per iteration -- pure streaming, no random access.  The rounded product and
+ * the segmented sum are those of the fused step; only the tiling of the scan differs (same tolerance).  d_b == d_a allowed.
+ * reference: hw/hw_final/programming/fp.cu:124-125 (xx = x[k] flattened once), :139-149 / :174-180 (multiply, scan). */
+int cme213_gather_f32(cme213_ctx *ctx, const float *d_x, const int32_t *d_k, float *d_xx, int64_t n, void *stream);
+int cme213_gather_f64(cme213_ctx *ctx, const double *d_x, const int32_t *d_k, double *d_xx, int64_t n, void *stream);
+int cme213_mul_segscan_f32(cme213_ctx *ctx, const float *d_a, const float *d_xx, const uint32_t *d_flag_bits, float *d_b,
+                           int64_t n, void *stream);
+int cme213_mul_segscan_f64(cme213_ctx *ctx, const double *d_a, const double *d_xx, const uint32_t *d_flag_bits, double *d_b,
+                           int64_t n, void *stream);
+
 /* ---- CSR SpMV ---------------------------------------------------------- */
 /* y[r] = sum_j val[j] * x[col[j]], j in [row_ptr[r], row_ptr[r+1]), for rows r in [row_begin, row_end).
  * row_ptr, y are indexed by r itself (not r - row_begin) so a caller can split one matrix into
@@ -159,11 +175,17 @@ int cme213_spmv_csr_f64(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, con
 /* The dispatcher as an object.  CME213_CSR_AUTO in the calls above builds (first call on a matrix: one small kernel and
  * ONE synchronisation) and caches such a plan per (row_ptr, row range); a caller that must never synchronise -- a timed
  * loop, a stream capture -- creates the plan during set-up and multiplies through it.  The plan reads the row-length
- * histogram and picks: stream (short / irregular rows), stream-padded (all rows 8, 16, 32 ... long), stream-keep
- * (x between L1 and L2 size), vector with 32 lanes (long rows: mean >= 48), or BINNED for skewed matrices (>= 20 % of
- * the nonzeros in rows >= 96 long): the 256-row blocks are split by stream compaction into a short list for the stream
- * kernel and a long list for the vector kernel, two launches.  stream / scalar / padded / keep keep the CPU loop's
- * summation order (bit-identical); vector and the long blocks of BINNED sum in another order (reduction-order bound).
+ * histogram and picks (thresholds measured on B200, profiles/r02_csr_kernel_sweep.csv):
+ *   scalar         mean row length <= 2.5
+ *   stream-padded  every row 8, 16, 24 ... 128 entries long
+ *   vector         mean >= 96 (16 lanes below a mean of 128, 32 from there on)
+ *   BINNED         skewed matrices whose long rows sit together: 256-row blocks with >= 32 entries per row holding >= 30 % of
+ *                  the nonzeros go to the vector kernel, the others to the stream kernel (lists built by mark +
+ *                  exclusive scan + compaction; two launches)
+ *   stream         everything else
+ * scalar / stream / stream-padded keep the CPU loop's summation order (bit-identical to it); vector and the long blocks
+ * of BINNED sum in another order (reduction-order bound gamma_k * sum|a_ij x_j|).  CME213_CSR_AUTO_ORDERED / CME213_PLAN_ORDERED
+ * restrict the choice to the order-preserving kernels.
  * reference: slides/Lecture22.pdf slides 20, 21, 25; refs/Bell Tech Report 2008.pdf Figs. 20, 22 and section 5;
  * hw/hw_final/programming/paper/Final_Report_DongBang_Tsai.tex:228 (warp-per-segment regresses on short segments). */
 int cme213_csr_plan_create(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, int64_t num_cols, const int32_t *d_row_ptr,

@@ -43,7 +43,7 @@ def test_coo_to_csr_matches_numpy(ctx, dtype, rows, cols, nnz):
     if nnz:                            # and the CSR arrays feed the SpMV: same bits as the oracle's CSR loop
         x = rng.uniform(-1, 1, cols).astype(dtype)
         d_y = dev_empty(rows, dtype)
-        ctx.call("cme213_spmv_csr_" + sfx, 0, rows, d_ptr, d_col, d_val, dev(x), d_y, 0)
+        ctx.call("cme213_spmv_csr_" + sfx, 0, rows, d_ptr, d_col, d_val, dev(x), d_y, 8)   # CME213_CSR_AUTO_ORDERED: CPU order whatever the row lengths
         assert np.array_equal(host(d_y), oracle.csr_spmv(ptr, col, val, x))
 
 

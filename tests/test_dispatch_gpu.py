@@ -61,8 +61,10 @@ def test_plan_picks_by_row_length_and_every_choice_matches_the_cpu_loop(ctx, cme
     cases.append(("laplace", ptr, col, val, 200 * 150, (STREAM,)))
     cases.append(("regular16",) + regular_csr(20000, 30000, 16, 1, dtype) + (30000, (PADDED,)))
     cases.append(("regular7",) + regular_csr(20000, 30000, 7, 2, dtype) + (30000, (STREAM,)))
-    cases.append(("long64",) + regular_csr(6000, 50000, 64, 3, dtype) + (50000, (VECTOR,)))
+    cases.append(("regular64",) + regular_csr(6000, 50000, 64, 3, dtype) + (50000, (PADDED,)))
+    cases.append(("short2",) + regular_csr(50000, 50000, 2, 6, dtype) + (50000, (SCALAR,)))
     cases.append(("long300",) + regular_csr(1500, 50000, 300, 4, dtype) + (50000, (VECTOR,)))
+    cases.append(("long100",) + regular_csr(3000, 50000, 100, 5, dtype) + (50000, (VECTOR,)))
     for name, ptr, col, val, cols, expect in cases:
         x = np.random.default_rng(9).uniform(-1, 1, cols).astype(dtype)
         plan, d_ptr = make_plan(ctx, cme, ptr, cols, eb)
@@ -81,16 +83,52 @@ def test_plan_picks_by_row_length_and_every_choice_matches_the_cpu_loop(ctx, cme
         lib.cme213_csr_plan_destroy(plan)
 
 
-def test_plan_large_x_takes_the_evict_last_variant(ctx, cme):
-    # x of 3 Mi floats = 12 MB: beyond L1, inside L2
+def test_ordered_plans_stay_bit_identical_on_long_rows(ctx, cme):
+    """CME213_PLAN_ORDERED / CME213_CSR_AUTO_ORDERED: the dispatcher may only pick kernels that keep the CPU loop's order."""
     lib = cme.load()
-    rows = cols = 3 << 20
-    ptr, col, val = regular_csr(rows, cols, 3, 5)
-    plan, d_ptr = make_plan(ctx, cme, ptr, cols, 4)
-    assert lib.cme213_csr_plan_kernel(plan) == KEEP, lib.cme213_csr_plan_describe(plan)
-    x = np.random.default_rng(1).uniform(-1, 1, cols).astype(np.float32)
-    assert np.array_equal(run_plan(ctx, cme, plan, d_ptr, col, val, x), oracle.csr_spmv(ptr, col, val, x))
+    ptr, col, val = regular_csr(1500, 50000, 300, 4)
+    x = np.random.default_rng(1).uniform(-1, 1, 50000).astype(np.float32)
+    want = oracle.csr_spmv(ptr, col, val, x)
+    plan, d_ptr = make_plan(ctx, cme, ptr, 50000, 4 | cme.capi.PLAN_ORDERED)
+    assert lib.cme213_csr_plan_kernel(plan) & 0xFF in (SCALAR, STREAM, PADDED), lib.cme213_csr_plan_describe(plan)
+    assert np.array_equal(run_plan(ctx, cme, plan, d_ptr, col, val, x), want)
     lib.cme213_csr_plan_destroy(plan)
+    d_y = dev(np.zeros(1500, np.float32))
+    ctx.call("cme213_spmv_csr_f32", 0, 1500, d_ptr, dev(col), dev(val), dev(x), d_y, cme.capi.CSR_AUTO_ORDERED)
+    assert np.array_equal(host(d_y), want)
+    for kernel in (KEEP, 7):                     # the explicit evict-last and software-pipelined variants: same bits
+        d_y = dev(np.zeros(1500, np.float32))
+        ctx.call("cme213_spmv_csr_f32", 0, 1500, d_ptr, dev(col), dev(val), dev(x), d_y, kernel)
+        assert np.array_equal(host(d_y), want), kernel
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_pipelined_stream_kernel_bit_exact(ctx, dtype):
+    """CME213_CSR_STREAM_PIPE: persistent CTAs, three row blocks in flight; blocks with more nonzeros than a tile take
+    the multi-pass path inside the same kernel."""
+    sfx = "f64" if dtype == np.float64 else "f32"
+    rng = np.random.default_rng(12)
+    mats = [g.laplace3d(40, 30, 20, dtype=dtype), g.laplace2d(300, 200, dtype), g.random_csr(70000, 50000, 9.0, seed=3, dtype=dtype),
+            g.random_csr(257, 300, 0.3, seed=4, dtype=dtype), g.random_csr(3000, 20000, 40.0, seed=5, dtype=dtype)]
+    length = np.array([0, 5000, 3, 0, 2048, 2049, 1, 7000, 0, 0, 2, 4097] + [3] * 600 + [0, 6000])
+    ptr = np.concatenate([[0], np.cumsum(length)]).astype(np.int32)
+    col = np.concatenate([np.sort(rng.choice(9000, l, replace=False)) for l in length]).astype(np.int32)
+    mats.append((ptr, col, rng.uniform(-1, 1, ptr[-1]).astype(dtype)))
+    for ptr, col, val in mats:
+        cols = int(col.max()) + 1 if len(col) else 1
+        x = rng.uniform(-1, 1, cols).astype(dtype)
+        rows = len(ptr) - 1
+        d_y = dev(np.full(rows, -7.0, dtype))
+        ctx.call("cme213_spmv_csr_" + sfx, 0, rows, dev(ptr), dev(col if len(col) else np.zeros(4, np.int32)),
+                 dev(val if len(val) else np.zeros(4, dtype)), dev(x), d_y, 7)
+        assert np.array_equal(host(d_y), oracle.csr_spmv(ptr, col, val, x))
+        # a row range in the middle (as a shard would call it): untouched outside
+        if rows > 600:
+            d_y = dev(np.full(rows, -7.0, dtype))
+            ctx.call("cme213_spmv_csr_" + sfx, 300, rows - 200, dev(ptr), dev(col), dev(val), dev(x), d_y, 7)
+            got = host(d_y)
+            assert np.array_equal(got[300:rows - 200], oracle.csr_spmv(ptr, col, val, x)[300:rows - 200])
+            assert (got[:300] == -7).all() and (got[rows - 200:] == -7).all()
 
 
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])

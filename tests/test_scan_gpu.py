@@ -288,3 +288,51 @@ def test_blocked_radix_pass_sorts(ctx):
         assert np.array_equal(out, oracle.radix_pass_u32(k, start, 8))
         k = out
     assert np.array_equal(k, np.sort(keys))
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("n", [1, 777, 70001, 3 * (1 << 20) + 13])
+def test_hoisted_gather_then_streamed_step_matches_the_fused_step(ctx, dtype, n):
+    """cme213_gather_* once + cme213_mul_segscan_* per iteration = the final project's loop with xx = x[k] flattened once
+    (fp.cu:124-125).  Same rounded products, same segments: equal to the double-precision recurrence within the scan's
+    tolerance, and the gathered vector is exact."""
+    sfx = "f64" if dtype == np.float64 else "f32"
+    q = 5000
+    a, s, k, x = g.fp_inputs(n, max(2, n // 50 + 2), q, seed=n % 97, dtype=dtype)
+    flags = g.pack_flags(g.offsets_to_flags(s, n))
+    d_a, d_k, d_x, d_f = dev(a), dev(k), dev(x), dev(flags)
+    d_xx = dev_empty(n, dtype)
+    ctx.call("cme213_gather_" + sfx, d_x, d_k, d_xx, n)
+    assert np.array_equal(host(d_xx), x[k])
+    iters = 3
+    for _ in range(iters):
+        ctx.call("cme213_mul_segscan_" + sfx, d_a, d_xx, d_f, d_a, n)       # in place: b becomes the next a
+    want = oracle.sparse_mv_scan(a.astype(np.float64), s, k, x.astype(np.float64), iters)
+    got = host(d_a).astype(np.float64)
+    norms = oracle.error_norms(want, got)
+    assert norms[2] < (1e-5 if dtype == np.float32 else 1e-13), norms
+    # against the fused kernel on the same inputs: both are fp scans of the same rounded products
+    d_b = dev(a)
+    for _ in range(iters):
+        ctx.call("cme213_mul_gather_segscan_" + sfx, d_b, d_k, d_x, d_f, d_b, n)
+    assert oracle.error_norms(host(d_b).astype(np.float64), got)[2] < (1e-5 if dtype == np.float32 else 1e-13)
+
+
+def test_streamed_step_exact_on_integer_data_full_size(ctx):
+    """n = 2^27: small-integer data make every order of summation exact, so the streamed step must equal the fused one bit for bit."""
+    import torch
+    n, q = 1 << 27, 1 << 16
+    k = dev_empty(n, np.int32)
+    ctx.call("cme213_fill_hash_u32", k, n, 6, q)
+    a = (torch.randint(-2, 3, (n,), device="cuda", dtype=torch.int32)).to(torch.float32)
+    x = (torch.randint(-1, 2, (q,), device="cuda", dtype=torch.int32)).to(torch.float32)
+    bits = dev_empty((n + 31) // 32, np.uint32)
+    ctx.call("cme213_fill_random_flags", bits, n, 5, (1 << 32) // 16)
+    xx = torch.empty_like(a)
+    ctx.call("cme213_gather_f32", x, k, xx, n)
+    assert torch.equal(xx, x[k.to(torch.int64)])
+    b1, b2 = torch.empty_like(a), torch.empty_like(a)
+    ctx.call("cme213_mul_segscan_f32", a, xx, bits, b1, n)
+    ctx.call("cme213_mul_gather_segscan_f32", a, k, x, bits, b2, n)
+    torch.cuda.synchronize()
+    assert torch.equal(b1, b2)
