@@ -420,8 +420,11 @@ CME213_API int cme213_shard_step(cme213_shard *s, int src, void *stream) {
         memset(&k, 0, sizeof(k));
         const bool has_lo = s->rank > 0, has_hi = s->rank + 1 < s->world;
         // a side's boundary = the rows the neighbour needs from me or that read the neighbour's rows, whichever reaches further
-        const int64_t side_lo = has_lo ? (s->push_lo > s->need_lo ? s->push_lo : s->need_lo) : 0;
-        const int64_t side_hi = has_hi ? (s->push_hi > s->need_hi ? s->push_hi : s->need_hi) : 0;
+        // (need_* counts rows of the NEIGHBOUR and may exceed this rank's own row count: then every row here is a boundary row)
+        int64_t side_lo = has_lo ? (s->push_lo > s->need_lo ? s->push_lo : s->need_lo) : 0;
+        int64_t side_hi = has_hi ? (s->push_hi > s->need_hi ? s->push_hi : s->need_hi) : 0;
+        if (side_lo > s->nloc) side_lo = s->nloc;
+        if (side_hi > s->nloc) side_hi = s->nloc;
         k.peer_lo = has_lo && side_lo > 0 ? s->px[dst][s->rank - 1] + s->lo : nullptr;
         k.peer_hi = has_hi && side_hi > 0 ? s->px[dst][s->rank + 1] + s->lo : nullptr;
         k.push_lo_end = s->push_lo; k.push_hi_begin = s->nloc - s->push_hi;
