@@ -12,7 +12,8 @@ LIB_PATH = os.path.join(HERE, "libcme213_b200.so")
 OK = 0
 ERR_INVALID, ERR_CUDA, ERR_ALLOC, ERR_UNSUPPORTED, ERR_TIMEOUT = -1, -2, -3, -4, -5
 SHARD_AUTO, SHARD_HALO, SHARD_GATHER, SHARD_GATHER_SPLIT = 0, 1, 2, 3
-CSR_AUTO, CSR_SCALAR, CSR_VECTOR, CSR_STREAM, CSR_STREAM_PADDED, CSR_STREAM_KEEP, CSR_BINNED, CSR_STREAM_PIPE, CSR_AUTO_ORDERED, CSR_STREAM_BALANCED = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9
+CSR_AUTO, CSR_SCALAR, CSR_VECTOR, CSR_STREAM, CSR_STREAM_PADDED, CSR_STREAM_KEEP, CSR_BINNED = 0, 1, 2, 3, 4, 5, 6
+CSR_AUTO_ORDERED, CSR_STREAM_BALANCED = 8, 9
 PLAN_ORDERED = 0x100
 FORMAT_CSR, FORMAT_ELL, FORMAT_HYB = 0, 1, 2
 
@@ -62,6 +63,7 @@ PROTOTYPES = {
     "cme213_spmv_csr_f64": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _i, _p]),
     "cme213_csr_plan_create": (_i, [_p, _i64, _i64, _i64, _p, _i, _p, C.POINTER(_p)]),
     "cme213_csr_plan_destroy": (_i, [_p]),
+    "cme213_ctx_clear_plans": (_i, [_p]),
     "cme213_csr_plan_kernel": (_i, [_p]),
     "cme213_csr_plan_describe": (C.c_char_p, [_p]),
     "cme213_spmv_csr_plan_f32": (_i, [_p, _p, _p, _p, _p, _p, _p, _p]),

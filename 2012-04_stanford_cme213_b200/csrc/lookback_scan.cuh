@@ -1118,7 +1118,10 @@ template <class P>
 int launch_with_scratch(cme213_ctx *ctx, const P &p, int64_t n, bool vec_ok, cudaStream_t st, const char *name,
                         void *scratch_mem, size_t scratch_avail) {
     if constexpr (P::BULK) {
-        if (vec_ok && n >= (int64_t)1 << 20)
+        // the persistent pipeline pays off from about a million items per stream; with two value streams per tile (a and xx of
+        // the hoisted final-project step) its tiles are smaller and the one-CTA-per-tile kernel stays ahead up to ~16 M items
+        // (the 15 benchmark shapes of the final project, n = 1-12 M: profiles/r02_reference_gpu_programs.md)
+        if (vec_ok && n >= (Cfg<P>::TWO_VALUE_STREAMS ? (int64_t)1 << 24 : (int64_t)1 << 20))
             return launch_bulk<P, Cfg<P>::B_THREADS, Cfg<P>::B_VECS, Cfg<P>::B_STAGES, Cfg<P>::DPL, true, Cfg<P>::B_DEFER>(ctx, p, n, st, name, scratch_mem, scratch_avail);
     }
     return launch_direct<P, Cfg<P>::DIRECT_THREADS, Cfg<P>::DIRECT_VECS, Cfg<P>::DIRECT_MIN_BLOCKS>(ctx, p, n, vec_ok, st, name, scratch_mem);

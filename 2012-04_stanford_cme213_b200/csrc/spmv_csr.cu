@@ -284,86 +284,6 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename s
     }
 }
 
-// Persistent, software-pipelined form of the lean kernel.  The lean kernel's CTA goes through three dependent round trips
-// to memory (row pointers -> col/val -> x) before it can sum, and hides them only by having many CTAs resident; on a
-// matrix of a few waves (config C1: 4096 CTAs, 3.5 waves) there is nothing to hide them behind.  Here a CTA walks over
-// row blocks b, b + grid, b + 2 grid, ... and keeps three blocks in flight: the row pointers of block i+2, the col/val
-// vectors of block i+1 (in registers) and the gathers / sums of block i, with two product buffers so that one barrier per
-// block is enough.  Same products, same order: bit-identical to the CPU loop.  Blocks with more than TILE nonzeros fall
-// back to the multi-pass loop inside the same kernel.
-template <typename T, int THREADS, int TILE>
-__global__ void __launch_bounds__(THREADS)
-csr_stream_pipe_kernel(Args<T> a, int64_t row_begin, int64_t row_end, int64_t nblocks) {
-    constexpr int V = TILE / (4 * THREADS);
-    static_assert(TILE % (4 * THREADS) == 0 && V >= 1, "tile = whole 4-wide vectors per thread");
-    __shared__ __align__(16) T prod[2][TILE];
-    const int tid = threadIdx.x;
-    const int64_t G = gridDim.x;
-    struct Ptr { int rs, re, b0, b1; };
-    struct Vec { int4 c[V]; V4<T> w[V]; };
-    auto load_ptr = [&](int64_t blk) {
-        Ptr p{0, 0, 0, 0};
-        if (blk < nblocks) {
-            const int64_t r0 = row_begin + blk * THREADS, r = r0 + tid, rl = r0 + THREADS < row_end ? r0 + THREADS : row_end;
-            if (r < row_end) { p.rs = a.row_ptr[r]; p.re = a.row_ptr[r + 1]; }
-            p.b0 = __ldg(a.row_ptr + r0);
-            p.b1 = __ldg(a.row_ptr + rl);
-        }
-        return p;
-    };
-    auto load_vec = [&](const Ptr &p, Vec &v) {   // the first TILE entries of the block, whole vectors only
-        const int base = p.b0 & ~3;
-#pragma unroll
-        for (int k = 0; k < V; k++) {
-            const int j = base + (k * THREADS + tid) * 4;
-            if (j + 4 <= p.b1) {
-                v.c[k] = ld_stream(reinterpret_cast<const int4 *>(a.col + j));
-                v.w[k] = V4<T>::load(a.val + j);
-            }
-        }
-    };
-    int64_t blk = blockIdx.x;
-    Ptr p0 = load_ptr(blk), p1 = load_ptr(blk + G);
-    Vec v0, v1;
-    load_vec(p0, v0);
-    for (int it = 0; blk < nblocks; blk += G, it++) {
-        const Ptr p2 = load_ptr(blk + 2 * G);          // block i+2: row pointers
-        load_vec(p1, v1);                              // block i+1: col / val (p1 arrived during the previous iteration)
-        T *pr = prod[it & 1];
-        const int64_t r = row_begin + blk * THREADS + tid;
-        T sum = T(0);
-        bool first = true;
-        for (int base = p0.b0 & ~3; base < p0.b1; base += TILE, first = false) {
-            if (!first) __syncthreads();               // rare multi-pass block: the previous pass's products are being summed
-#pragma unroll
-            for (int k = 0; k < V; k++) {
-                const int o = (k * THREADS + tid) * 4;
-                const int j = base + o;
-                if (j + 4 <= p0.b1) {
-                    int4 c;
-                    V4<T> w;
-                    if (first) { c = v0.c[k]; w = v0.w[k]; }
-                    else { c = ld_stream(reinterpret_cast<const int4 *>(a.col + j)); w = V4<T>::load(a.val + j); }
-                    pr[o + 0] = mul_rn(w.v[0], __ldg(a.x + c.x));
-                    pr[o + 1] = mul_rn(w.v[1], __ldg(a.x + c.y));
-                    pr[o + 2] = mul_rn(w.v[2], __ldg(a.x + c.z));
-                    pr[o + 3] = mul_rn(w.v[3], __ldg(a.x + c.w));
-                } else {
-#pragma unroll
-                    for (int t = 0; t < 4; t++)
-                        if (j + t < p0.b1) pr[o + t] = mul_rn(a.val[j + t], __ldg(a.x + a.col[j + t]));
-                }
-            }
-            __syncthreads();
-            const int lo = p0.rs > base ? p0.rs : base;
-            const int hi = p0.re < base + TILE ? p0.re : base + TILE;
-            for (int j = lo; j < hi; j++) sum = add_rn(sum, pr[j - base]);
-        }
-        if (r < row_end) st_stream(a.y + r, sum);
-        p0 = p1; p1 = p2; v0 = v1;
-    }
-}
-
 // Load-balanced form of the stream kernel for skewed row lengths.  The stream kernel sums each row with one thread; on a
 // power-law matrix a 256-row CTA then waits for its one 256-entry row while 250 threads that had 5 entries idle.  Here the
 // products of a tile are reduced by an in-place SEGMENTED SCAN over shared memory (heads = row starts): every thread scans 8
@@ -698,7 +618,7 @@ int plan_build(cme213_ctx *ctx, cme213_csr_plan *p, const int32_t *d_row_ptr, cu
     // skewed rows scattered all over the matrix (power-law graphs): the load-balanced stream kernel
     if ((p->kernel & 0xFF) == CME213_CSR_STREAM && !ordered_only && p->long_nnz_fraction >= PLAN_BALANCED_FRACTION)
         p->kernel = CME213_CSR_STREAM_BALANCED;
-    const char *names[] = {"auto", "scalar", "vector", "stream", "stream-padded", "stream-keep", "binned", "stream-pipe", "auto-ordered", "stream-balanced"};
+    const char *names[] = {"auto", "scalar", "vector", "stream", "stream-padded", "stream-keep", "binned", "(unused)", "auto-ordered", "stream-balanced"};
     const int kind = p->kernel & 0xFF;
     char lanes[24] = "";
     if (kind == CME213_CSR_VECTOR) snprintf(lanes, sizeof(lanes), " (%d lanes)", (p->kernel >> 8) & 0xFF);
@@ -743,28 +663,6 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
                 constexpr int THREADS = 256, TILE = 2048;
                 csr_stream_balanced_kernel<T, MODE, THREADS, TILE><<<(unsigned)div_up(rows, THREADS), THREADS, 0, st>>>(a, row_begin, row_end);
                 CME213_LAUNCHED(ctx, "csr_stream_balanced_kernel");
-                return CME213_OK;
-            }
-        } else {
-            kind = CME213_CSR_STREAM;
-        }
-    }
-    if (kind == CME213_CSR_STREAM_PIPE) {
-        if constexpr (MODE == MODE_CSR) {
-            if (a.order || !(aligned16(a.col) && aligned16(a.val))) { kind = CME213_CSR_STREAM; }
-            else {
-                constexpr int THREADS = sizeof(T) == 8 ? 128 : 256, TILE = THREADS * 8;
-                const int64_t nblocks = div_up(rows, THREADS);
-                static int per_sm_dev[64] = {0};
-                int &per_sm = per_sm_dev[ctx->device & 63];
-                if (per_sm == 0) {
-                    CME213_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, csr_stream_pipe_kernel<T, THREADS, TILE>, THREADS, 0));
-                    if (per_sm < 1) per_sm = 1;
-                }
-                int64_t grid = (int64_t)per_sm * ctx->sm_count;
-                if (grid > nblocks) grid = nblocks;
-                csr_stream_pipe_kernel<T, THREADS, TILE><<<(unsigned)grid, THREADS, 0, st>>>(a, row_begin, row_end, nblocks);
-                CME213_LAUNCHED(ctx, "csr_stream_pipe_kernel");
                 return CME213_OK;
             }
         } else {
@@ -988,6 +886,15 @@ CME213_API int cme213_csr_plan_create(cme213_ctx *ctx, int64_t row_begin, int64_
         if (rc) { cme213_csr_plan_destroy(p); return rc; }
     }
     *out = p;
+    return CME213_OK;
+}
+CME213_API int cme213_ctx_clear_plans(cme213_ctx *ctx) {
+    CME213_CHECK_CTX(ctx);
+    for (int i = 0; i < cme213_ctx::CSR_CACHE; i++) {
+        cme213_csr_plan_destroy(ctx->csr_cache[i].plan);
+        ctx->csr_cache[i].plan = nullptr;
+        ctx->csr_cache[i].row_ptr = nullptr;
+    }
     return CME213_OK;
 }
 CME213_API int cme213_csr_plan_destroy(cme213_csr_plan *p) {

@@ -48,8 +48,6 @@ extern "C" {
 #define CME213_CSR_STREAM_PADDED 4 /* same, shared-memory products padded against bank conflicts: for matrices whose rows all have 8, 16, 32 ... entries.
                                       AUTO picks between 3 and 4 from the mean row length (one small device read per new matrix). */
 
-#define CME213_CSR_STREAM_PIPE 7 /* CSR_STREAM as a persistent, software-pipelined kernel (three row blocks in flight per CTA): for matrices of a
-                                    few waves, where the plain kernel has nothing to hide its three dependent round trips behind */
 #define CME213_CSR_STREAM_BALANCED 9 /* CSR_STREAM with the per-row sums replaced by a segmented scan of the tile's products in shared memory:
                                         work independent of how the entries are split into rows (skewed / power-law row lengths);
                                         sums in scan order (reduction-order bound, not bit-identical) */
@@ -194,6 +192,10 @@ int cme213_spmv_csr_f64(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, con
 int cme213_csr_plan_create(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, int64_t num_cols, const int32_t *d_row_ptr,
                            int elem_bytes, void *stream, cme213_csr_plan **out);
 int cme213_csr_plan_destroy(cme213_csr_plan *plan);
+/* CME213_CSR_AUTO's cached plans are keyed by the ADDRESS of row_ptr (and the row range): if a matrix is freed and another
+ * of the same size lands at the same address, the old plan is applied to it.  Every kernel is correct on every matrix, so
+ * results stay right -- only the choice may no longer fit.  Call this when matrices come and go (or use explicit plans). */
+int cme213_ctx_clear_plans(cme213_ctx *ctx);
 int cme213_csr_plan_kernel(const cme213_csr_plan *plan);           /* CME213_CSR_* (| lanes << 8) */
 const char *cme213_csr_plan_describe(const cme213_csr_plan *plan); /* one line: choice and the statistics behind it */
 int cme213_spmv_csr_plan_f32(cme213_ctx *ctx, const cme213_csr_plan *plan, const int32_t *d_row_ptr, const int32_t *d_col,

@@ -77,6 +77,7 @@ def test_plan_picks_by_row_length_and_every_choice_matches_the_cpu_loop(ctx, cme
         else:
             assert np.array_equal(got, oracle.csr_spmv(ptr, col, val, x)), (name, text)
         # AUTO through the ordinary entry point takes the same decision (its own cached plan) and gives the same bits
+        ctx.lib.cme213_ctx_clear_plans(ctx.h)       # cached plans are keyed by address: an earlier test's matrix may have lived here
         d_y = dev(np.zeros(len(ptr) - 1, dtype))
         ctx.call("cme213_spmv_csr_" + ("f64" if eb == 8 else "f32"), 0, len(ptr) - 1, d_ptr, dev(col), dev(val), dev(x), d_y, 0)
         assert np.array_equal(host(d_y), got), name
@@ -96,39 +97,10 @@ def test_ordered_plans_stay_bit_identical_on_long_rows(ctx, cme):
     d_y = dev(np.zeros(1500, np.float32))
     ctx.call("cme213_spmv_csr_f32", 0, 1500, d_ptr, dev(col), dev(val), dev(x), d_y, cme.capi.CSR_AUTO_ORDERED)
     assert np.array_equal(host(d_y), want)
-    for kernel in (KEEP, 7):                     # the explicit evict-last and software-pipelined variants: same bits
+    for kernel in (KEEP,):                       # the explicit evict-last variant: same bits
         d_y = dev(np.zeros(1500, np.float32))
         ctx.call("cme213_spmv_csr_f32", 0, 1500, d_ptr, dev(col), dev(val), dev(x), d_y, kernel)
         assert np.array_equal(host(d_y), want), kernel
-
-
-@pytest.mark.parametrize("dtype", [np.float32, np.float64])
-def test_pipelined_stream_kernel_bit_exact(ctx, dtype):
-    """CME213_CSR_STREAM_PIPE: persistent CTAs, three row blocks in flight; blocks with more nonzeros than a tile take
-    the multi-pass path inside the same kernel."""
-    sfx = "f64" if dtype == np.float64 else "f32"
-    rng = np.random.default_rng(12)
-    mats = [g.laplace3d(40, 30, 20, dtype=dtype), g.laplace2d(300, 200, dtype), g.random_csr(70000, 50000, 9.0, seed=3, dtype=dtype),
-            g.random_csr(257, 300, 0.3, seed=4, dtype=dtype), g.random_csr(3000, 20000, 40.0, seed=5, dtype=dtype)]
-    length = np.array([0, 5000, 3, 0, 2048, 2049, 1, 7000, 0, 0, 2, 4097] + [3] * 600 + [0, 6000])
-    ptr = np.concatenate([[0], np.cumsum(length)]).astype(np.int32)
-    col = np.concatenate([np.sort(rng.choice(9000, l, replace=False)) for l in length]).astype(np.int32)
-    mats.append((ptr, col, rng.uniform(-1, 1, ptr[-1]).astype(dtype)))
-    for ptr, col, val in mats:
-        cols = int(col.max()) + 1 if len(col) else 1
-        x = rng.uniform(-1, 1, cols).astype(dtype)
-        rows = len(ptr) - 1
-        d_y = dev(np.full(rows, -7.0, dtype))
-        ctx.call("cme213_spmv_csr_" + sfx, 0, rows, dev(ptr), dev(col if len(col) else np.zeros(4, np.int32)),
-                 dev(val if len(val) else np.zeros(4, dtype)), dev(x), d_y, 7)
-        assert np.array_equal(host(d_y), oracle.csr_spmv(ptr, col, val, x))
-        # a row range in the middle (as a shard would call it): untouched outside
-        if rows > 600:
-            d_y = dev(np.full(rows, -7.0, dtype))
-            ctx.call("cme213_spmv_csr_" + sfx, 300, rows - 200, dev(ptr), dev(col), dev(val), dev(x), d_y, 7)
-            got = host(d_y)
-            assert np.array_equal(got[300:rows - 200], oracle.csr_spmv(ptr, col, val, x)[300:rows - 200])
-            assert (got[:300] == -7).all() and (got[rows - 200:] == -7).all()
 
 
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
