@@ -13,7 +13,7 @@ OK = 0
 ERR_INVALID, ERR_CUDA, ERR_ALLOC, ERR_UNSUPPORTED, ERR_TIMEOUT = -1, -2, -3, -4, -5
 SHARD_AUTO, SHARD_HALO, SHARD_GATHER, SHARD_GATHER_SPLIT = 0, 1, 2, 3
 CSR_AUTO, CSR_SCALAR, CSR_VECTOR, CSR_STREAM, CSR_STREAM_PADDED, CSR_STREAM_KEEP, CSR_BINNED = 0, 1, 2, 3, 4, 5, 6
-CSR_AUTO_ORDERED, CSR_STREAM_BALANCED = 8, 9
+CSR_AUTO_ORDERED = 8
 PLAN_ORDERED = 0x100
 FORMAT_CSR, FORMAT_ELL, FORMAT_HYB = 0, 1, 2
 
@@ -69,8 +69,8 @@ PROTOTYPES = {
     "cme213_spmv_csr_plan_f32": (_i, [_p, _p, _p, _p, _p, _p, _p, _p]),
     "cme213_spmv_csr_plan_f64": (_i, [_p, _p, _p, _p, _p, _p, _p, _p]),
     "cme213_spmv_pick_format": (_i, [_p, _i64, _p, _p, _p]),
-    "cme213_spmv_hyb_csrtail_f32": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _p, _p, _p, _p, _i, _p]),
-    "cme213_spmv_hyb_csrtail_f64": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _p, _p, _p, _p, _i, _p]),
+    "cme213_spmv_hyb_csrtail_f32": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "cme213_spmv_hyb_csrtail_f64": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _p, _p, _p, _p, _p]),
     "cme213_csr_tail_row_ptr": (_i, [_p, _i64, _p, _i, _p, _pi64, _p]),
     "cme213_spmv_csr_block_rows": (_i, []),
     "cme213_spmv_csr_f32_ordered": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _p, _i64, _p]),

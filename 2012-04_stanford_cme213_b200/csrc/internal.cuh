@@ -50,10 +50,6 @@ int cme213_internal_spmv_csr_f64_acc_keep(cme213_ctx *ctx, int64_t rows_local, c
                                           const double *d_val, const double *d_x, double *d_y, cudaStream_t st);
 int cme213_internal_spmv_csr_f32_acc_keep(cme213_ctx *ctx, int64_t rows_local, const int32_t *d_row_ptr, const int32_t *d_col,
                                           const float *d_val, const float *d_x, float *d_y, cudaStream_t st);
-int cme213_internal_spmv_csr_f32_acc_balanced(cme213_ctx *ctx, int64_t rows_local, const int32_t *d_row_ptr, const int32_t *d_col,
-                                              const float *d_val, const float *d_x, float *d_y, cudaStream_t st);
-int cme213_internal_spmv_csr_f64_acc_balanced(cme213_ctx *ctx, int64_t rows_local, const int32_t *d_row_ptr, const int32_t *d_col,
-                                              const double *d_val, const double *d_x, double *d_y, cudaStream_t st);
 // convert.cu: histogram of row lengths (4096 bins, the last collects everything longer) + the longest row; synchronises
 constexpr int CME213_HIST_BINS = 4096;
 int cme213_internal_row_length_hist(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr, unsigned long long *h_hist,

@@ -988,11 +988,10 @@ template <class P> struct Cfg {
     static constexpr int DPL = 5;                               // a wave holds at most 32*DPL = 160 tiles
     // blocked bulk kernel (dense-output policies): ~700 threads x 5 consecutive vectors = 55 KiB tiles, 4 ring slots,
     // finish deferred by 2 iterations (sweep in profiles/r01_notes.md; segmented scans also stage their flag words)
-    // Policies that stage two value streams (the hoisted final-project step: a and xx) get tiles of 3 vectors per thread
-    // and a 3-slot ring with the finish deferred by one iteration: 4 slots of 5 vectors would not fit in shared memory.
+    // Policies that stage two value streams (the hoisted final-project step: a and xx) get 512 threads x 3 vectors (49 KiB tiles:
+    // 4 slots of the 640 x 5 shape would not fit in shared memory); sweep of 6 shapes in profiles/r02_notes.md.
     static constexpr bool TWO_VALUE_STREAMS = P::BULK && P::NIN >= 3;
-    static constexpr int B_THREADS = P::SEG ? 640 : 704, B_VECS = TWO_VALUE_STREAMS ? 3 : 5, B_STAGES = TWO_VALUE_STREAMS ? 3 : 4,
-                         B_DEFER = TWO_VALUE_STREAMS ? 1 : 2;
+    static constexpr int B_THREADS = TWO_VALUE_STREAMS ? 512 : P::SEG ? 640 : 704, B_VECS = TWO_VALUE_STREAMS ? 3 : 5, B_STAGES = 4, B_DEFER = 2;
     static constexpr int DIRECT_THREADS = 256, DIRECT_VECS = 4; // one-tile-per-CTA kernel
     static constexpr int DIRECT_MIN_BLOCKS = 6;   // 40 registers per thread: the gather-heavy policies want occupancy more than registers (fused step 1.68 -> 1.41 ms)
 };

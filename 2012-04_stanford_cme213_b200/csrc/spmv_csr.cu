@@ -284,113 +284,6 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename s
     }
 }
 
-// Load-balanced form of the stream kernel for skewed row lengths.  The stream kernel sums each row with one thread; on a
-// power-law matrix a 256-row CTA then waits for its one 256-entry row while 250 threads that had 5 entries idle.  Here the
-// products of a tile are reduced by an in-place SEGMENTED SCAN over shared memory (heads = row starts): every thread scans 8
-// consecutive products, a warp scan and a scan of the warp totals carry the open segment across threads, and each row
-// picks its sum up at its last entry.  Work per tile no longer depends on how the entries are split into rows.  The
-// summation order is the scan's tree, not left to right: reduction-order bound instead of bit-identity.
-// reference: the segmented reduction of refs/Bell Tech Report 2008.pdf Fig. 24 and slides/Lecture21.pdf (segmented scan
-// with head flags), applied per tile instead of per COO array.
-template <typename T, int MODE, int THREADS, int TILE>
-__global__ void __launch_bounds__(THREADS)
-csr_stream_balanced_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
-    constexpr int E = TILE / THREADS;              // consecutive products per thread in the scan
-    constexpr int WARPS = THREADS / 32;
-    static_assert(E == 8 && TILE % (4 * THREADS) == 0, "8 products per thread: two 4-wide vectors, head bits in one byte");
-    __shared__ __align__(16) T prod[TILE];
-    __shared__ uint32_t heads[TILE / 32];
-    __shared__ T w_val[WARPS];
-    __shared__ int w_flag[WARPS];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int64_t r0 = row_begin + (int64_t)blockIdx.x * THREADS;
-    const int64_t r = r0 + tid;
-    const int64_t rl = r0 + THREADS < row_end ? r0 + THREADS : row_end;
-    int rs = 0, re = 0;
-    if (r < row_end) { rs = a.row_ptr[r]; re = a.row_ptr[r + 1]; }
-    const int b0 = __ldg(a.row_ptr + r0), b1 = __ldg(a.row_ptr + rl);
-    T sum = T(0);
-    for (int base = b0 & ~3; base < b1; base += TILE) {
-        if (tid < TILE / 32) heads[tid] = 0;
-        // 1. products of the tile (entries past b1 are zero so that the scan can run over the whole tile)
-#pragma unroll
-        for (int v = 0; v < TILE / (4 * THREADS); v++) {
-            const int o = (v * THREADS + tid) * 4;
-            const int j = base + o;
-            T p[4] = {T(0), T(0), T(0), T(0)};
-            if (j + 4 <= b1) {
-                const int4 c = ld_stream(reinterpret_cast<const int4 *>(a.col + j));
-                const V4<T> w = V4<T>::load(a.val + j);
-                p[0] = mul_rn(w.v[0], __ldg(a.x + c.x)); p[1] = mul_rn(w.v[1], __ldg(a.x + c.y));
-                p[2] = mul_rn(w.v[2], __ldg(a.x + c.z)); p[3] = mul_rn(w.v[3], __ldg(a.x + c.w));
-            } else {
-#pragma unroll
-                for (int t = 0; t < 4; t++)
-                    if (j + t < b1) p[t] = mul_rn(a.val[j + t], __ldg(a.x + a.col[j + t]));
-            }
-            prod[o + 0] = p[0]; prod[o + 1] = p[1]; prod[o + 2] = p[2]; prod[o + 3] = p[3];
-        }
-        __syncthreads();
-        // 2. head flags: where a row's part of this tile starts
-        const int lo = rs > base ? rs : base, hi = re < base + TILE ? re : base + TILE;
-        if (lo < hi) atomicOr(&heads[(lo - base) >> 5], 1u << ((lo - base) & 31));
-        __syncthreads();
-        // 3. segmented inclusive scan in place: thread-serial over 8, warp scan of (value, flag), scan of the warp totals
-        T v[E];
-#pragma unroll
-        for (int q = 0; q < E; q++) v[q] = prod[tid * E + q];
-        const unsigned hb = (heads[(tid * E) >> 5] >> ((tid * E) & 31)) & 0xFFu;
-#pragma unroll
-        for (int q = 1; q < E; q++)
-            if (!((hb >> q) & 1u)) v[q] = v[q - 1] + v[q];
-        T agg = v[E - 1];
-        int flag = hb != 0;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {           // inclusive segmented warp scan of the thread aggregates
-            const T up = __shfl_up_sync(0xFFFFFFFFu, agg, d);
-            const int uf = __shfl_up_sync(0xFFFFFFFFu, flag, d);
-            if (lane >= d) { if (!flag) agg = up + agg; flag |= uf; }
-        }
-        if (lane == 31) { w_val[warp] = agg; w_flag[warp] = flag; }
-        T carry = __shfl_up_sync(0xFFFFFFFFu, agg, 1);      // open segment arriving from the lanes before (this warp only)
-        int carry_closed = __shfl_up_sync(0xFFFFFFFFu, flag, 1);   // a head somewhere in those lanes: nothing older reaches this thread
-        if (lane == 0) { carry = T(0); carry_closed = 0; }
-        __syncthreads();
-        if (warp == 0) {                              // exclusive segmented scan of the warp totals (WARPS <= 32)
-            T wv = lane < WARPS ? w_val[lane] : T(0);
-            int wf = lane < WARPS ? w_flag[lane] : 0;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const T up = __shfl_up_sync(0xFFFFFFFFu, wv, d);
-                const int uf = __shfl_up_sync(0xFFFFFFFFu, wf, d);
-                if (lane >= d) { if (!wf) wv = up + wv; wf |= uf; }
-            }
-            const T ex = __shfl_up_sync(0xFFFFFFFFu, wv, 1);
-            if (lane < WARPS) w_val[lane] = lane == 0 ? T(0) : ex;
-        }
-        __syncthreads();
-        if (!carry_closed) carry = w_val[warp] + carry;      // the open segment may come from the warps before
-        if (!(hb & 1u)) {
-            v[0] = carry + v[0];
-#pragma unroll
-            for (int q = 1; q < E; q++) {
-                if ((hb >> q) & 1u) break;
-                v[q] = carry + v[q];
-            }
-        }
-#pragma unroll
-        for (int q = 0; q < E; q++) prod[tid * E + q] = v[q];
-        __syncthreads();
-        // 4. every row picks up the sum of its part of the tile at its last entry there
-        if (lo < hi) sum = sum + prod[hi - 1 - base];
-        __syncthreads();
-    }
-    if (r < row_end) {
-        if (MODE == MODE_CSR_ACC) { if (re > rs) a.y[r] = a.y[r] + sum; }
-        else st_stream(a.y + r, sum);
-    }
-}
-
 template <typename T, int MODE, int THREADS, int RPT, int TILE, bool PADDED, bool ORDERED = true, bool KEEP = true>
 __global__ void __launch_bounds__(THREADS)
 csr_stream_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
@@ -497,7 +390,10 @@ constexpr int PLAN_BLOCK_ROWS = 256;       // = cme213_spmv_csr_block_rows()
 //     vs stream 0.66 on 2 per row);
 //   every row 8, 16, ... 128 long: stream-padded (0.24-0.26 ms where plain stream needs 0.33-0.66 and the best vector 0.23-0.30);
 //   mean >= 96 (or regular rows beyond 128): vector, 16 lanes below a mean of 128, 32 above (256 per row: 0.16 ms vs stream 0.72);
-//   otherwise stream.  Evict-last x gathers measured exactly like plain stream on every matrix: not used.
+//   otherwise stream.  Evict-last x gathers measured exactly like plain stream on every matrix: not used.  Two further variants
+//   were built, verified and dropped after measuring (profiles/r02_notes.md): a persistent software-pipelined stream kernel
+//   (C1 0.0196 vs 0.0173 ms, C5 3.76 vs 2.52 ms) and a load-balanced one that reduces each tile by a segmented scan (power-law
+//   matrix 1.367 vs 1.345 ms uniform, 0.860 vs 0.819 banded): scattered gathers cost one L1 wavefront each whatever the sums do.
 //   BINNED only when whole 256-row blocks are long (>= 32 per row on average) and hold >= 30 % of the nonzeros: the block-list
 //   kernels cost ~10 % more than the plain one, which scattered long rows (the power-law matrix) do not pay back.
 constexpr double PLAN_SCALAR_MEAN = 2.5;
@@ -506,7 +402,6 @@ constexpr int PLAN_PADDED_MAX = 128;
 constexpr int PLAN_LONG_ROW = 96;          // statistics only: share of the nonzeros in rows at least this long
 constexpr int PLAN_LONG_BLOCK_MEAN = 32;   // a 256-row block is "long" from this mean row length on
 constexpr double PLAN_BINNED_FRACTION = 0.30;
-constexpr double PLAN_BALANCED_FRACTION = 0.15;   // share of the nonzeros in rows >= PLAN_LONG_ROW from which one-thread-per-row sums stall the CTA
 
 __global__ void plan_block_class_kernel(int64_t nblocks, int64_t rows, const int32_t *__restrict__ row_ptr, int thresh_nnz,
                                         uint32_t *is_long, unsigned long long *long_nnz) {
@@ -615,10 +510,7 @@ int plan_build(cme213_ctx *ctx, cme213_csr_plan *p, const int32_t *d_row_ptr, cu
             p->d_short = p->d_long = nullptr;
         }
     }
-    // skewed rows scattered all over the matrix (power-law graphs): the load-balanced stream kernel
-    if ((p->kernel & 0xFF) == CME213_CSR_STREAM && !ordered_only && p->long_nnz_fraction >= PLAN_BALANCED_FRACTION)
-        p->kernel = CME213_CSR_STREAM_BALANCED;
-    const char *names[] = {"auto", "scalar", "vector", "stream", "stream-padded", "stream-keep", "binned", "(unused)", "auto-ordered", "stream-balanced"};
+    const char *names[] = {"auto", "scalar", "vector", "stream", "stream-padded", "stream-keep", "binned", "(unused)", "auto-ordered"};
     const int kind = p->kernel & 0xFF;
     char lanes[24] = "";
     if (kind == CME213_CSR_VECTOR) snprintf(lanes, sizeof(lanes), " (%d lanes)", (p->kernel >> 8) & 0xFF);
@@ -656,19 +548,6 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
     if (rows <= 0) return CME213_OK;
     int kind = kernel & 0xFF;
     const int lanes = (kernel >> 8) & 0xFF;
-    if (kind == CME213_CSR_STREAM_BALANCED) {
-        if constexpr (MODE == MODE_CSR || MODE == MODE_CSR_ACC) {
-            if (a.order || !(aligned16(a.col) && aligned16(a.val))) { kind = CME213_CSR_STREAM; }
-            else {
-                constexpr int THREADS = 256, TILE = 2048;
-                csr_stream_balanced_kernel<T, MODE, THREADS, TILE><<<(unsigned)div_up(rows, THREADS), THREADS, 0, st>>>(a, row_begin, row_end);
-                CME213_LAUNCHED(ctx, "csr_stream_balanced_kernel");
-                return CME213_OK;
-            }
-        } else {
-            kind = CME213_CSR_STREAM;
-        }
-    }
     const bool padded = kind == CME213_CSR_STREAM_PADDED;
     const bool keep = kind == CME213_CSR_STREAM_KEEP;
     if (padded || keep) kind = CME213_CSR_STREAM;
@@ -1010,23 +889,6 @@ int cme213_internal_spmv_csr_f64_acc(cme213_ctx *ctx, int64_t rows_local, const 
 int cme213_internal_spmv_csr_f64_acc_keep(cme213_ctx *ctx, int64_t rows_local, const int32_t *d_row_ptr, const int32_t *d_col,
                                           const double *d_val, const double *d_x, double *d_y, cudaStream_t st) {
     return spmv_csr_acc<double>(ctx, rows_local, d_row_ptr, d_col, d_val, d_x, d_y, true, st);
-}
-template <typename T>
-static int spmv_csr_acc_balanced(cme213_ctx *ctx, int64_t rows_local, const int32_t *d_row_ptr, const int32_t *d_col, const T *d_val,
-                                 const T *d_x, T *d_y, cudaStream_t st) {
-    if (rows_local <= 0) return CME213_OK;
-    DeviceGuard g(ctx->device);
-    if (!(aligned16(d_col) && aligned16(d_val))) { set_error("spmv_csr acc: col/val must be 16-byte aligned"); return CME213_ERR_INVALID; }
-    Args<T> a{d_row_ptr, d_col, d_val, d_x, nullptr, d_y, nullptr, T(0), nullptr, nullptr, nullptr, 0, 0};
-    return launch_csr<T, MODE_CSR_ACC>(ctx, a, 0, rows_local, CME213_CSR_STREAM_BALANCED, st);
-}
-int cme213_internal_spmv_csr_f32_acc_balanced(cme213_ctx *ctx, int64_t rows_local, const int32_t *d_row_ptr, const int32_t *d_col,
-                                              const float *d_val, const float *d_x, float *d_y, cudaStream_t st) {
-    return spmv_csr_acc_balanced<float>(ctx, rows_local, d_row_ptr, d_col, d_val, d_x, d_y, st);
-}
-int cme213_internal_spmv_csr_f64_acc_balanced(cme213_ctx *ctx, int64_t rows_local, const int32_t *d_row_ptr, const int32_t *d_col,
-                                              const double *d_val, const double *d_x, double *d_y, cudaStream_t st) {
-    return spmv_csr_acc_balanced<double>(ctx, rows_local, d_row_ptr, d_col, d_val, d_x, d_y, st);
 }
 int cme213_internal_spmv_csr_f32_acc_keep(cme213_ctx *ctx, int64_t rows_local, const int32_t *d_row_ptr, const int32_t *d_col,
                                           const float *d_val, const float *d_x, float *d_y, cudaStream_t st) {

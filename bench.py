@@ -565,9 +565,8 @@ def make_powerlaw(ctx, torch, args, fmt):
 
         def step():
             ctx.call("cme213_spmv_hyb_csrtail_f32", rows, pitch, Kell, e_idx, e_val, t_p if tail.value else None, t_c, t_v, x, y,
-                     args.hyb_tail_kernel, stream=torch.cuda.current_stream())
-        meta["workload"] = "C4: HYB SpMV fp32 (ELL K=%d + tail as CSR, %s), %s, %d rows" % (
-            Kell, {3: "ordered tail sums", 9: "balanced tail sums"}[args.hyb_tail_kernel], name, rows)
+                     stream=torch.cuda.current_stream())
+        meta["workload"] = "C4: HYB SpMV fp32 (ELL K=%d + tail as CSR), %s, %d rows" % (Kell, name, rows)
         return dict(step=step, alg_bytes=alg, flops=2 * nnz.value, kernel="ell_v4_kernel<float> + csr_stream_lean_kernel<float,acc>",
                     launches_per_step=2 if tail.value else 1, meta=meta, keep=(e_idx, e_val, t_p, t_c, t_v, x, y))
     tail = C.c_int64()
@@ -1079,7 +1078,6 @@ def main():
     ap.add_argument("--powerlaw-rows", type=int, default=1 << 24)
     ap.add_argument("--window", type=int, default=0)
     ap.add_argument("--regular", type=int, default=0)
-    ap.add_argument("--hyb-tail-kernel", type=int, default=9, choices=[3, 9], help="hyb workload: 3 = tail rows summed in order (bit-identical to CSR), 9 = load-balanced segmented scan")
     ap.add_argument("--hyb-k", type=int, default=0, help="hyb workload: ELL width (0 = cme213_spmv_pick_format's choice)")
     ap.add_argument("--extras", type=int, default=1, help="also time the other single-GPU configs (N=1 only)")
     ap.add_argument("--no-cpu", action="store_true")

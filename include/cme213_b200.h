@@ -48,9 +48,6 @@ extern "C" {
 #define CME213_CSR_STREAM_PADDED 4 /* same, shared-memory products padded against bank conflicts: for matrices whose rows all have 8, 16, 32 ... entries.
                                       AUTO picks between 3 and 4 from the mean row length (one small device read per new matrix). */
 
-#define CME213_CSR_STREAM_BALANCED 9 /* CSR_STREAM with the per-row sums replaced by a segmented scan of the tile's products in shared memory:
-                                        work independent of how the entries are split into rows (skewed / power-law row lengths);
-                                        sums in scan order (reduction-order bound, not bit-identical) */
 #define CME213_CSR_AUTO_ORDERED 8 /* the dispatcher restricted to kernels that keep the CPU loop's summation order (scalar, stream, stream-padded):
                                      bit-identical to the CPU loop on every matrix, at the price of long rows being summed by one thread */
 #define CME213_PLAN_ORDERED 0x100  /* OR into cme213_csr_plan_create's elem_bytes for the same restriction */
@@ -344,17 +341,15 @@ int cme213_spmv_hyb_f64(cme213_ctx *ctx, int64_t num_rows, int64_t pitch, int K,
 /* HYB with the tail as a CSR matrix of its own instead of COO triplets: d_tail_ptr from cme213_csr_tail_row_ptr, its
  * column / value arrays are the d_coo_col / d_coo_val of cme213_csr_to_coo_tail_* (same order).  The tail runs through
  * the CSR stream kernel in accumulate mode (8 bytes per entry instead of COO's 12, coalesced update of y for the rows
- * that have a tail).  tail_kernel = CME213_CSR_STREAM: a row is summed ELL columns first, then its tail left to right --
- * bit-identical to the CPU loop; CME213_CSR_STREAM_BALANCED: the tail rows (the long ones) are reduced by a segmented
- * scan in shared memory, load-balanced, reduction-order bound.  d_tail_ptr == NULL: no tail.
- * reference: refs/Bell SC 2009.pdf section 3.5 (the split); slides/Lecture22.pdf slide 20 (the tail's CSR loop);
- * refs/Bell Tech Report 2008.pdf Fig. 24 (segmented reduction). */
+ * that have a tail).  A row is summed ELL columns first, then its tail left to right: bit-identical to the CPU loop.
+ * d_tail_ptr == NULL: no tail.  reference: refs/Bell SC 2009.pdf section 3.5 (the split); the tail kernel is the CSR
+ * shape of slides/Lecture22.pdf slide 20. */
 int cme213_spmv_hyb_csrtail_f32(cme213_ctx *ctx, int64_t num_rows, int64_t pitch, int K, const int32_t *d_ell_idx,
                                 const float *d_ell_val, const int32_t *d_tail_ptr, const int32_t *d_tail_col,
-                                const float *d_tail_val, const float *d_x, float *d_y, int tail_kernel, void *stream);
+                                const float *d_tail_val, const float *d_x, float *d_y, void *stream);
 int cme213_spmv_hyb_csrtail_f64(cme213_ctx *ctx, int64_t num_rows, int64_t pitch, int K, const int32_t *d_ell_idx,
                                 const double *d_ell_val, const int32_t *d_tail_ptr, const int32_t *d_tail_col,
-                                const double *d_tail_val, const double *d_x, double *d_y, int tail_kernel, void *stream);
+                                const double *d_tail_val, const double *d_x, double *d_y, void *stream);
 
 /* ---- format conversion on the device ----------------------------------- */
 /* Row pointers (num_rows + 1) of the tail left after an ELL(K) split: exclusive scan of max(len - K, 0). */

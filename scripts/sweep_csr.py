@@ -23,7 +23,7 @@ def main():
     lib = ctx.lib
     has_plan = hasattr(lib, "cme213_csr_plan_create")
     kernels = [("scalar", 1), ("vec2", 2 | 2 << 8), ("vec4", 2 | 4 << 8), ("vec8", 2 | 8 << 8), ("vec16", 2 | 16 << 8), ("vec32", 2 | 32 << 8),
-               ("stream", 3), ("padded", 4), ("balanced", 9), ("auto", 0)]
+               ("stream", 3), ("padded", 4), ("auto", 0)]
     print("matrix,rows,nnz,window," + ",".join(k for k, _ in kernels) + ",best,auto_vs_best")
     cases = [("len%d" % L, L, False) for L in (2, 8, 16, 64, 256)] + [("powerlaw", 0, True)]
     for name, L, power in cases:

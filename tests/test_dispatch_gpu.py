@@ -12,7 +12,7 @@ from oracle import generators as g
 from conftest import dev, dev_empty, host
 
 pytestmark = pytest.mark.gpu
-SCALAR, VECTOR, STREAM, PADDED, KEEP, BINNED, BALANCED = 1, 2, 3, 4, 5, 6, 9
+SCALAR, VECTOR, STREAM, PADDED, KEEP, BINNED = 1, 2, 3, 4, 5, 6
 
 
 def make_plan(ctx, cme, ptr, cols, elem_bytes):
@@ -202,54 +202,5 @@ def test_hyb_with_csr_tail_is_bit_identical_to_the_cpu_loop(ctx, cme, dtype):
         if tail.value:
             ctx.call("cme213_csr_to_coo_tail_" + sfx, rows, d_ptr, d_col, d_val, K, None, d_tr, d_tc, d_tv)
         d_y = dev(np.full(rows, -7.0, dtype))
-        ctx.call("cme213_spmv_hyb_csrtail_" + sfx, rows, pitch, K, d_ei, d_ev, d_tp if tail.value else None, d_tc, d_tv, d_x, d_y, STREAM)
+        ctx.call("cme213_spmv_hyb_csrtail_" + sfx, rows, pitch, K, d_ei, d_ev, d_tp if tail.value else None, d_tc, d_tv, d_x, d_y)
         assert np.array_equal(host(d_y), want), K          # ELL columns, then the tail in order = the CPU loop's order
-        d_y = dev(np.full(rows, -7.0, dtype))
-        ctx.call("cme213_spmv_hyb_csrtail_" + sfx, rows, pitch, K, d_ei, d_ev, d_tp if tail.value else None, d_tc, d_tv, d_x, d_y, BALANCED)
-        assert within_bound(host(d_y), lp, col, val, x), K  # tail by segmented scan: reduction-order bound
-        short = np.diff(lp) <= K
-        assert np.array_equal(host(d_y)[short], want[short])   # rows without a tail never leave the ELL kernel
-
-
-@pytest.mark.parametrize("dtype", [np.float32, np.float64])
-def test_balanced_stream_kernel_within_the_reduction_order_bound(ctx, cme, dtype):
-    """CME213_CSR_STREAM_BALANCED: per-row sums by a segmented scan of each tile's products.  Rows longer than a tile, empty
-    rows, ragged ends, a row range; and the dispatcher picks it for power-law rows scattered over the matrix."""
-    sfx = "f64" if dtype == np.float64 else "f32"
-    rng = np.random.default_rng(21)
-    length = np.array([0, 5000, 3, 0, 2048, 2049, 1, 7000, 0, 0, 2, 4097] + [3] * 600 + [0, 6000] + [1] * 300 + [9] * 77)
-    ptr = np.concatenate([[0], np.cumsum(length)]).astype(np.int32)
-    col = np.concatenate([np.sort(rng.choice(9000, l, replace=False)) for l in length]).astype(np.int32)
-    mats = [(ptr, col, rng.uniform(-1, 1, ptr[-1]).astype(dtype)), g.laplace3d(30, 20, 10, dtype=dtype),
-            g.random_csr(70000, 50000, 9.0, seed=3, dtype=dtype), g.random_csr(257, 300, 0.3, seed=4, dtype=dtype)]
-    lp = g.powerlaw_lengths(60000, 4, 265, 100, 256, seed=6)
-    pc, pv = g.random_csr_fill(lp, 60000, 0, seed=7)
-    mats.append((lp, pc, pv.astype(dtype)))
-    for ptr, col, val in mats:
-        cols = int(col.max()) + 1 if len(col) else 1
-        rows = len(ptr) - 1
-        x = rng.uniform(-1, 1, cols).astype(dtype)
-        d_ptr, d_col, d_val, d_x = dev(ptr), dev(col if len(col) else np.zeros(4, np.int32)), dev(val if len(val) else np.zeros(4, dtype)), dev(x)
-        d_y = dev(np.full(rows, -7.0, dtype))
-        ctx.call("cme213_spmv_csr_" + sfx, 0, rows, d_ptr, d_col, d_val, d_x, d_y, BALANCED)
-        got = host(d_y)
-        assert within_bound(got, ptr, col, val, x)
-        short = np.diff(ptr) <= 1
-        assert np.array_equal(got[short], oracle.csr_spmv(ptr, col, val, x)[short])      # nothing to reorder in rows of 0 or 1 entries
-        if rows > 600:
-            d_y = dev(np.full(rows, -7.0, dtype))
-            ctx.call("cme213_spmv_csr_" + sfx, 300, rows - 200, d_ptr, d_col, d_val, d_x, d_y, BALANCED)
-            part = host(d_y)
-            assert np.array_equal(part[300:rows - 200], got[300:rows - 200]) and (part[:300] == -7).all() and (part[rows - 200:] == -7).all()
-    # small-integer data: every summation order is exact, so the balanced kernel must equal the CPU loop bit for bit
-    ptr, col, _ = mats[0]
-    val = rng.integers(-3, 4, ptr[-1]).astype(dtype)
-    x = rng.integers(-3, 4, 9000).astype(dtype)
-    d_y = dev(np.full(len(ptr) - 1, -7.0, dtype))
-    ctx.call("cme213_spmv_csr_" + sfx, 0, len(ptr) - 1, dev(ptr), dev(col), dev(val), dev(x), d_y, BALANCED)
-    assert np.array_equal(host(d_y), oracle.csr_spmv(ptr, col, val, x))
-    # the dispatcher: scattered power-law rows -> balanced
-    lib = cme.load()
-    plan, d_ptr = make_plan(ctx, cme, lp, 60000, np.dtype(dtype).itemsize)
-    assert lib.cme213_csr_plan_kernel(plan) == BALANCED, lib.cme213_csr_plan_describe(plan)
-    lib.cme213_csr_plan_destroy(plan)

@@ -214,24 +214,10 @@ def test_c4_hyb_with_csr_tail_16mi_rows_bit_identical_to_csr(ctx, cme):
     y_csr = torch.empty(rows, dtype=torch.float32, device="cuda")
     ctx.call("cme213_spmv_csr_f32", 0, rows, d_ptr, d_col, d_val, d_x, y_csr, STREAM)
     y = torch.full((rows,), -7.0, dtype=torch.float32, device="cuda")
-    ctx.call("cme213_spmv_hyb_csrtail_f32", rows, pitch, K, e_idx, e_val, t_p, t_c, t_v, d_x, y, STREAM)
+    ctx.call("cme213_spmv_hyb_csrtail_f32", rows, pitch, K, e_idx, e_val, t_p, t_c, t_v, d_x, y)
+    y_auto = torch.empty_like(y)
+    ctx.call("cme213_spmv_csr_f32", 0, rows, d_ptr, d_col, d_val, d_x, y_auto, 0)     # the dispatcher's choice for this matrix: an order-preserving kernel
     torch.cuda.synchronize()
     assert torch.equal(y, y_csr)
-    # the dispatcher's own choice for this matrix (the load-balanced kernel: scan order) and HYB with a balanced tail:
-    # within gamma_k * sum|a x| of the CSR-stream result, and exact on rows that have nothing to reorder
-    lens = (d_ptr[1:] - d_ptr[:-1])
-    bound = torch.empty(rows, dtype=torch.float32, device="cuda")
-    ctx.call("cme213_spmv_csr_f32", 0, rows, d_ptr, d_col, d_val.abs(), d_x.abs(), bound, STREAM)
-    tol = 2.0 * (lens.to(torch.float64) + 2) * 2.0 ** -24 * bound.to(torch.float64) * (1 + 2.0 ** -20)
-    y_auto = torch.empty_like(y)
-    ctx.call("cme213_spmv_csr_f32", 0, rows, d_ptr, d_col, d_val, d_x, y_auto, 0)
-    y_bal = torch.full((rows,), -7.0, dtype=torch.float32, device="cuda")
-    ctx.call("cme213_spmv_hyb_csrtail_f32", rows, pitch, K, e_idx, e_val, t_p, t_c, t_v, d_x, y_bal, 9)
-    ordered = torch.empty_like(y)
-    ctx.call("cme213_spmv_csr_f32", 0, rows, d_ptr, d_col, d_val, d_x, ordered, 8)    # CME213_CSR_AUTO_ORDERED
-    torch.cuda.synchronize()
-    assert torch.equal(ordered, y_csr)
-    for other in (y_auto, y_bal):
-        assert bool(((other.to(torch.float64) - y_csr.to(torch.float64)).abs() <= tol).all())
-    assert torch.equal(y_bal[lens <= K], y_csr[lens <= K])
+    assert torch.equal(y_auto, y_csr)
     _free(torch)
