@@ -78,18 +78,22 @@ int main(int argc, char **argv) {
             cpu_pass(rows, ptr.data(), col.data(), val.data(), a.data(), b.data());
             cpu_pass(rows, ptr.data(), col.data(), val.data(), b.data(), a.data());
         }
+        // bitwise for the order-preserving modes; the split mode sums a row's owned and foreign columns separately, so it is held to
+        // the error norm of the instructors' checker (reference_spMVscan-released.cu:65-144): max |difference| over max |value|
+        // (an element-wise relative error is meaningless where a row cancels to ~0)
         int64_t diff = 0;
-        double worst = 0.0;
+        double worst = 0.0, big = 0.0;
         for (int64_t i = 0; i < rows; i++) {
             if (memcmp(&a[(size_t)i], &y[(size_t)i], 8)) diff++;
             const double d = a[(size_t)i] - y[(size_t)i], m = a[(size_t)i] < 0 ? -a[(size_t)i] : a[(size_t)i];
-            const double rel = (d < 0 ? -d : d) / (m > 1e-300 ? m : 1e-300);
-            worst = rel > worst ? rel : worst;
+            worst = (d < 0 ? -d : d) > worst ? (d < 0 ? -d : d) : worst;
+            big = m > big ? m : big;
         }
-        printf("check against the CPU loop: %lld of %lld elements differ bitwise, worst relative difference %.3e\n", (long long)diff,
-               (long long)rows, worst);
+        const double rel = worst / (big > 1e-300 ? big : 1e-300);
+        printf("check against the CPU loop: %lld of %lld elements differ bitwise, max |difference| / max |value| = %.3e\n", (long long)diff,
+               (long long)rows, rel);
         if (mode != CME213_SHARD_GATHER_SPLIT && diff) { printf("Test FAILED\n"); return 2; }
-        if (worst > 1e-9) { printf("Test FAILED\n"); return 2; }
+        if (rel > 1e-12) { printf("Test FAILED\n"); return 2; }
         printf("Test PASSED\n");
     }
     return 0;
