@@ -95,6 +95,7 @@ int csr_upload_host(int64_t num_rows, int64_t nnz, const int32_t *h_row_ptr, con
         // the dispatcher looks at the matrix here, once: no SpMV call of the timed loop ever synchronises
         rc = cme213_csr_plan_create(m->ctx, 0, num_rows, num_rows, m->d_ptr, (int)sizeof(T), nullptr, &m->plan);
         if (rc) return fail(rc);
+        cme213_internal_preload_spmv();
     }
     *out = m;
     return CME213_OK;
@@ -183,6 +184,8 @@ int fp_iterate_host(int n, int p, int q, int iters, const T *h_a, const int32_t 
     // Head flags depend on s only: built before the timer starts (Final.pdf p.3 allows work that
     // does not need entries of x outside the timed region).  The x gather is inside.
     TRY(cme213_segment_flags_from_offsets(c.ctx, d_s, p, n, d_flags, nullptr));
+    cme213_internal_preload_fp((int)sizeof(T));
+    CME213_CUDA(cudaDeviceSynchronize());
     Timer t;
     TRY(t.start());
     // x[k[i]] does not change between the iterations: gather it ONCE, inside the timed region (the reference does the same
@@ -362,6 +365,7 @@ CME213_API int cme213_pagerank_iterate_host(const uint32_t *h_graph_indices, con
     CME213_CUDA(cudaMemcpy(d_edges, h_graph_edges, nnz * 4, cudaMemcpyHostToDevice));
     CME213_CUDA(cudaMemcpy(d_inv, h_inv_edges_per_node, N * 4, cudaMemcpyHostToDevice));
     CME213_CUDA(cudaMemcpy(d_A, h_nodes_input, N * 4, cudaMemcpyHostToDevice));
+    cme213_internal_preload_spmv();
     Timer t;
     TRY(t.start());
     for (int it = 0; it < nr_iterations; it += 2) {

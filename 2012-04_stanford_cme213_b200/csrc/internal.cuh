@@ -54,3 +54,7 @@ int cme213_internal_spmv_csr_f32_acc_keep(cme213_ctx *ctx, int64_t rows_local, c
 constexpr int CME213_HIST_BINS = 4096;
 int cme213_internal_row_length_hist(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_row_ptr, unsigned long long *h_hist,
                                     int *max_len_out, cudaStream_t st);
+
+// preload the kernels of the host-pointer loops (spmv_csr.cu, scan.cu) so that lazy module loading stays outside their timers
+void cme213_internal_preload_spmv(void);
+void cme213_internal_preload_fp(int elem_bytes);

@@ -522,6 +522,26 @@ CME213_API int cme213_spmv_coo_accumulate_f64(cme213_ctx *ctx, int64_t nnz, cons
 
 // ---- internal: scan with caller-provided scratch (see internal.cuh) ----------------------------------
 #include "internal.cuh"
+void cme213_internal_preload_fp(int elem_bytes) {
+    cudaFuncAttributes at;
+    using scan::Cfg;
+    if (elem_bytes == 4) {
+        using P = MulPolicy<float>;
+        using G = MulGatherPolicy<float>;
+        cudaFuncGetAttributes(&at, gather_kernel<float>);
+        cudaFuncGetAttributes(&at, scan::lookback_scan_kernel<P, Cfg<P>::DIRECT_THREADS, Cfg<P>::DIRECT_VECS, Cfg<P>::DIRECT_MIN_BLOCKS>);
+        cudaFuncGetAttributes(&at, scan::scan_bulk_blocked_kernel<P, Cfg<P>::B_THREADS, Cfg<P>::B_VECS, Cfg<P>::B_STAGES, Cfg<P>::DPL, Cfg<P>::B_DEFER>);
+        cudaFuncGetAttributes(&at, scan::lookback_scan_kernel<G, Cfg<G>::DIRECT_THREADS, Cfg<G>::DIRECT_VECS, Cfg<G>::DIRECT_MIN_BLOCKS>);
+    } else {
+        using P = MulPolicy<double>;
+        using G = MulGatherPolicy<double>;
+        cudaFuncGetAttributes(&at, gather_kernel<double>);
+        cudaFuncGetAttributes(&at, scan::lookback_scan_kernel<P, Cfg<P>::DIRECT_THREADS, Cfg<P>::DIRECT_VECS, Cfg<P>::DIRECT_MIN_BLOCKS>);
+        cudaFuncGetAttributes(&at, scan::scan_bulk_blocked_kernel<P, Cfg<P>::B_THREADS, Cfg<P>::B_VECS, Cfg<P>::B_STAGES, Cfg<P>::DPL, Cfg<P>::B_DEFER>);
+        cudaFuncGetAttributes(&at, scan::lookback_scan_kernel<G, Cfg<G>::DIRECT_THREADS, Cfg<G>::DIRECT_VECS, Cfg<G>::DIRECT_MIN_BLOCKS>);
+    }
+    cudaGetLastError();
+}
 size_t cme213_internal_scan_u32_scratch_bytes(int64_t n) {
     return scan::scratch_bytes_for<PlainPolicy<uint32_t, false, false>>(n);
 }
