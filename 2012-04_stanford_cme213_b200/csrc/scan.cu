@@ -365,6 +365,8 @@ int run(cme213_ctx *ctx, const P &p, int64_t n, bool vec_ok, void *stream, const
                     CME213_TRY_BLOCKED(1024, 2, 3, 1) CME213_TRY_BLOCKED(896, 2, 3, 1)
                 } else {
                     CME213_TRY_BLOCKED(1024, 3, 4, 2) CME213_TRY_BLOCKED(896, 5, 3, 1) CME213_TRY_BLOCKED(640, 5, 4, 2)
+                    CME213_TRY_BLOCKED(768, 4, 4, 2) CME213_TRY_BLOCKED(512, 6, 4, 2) CME213_TRY_BLOCKED(704, 4, 4, 2) CME213_TRY_BLOCKED(640, 4, 5, 3)
+                    CME213_TRY_BLOCKED(576, 5, 4, 2) CME213_TRY_BLOCKED(640, 6, 3, 1) CME213_TRY_BLOCKED(512, 5, 5, 3) CME213_TRY_BLOCKED(832, 4, 4, 2)
                 }
 #undef CME213_TRY_BLOCKED
             }
