@@ -1155,9 +1155,18 @@ def main():
     # roofline of the dominant kernel: algorithmic bytes of ONE launch (this rank's rows) over its
     # average duration, timed alone with CUDA events on its launch stream
     roof = None
+    kms_all = None
     if args.workload == "c5":
         kms = time_steps(torch, wl["kernel_step"], args.steps, 3) / args.steps
         ach = wl["local_alg_bytes"] / (kms * 1e-3) / 1e9
+        kms_all = None
+        if dist is not None:   # the same kernel on every rank's own shard, all at once, no exchange: the slowest GPU bounds a coupled pass
+            dist.barrier()
+            mine = time_steps(torch, wl["kernel_step"], args.steps, 3) / args.steps
+            t = torch.zeros(world, dtype=torch.float64, device="cuda")
+            t[rank] = mine
+            dist.all_reduce(t)
+            kms_all = [float(v) for v in t.tolist()]
     else:
         kms = ms_step
         ach = value
@@ -1167,7 +1176,7 @@ def main():
     traffic, traffic_src = ncu_traffic(args.workload) if (world == 1 and args.grid == 512) else (None, None)
     roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic, "traffic_source": traffic_src,
             "kernel": wl["kernel"], "kernel_ms": kms, "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)" if peak_kind == "measured" else "fallback 6650 GB/s",
-            "frac_of_8TBs_spec": ach / 8000.0, "gflops": wl["flops"] / max(world, 1) / (kms * 1e-3) / 1e9 if args.workload == "c5" else wl["flops"] / (kms * 1e-3) / 1e9}
+            "kernel_ms_per_rank_uncoupled": kms_all if args.workload == "c5" else None, "frac_of_8TBs_spec": ach / 8000.0, "gflops": wl["flops"] / max(world, 1) / (kms * 1e-3) / 1e9 if args.workload == "c5" else wl["flops"] / (kms * 1e-3) / 1e9}
 
     out = {"metric": "spmv_algorithmic_gbs" if args.workload in ("c5", "c1", "ell", "hyb", "csr_powerlaw", "pagerank") else "algorithmic_gbs",
            "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
