@@ -363,13 +363,14 @@ int run(cme213_ctx *ctx, const P &p, int64_t n, bool vec_ok, void *stream, const
                 if constexpr (P::NIN >= 3) {   // two value streams per tile: smaller tiles
                     CME213_TRY_BLOCKED(640, 3, 3, 1) CME213_TRY_BLOCKED(640, 2, 4, 2) CME213_TRY_BLOCKED(768, 2, 4, 2) CME213_TRY_BLOCKED(512, 3, 4, 2)
                     CME213_TRY_BLOCKED(1024, 2, 3, 1) CME213_TRY_BLOCKED(896, 2, 3, 1) CME213_TRY_BLOCKED(576, 3, 4, 2) CME213_TRY_BLOCKED(448, 5, 3, 1)
-                    CME213_TRY_BLOCKED(384, 5, 3, 1) CME213_TRY_BLOCKED(448, 3, 5, 3)
+                    CME213_TRY_BLOCKED(384, 5, 3, 1) CME213_TRY_BLOCKED(448, 3, 5, 3) CME213_TRY_BLOCKED(384, 3, 6, 4) CME213_TRY_BLOCKED(320, 3, 7, 5)
                 } else {
                     CME213_TRY_BLOCKED(1024, 3, 4, 2) CME213_TRY_BLOCKED(896, 5, 3, 1) CME213_TRY_BLOCKED(640, 5, 4, 2)
                     CME213_TRY_BLOCKED(768, 4, 4, 2) CME213_TRY_BLOCKED(512, 6, 4, 2) CME213_TRY_BLOCKED(704, 4, 4, 2) CME213_TRY_BLOCKED(640, 4, 5, 3)
                     CME213_TRY_BLOCKED(576, 5, 4, 2) CME213_TRY_BLOCKED(640, 6, 3, 1) CME213_TRY_BLOCKED(512, 5, 5, 3) CME213_TRY_BLOCKED(832, 4, 4, 2)
                     CME213_TRY_BLOCKED(448, 7, 4, 2) CME213_TRY_BLOCKED(704, 5, 3, 1) CME213_TRY_BLOCKED(768, 5, 3, 1) CME213_TRY_BLOCKED(512, 7, 3, 1)
-                    CME213_TRY_BLOCKED(384, 7, 5, 3)
+                    CME213_TRY_BLOCKED(384, 7, 5, 3) CME213_TRY_BLOCKED(320, 7, 6, 4) CME213_TRY_BLOCKED(256, 7, 7, 5) CME213_TRY_BLOCKED(384, 5, 6, 4)
+                    CME213_TRY_BLOCKED(448, 5, 5, 3) CME213_TRY_BLOCKED(384, 7, 4, 2)
                 }
 #undef CME213_TRY_BLOCKED
             }
