@@ -986,12 +986,16 @@ template <class P> struct Cfg {
     static constexpr int VECS = STAGE_TARGET / (THREADS * VEC_BYTES) > 0 ? STAGE_TARGET / (THREADS * VEC_BYTES) : 1;
     static constexpr int STAGES = 2;   // large tiles amortise the ~0.7 us prefix round trip better than deep rings (profiles/r01_notes.md)
     static constexpr int DPL = 5;                               // a wave holds at most 32*DPL = 160 tiles
-    // blocked bulk kernel (dense-output policies): ~700 threads x 5 consecutive vectors = 55 KiB tiles, 4 ring slots,
-    // finish deferred by 2 iterations (sweep in profiles/r01_notes.md; segmented scans also stage their flag words)
-    // Policies that stage two value streams (the hoisted final-project step: a and xx) get 512 threads x 3 vectors (49 KiB tiles:
-    // 4 slots of the 640 x 5 shape would not fit in shared memory); sweep of 6 shapes in profiles/r02_notes.md.
+    // blocked bulk kernel (dense-output policies).  Shapes from the sweeps in profiles/r01_notes.md and profiles/r02_scan_shape_sweeps.txt;
+    // the number of vectors per thread must be odd (4 or 6 put the threads' runs on a power-of-two shared-memory stride: 0.56-0.76
+    // of peak where 5 and 7 reach 0.82-0.84) and threads * vectors a multiple of 64 (flag words are bulk-copied in 16-byte units):
+    //   plain scans              704 x 5, 4 ring slots, finish deferred by 2 iterations   (u32 scan 0.96)
+    //   segmented scans          384 x 7, 5 slots, deferred by 3                           (fp32 0.838; 640 x 5 x 4 x 2 gave 0.82)
+    //   two value streams (the hoisted final-project step: a and xx per tile)   576 x 3, 4 slots, deferred by 2   (7.77 ms per 10
+    //                            iterations; 512 x 3: 8.08, 640 x 3 with 3 slots: 9.05)
     static constexpr bool TWO_VALUE_STREAMS = P::BULK && P::NIN >= 3;
-    static constexpr int B_THREADS = TWO_VALUE_STREAMS ? 512 : P::SEG ? 640 : 704, B_VECS = TWO_VALUE_STREAMS ? 3 : 5, B_STAGES = 4, B_DEFER = 2;
+    static constexpr int B_THREADS = TWO_VALUE_STREAMS ? 576 : P::SEG ? 384 : 704, B_VECS = TWO_VALUE_STREAMS ? 3 : P::SEG ? 7 : 5,
+                         B_STAGES = (P::SEG && !TWO_VALUE_STREAMS) ? 5 : 4, B_DEFER = (P::SEG && !TWO_VALUE_STREAMS) ? 3 : 2;
     static constexpr int DIRECT_THREADS = 256, DIRECT_VECS = 4; // one-tile-per-CTA kernel
     static constexpr int DIRECT_MIN_BLOCKS = 6;   // 40 registers per thread: the gather-heavy policies want occupancy more than registers (fused step 1.68 -> 1.41 ms)
 };
