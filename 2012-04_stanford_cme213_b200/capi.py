@@ -62,7 +62,6 @@ PROTOTYPES = {
     "cme213_spmv_csr_f32": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _i, _p]),
     "cme213_spmv_csr_f64": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _i, _p]),
     "cme213_csr_plan_create": (_i, [_p, _i64, _i64, _i64, _p, _i, _p, C.POINTER(_p)]),
-    "cme213_csr_plan_create_with_columns": (_i, [_p, _i64, _i64, _i64, _p, _p, _i, _p, C.POINTER(_p)]),
     "cme213_csr_plan_destroy": (_i, [_p]),
     "cme213_ctx_clear_plans": (_i, [_p]),
     "cme213_csr_plan_kernel": (_i, [_p]),

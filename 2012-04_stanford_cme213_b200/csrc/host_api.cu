@@ -93,7 +93,7 @@ int csr_upload_host(int64_t num_rows, int64_t nnz, const int32_t *h_row_ptr, con
             if ((e = cudaMemcpy(m->d_val, h_val, (size_t)nnz * sizeof(T), cudaMemcpyHostToDevice)) != cudaSuccess) return fail(cuda_fail(e, "cudaMemcpy"));
         }
         // the dispatcher looks at the matrix here, once: no SpMV call of the timed loop ever synchronises
-        rc = cme213_csr_plan_create_with_columns(m->ctx, 0, num_rows, num_rows, m->d_ptr, m->d_col, (int)sizeof(T), nullptr, &m->plan);
+        rc = cme213_csr_plan_create(m->ctx, 0, num_rows, num_rows, m->d_ptr, (int)sizeof(T), nullptr, &m->plan);
         if (rc) return fail(rc);
         cme213_internal_preload_spmv();
     }

@@ -176,40 +176,11 @@ __device__ __forceinline__ void epilogue_lean(const Args<T> &a, int64_t r, T sum
 // (8 CTAs of 256 threads per SM); the feature-complete kernel below (block lists, padded products) needs 38-40
 // and measured 5-30 % slower on the same inputs, so it only runs when one of its features is asked for.
 struct NoSync {};
-// CTA order for stencil-like matrices (every row reaches exactly H rows back and H rows ahead: the z legs of a 3-D grid).
-// In row order the entries x[r+H] that a row block fetches are needed again by the block H rows later -- 27 MB of streamed
-// matrix later for the 512^3 grid, and again after another 27 MB -- and part of them has left L2 by then (C5: 15.2 GB of DRAM
-// traffic for 13.9 algorithmic).  The order below walks a strip of W row blocks through `zc` consecutive planes before moving
-// to the next strip, so the three planes a block touches are re-used within a few hundred blocks; planes are taken in chunks
-// of zc so that one chunk's pages stay within the TLB's reach (an order that ran z over the whole grid was slower in round 1).
-// The permutation is arithmetic (no table) and per-row sums are untouched: bit-identical results.
-struct PlaneOrder {
-    int P;      // row blocks per plane (H / THREADS)
-    int W;      // strip width in row blocks
-    int zc;     // planes per chunk
-    int planes; // planes in the launch (grid = planes * P blocks)
-};
-__device__ __forceinline__ int64_t plane_order_block(const PlaneOrder &o, unsigned bid) {
-    const unsigned chunk_blocks = (unsigned)o.zc * (unsigned)o.P;
-    const unsigned c = bid / chunk_blocks, rem = bid - c * chunk_blocks;
-    const unsigned z0 = c * (unsigned)o.zc;
-    const unsigned zn = (unsigned)o.planes - z0 < (unsigned)o.zc ? (unsigned)o.planes - z0 : (unsigned)o.zc;   // planes in this chunk
-    const unsigned strip_blocks = (unsigned)o.W * zn;
-    const unsigned s = rem / strip_blocks, rem2 = rem - s * strip_blocks;
-    const unsigned ws = (unsigned)o.P - s * (unsigned)o.W < (unsigned)o.W ? (unsigned)o.P - s * (unsigned)o.W : (unsigned)o.W;   // width of this strip
-    const unsigned z = rem2 / ws, w = rem2 - z * ws;
-    return (int64_t)(z0 + z) * o.P + (int64_t)s * o.W + w;
-}
-template <int X> struct ExtraArg { using type = NoSync; };
-template <> struct ExtraArg<1> { using type = ShardSync; };
-template <> struct ExtraArg<2> { using type = PlaneOrder; };
 // KEEP: 0 = plain (.cs streams, default-policy gathers), 1 = x gathers evict-last, 2 = 1 + col/val with an explicit
-// evict-first policy and no L1 allocation (tuning builds only).  XMODE: 0 = rows in order, 1 = SHARD (multi-GPU pass with the
-// exchange inside), 2 = PlaneOrder.
-template <typename T, int MODE, int THREADS, int TILE, bool PADDED, int XMODE = 0, int KEEP = 0>
+// evict-first policy and no L1 allocation (tuning builds only)
+template <typename T, int MODE, int THREADS, int TILE, bool PADDED, bool SHARD = false, int KEEP = 0>
 __global__ void __launch_bounds__(THREADS)
-csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename ExtraArg<XMODE>::type sync) {
-    constexpr bool SHARD = XMODE == 1;
+csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename std::conditional<SHARD, ShardSync, NoSync>::type sync) {
     static_assert(TILE % (4 * THREADS) == 0, "tile must be a whole number of 4-wide vectors per thread");
     constexpr int PAD = 128 / (int)sizeof(T);   // PADDED: one pad element per 128 bytes (see the kernel below)
     auto pidx = [](int j) { return PADDED ? j + j / PAD : j; };
@@ -223,7 +194,6 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename E
         blk -= sync.nb_hi;
         if (blk < 0) blk += gridDim.x;
     }
-    if constexpr (XMODE == 2) blk = plane_order_block(sync, blockIdx.x);
     const int64_t r0 = row_begin + blk * THREADS;
     const int64_t r = r0 + tid;
     const int64_t rl = r0 + THREADS < row_end ? r0 + THREADS : row_end;
@@ -411,8 +381,6 @@ struct cme213_csr_plan {
     int max_len = 0;
     double long_block_nnz_fraction = 0;
     bool ordered_only = false;            // CME213_CSR_AUTO_ORDERED: only kernels that keep the CPU loop's summation order
-    int order_P = 0, order_W = 0, order_zc = 0, order_planes = 0;   // stream kernel walks the row blocks in PlaneOrder (0 = row order)
-    long long reach = 0;                  // stencil-like matrices: every full row reaches exactly this many rows back and ahead
     int32_t *d_short = nullptr, *d_long = nullptr;   // BINNED: 256-row block numbers (counted from row_begin)
     int64_t n_short = 0, n_long = 0;
     char text[320] = "";
@@ -476,39 +444,9 @@ csr_vector_blocks_kernel(Args<T> a, int64_t row_begin, int64_t row_end, const in
     if (r < row_end && sub == 0) a.y[r] = sum;
 }
 
-// Does (almost) every row reach exactly H rows back and H rows ahead?  Pass 1: the extreme offsets; pass 2: how many rows have both.
-__global__ void plan_reach_kernel(int64_t rows, const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col, int64_t row0,
-                                  int *min_first, int *max_last) {
-    int lo = 0, hi = 0;
-    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += (int64_t)gridDim.x * blockDim.x) {
-        const int b = row_ptr[r], e = row_ptr[r + 1];
-        if (e > b) {
-            const int f = col[b] - (int)(row0 + r), l = col[e - 1] - (int)(row0 + r);
-            lo = f < lo ? f : lo;
-            hi = l > hi ? l : hi;
-        }
-    }
-    for (int d = 16; d > 0; d >>= 1) {
-        const int a = __shfl_xor_sync(0xFFFFFFFFu, lo, d), b = __shfl_xor_sync(0xFFFFFFFFu, hi, d);
-        lo = a < lo ? a : lo;
-        hi = b > hi ? b : hi;
-    }
-    if ((threadIdx.x & 31) == 0) { atomicMin(min_first, lo); atomicMax(max_last, hi); }
-}
-__global__ void plan_reach_count_kernel(int64_t rows, const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col, int64_t row0,
-                                        int first, int last, unsigned long long *both) {
-    unsigned cnt = 0;
-    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += (int64_t)gridDim.x * blockDim.x) {
-        const int b = row_ptr[r], e = row_ptr[r + 1];
-        if (e > b && col[b] - (int)(row0 + r) == first && col[e - 1] - (int)(row0 + r) == last) cnt++;
-    }
-    for (int d = 16; d > 0; d >>= 1) cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, d);
-    if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(both, (unsigned long long)cnt);
-}
-
 int vector_lanes_for(double mean) { return mean >= 24 ? 32 : mean >= 12 ? 16 : mean >= 6 ? 8 : mean >= 3 ? 4 : 2; }
 
-int plan_build(cme213_ctx *ctx, cme213_csr_plan *p, const int32_t *d_row_ptr, const int32_t *d_col, cudaStream_t st) {
+int plan_build(cme213_ctx *ctx, cme213_csr_plan *p, const int32_t *d_row_ptr, cudaStream_t st) {
     const int64_t rows = p->row_end - p->row_begin;
     const int32_t *ptr = d_row_ptr + p->row_begin;
     std::vector<unsigned long long> hist(CME213_HIST_BINS);
@@ -575,37 +513,6 @@ int plan_build(cme213_ctx *ctx, cme213_csr_plan *p, const int32_t *d_row_ptr, co
             p->d_short = p->d_long = nullptr;
         }
     }
-    // Stencil-like matrix under the stream kernel: if the rows reach exactly H back and ahead and 2 H rows of matrix do not fit
-    // comfortably in L2, walk the row blocks plane by plane inside strips (PlaneOrder above).  Needs the column indices.
-    if (d_col && (p->kernel & 0xFF) == CME213_CSR_STREAM && rows >= (1 << 20)) {
-        int *d_mm = nullptr;
-        CME213_CUDA(cudaMalloc(&d_mm, 16));
-        CME213_CUDA(cudaMemsetAsync(d_mm, 0, 16, st));
-        const int grid = ctx->sm_count * 8;
-        plan_reach_kernel<<<grid, 256, 0, st>>>(rows, ptr, d_col, p->row_begin, d_mm, d_mm + 1);
-        CME213_LAUNCHED(ctx, "plan_reach_kernel");
-        int mm[2] = {0, 0};
-        CME213_CUDA(cudaMemcpyAsync(mm, d_mm, 8, cudaMemcpyDeviceToHost, st));
-        CME213_CUDA(cudaStreamSynchronize(st));
-        const long long H = -(long long)mm[0];
-        const int threads = p->elem_bytes == 8 ? 128 : 256;
-        const double row_bytes = p->mean * (4 + p->elem_bytes) + 4 + 2 * p->elem_bytes;
-        if (H > 0 && H == (long long)mm[1] && H % threads == 0 && rows % H == 0 && rows / H >= 4 && 2.0 * (double)H * row_bytes >= 24e6) {
-            unsigned long long both = 0;
-            plan_reach_count_kernel<<<grid, 256, 0, st>>>(rows, ptr, d_col, p->row_begin, mm[0], mm[1], (unsigned long long *)(d_mm + 2));
-            CME213_LAUNCHED(ctx, "plan_reach_count_kernel");
-            CME213_CUDA(cudaMemcpyAsync(&both, d_mm + 2, 8, cudaMemcpyDeviceToHost, st));
-            CME213_CUDA(cudaStreamSynchronize(st));
-            if ((double)both >= 0.9 * (double)rows) {
-                p->reach = H;
-                p->order_P = (int)(H / threads);
-                p->order_W = p->order_P < 64 ? p->order_P : 64;
-                p->order_zc = 8;
-                p->order_planes = (int)(rows / H);
-            }
-        }
-        cudaFree(d_mm);
-    }
     const char *names[] = {"auto", "scalar", "vector", "stream", "stream-padded", "stream-keep", "binned", "(unused)", "auto-ordered"};
     const int kind = p->kernel & 0xFF;
     char lanes[24] = "";
@@ -614,16 +521,11 @@ int plan_build(cme213_ctx *ctx, cme213_csr_plan *p, const int32_t *d_row_ptr, co
              ordered_only ? " [order-preserving kernels only]" : "", (long long)rows, p->mean, p->max_len,
              regular ? "all rows equally long" : "irregular rows", 100.0 * p->long_nnz_fraction, PLAN_LONG_ROW,
              kind == CME213_CSR_BINNED ? "; short 256-row blocks -> stream, long blocks -> vector(32)" : "");
-    if (p->order_P) {
-        const size_t len = strlen(p->text);
-        snprintf(p->text + len, sizeof(p->text) - len, "; rows reach exactly %lld back and ahead: row blocks walked in strips of %d through %d planes at a time",
-                 p->reach, p->order_W, p->order_zc);
-    }
     return CME213_OK;
 }
 
 // the plan for (row_ptr, range), from the context's cache or built now (first call: synchronises)
-int plan_for(cme213_ctx *ctx, const int32_t *row_ptr, const int32_t *col, int64_t row_begin, int64_t row_end, int64_t num_cols, int elem_bytes,
+int plan_for(cme213_ctx *ctx, const int32_t *row_ptr, int64_t row_begin, int64_t row_end, int64_t num_cols, int elem_bytes,
              bool ordered_only, cudaStream_t st, cme213_csr_plan **out) {
     for (int i = 0; i < cme213_ctx::CSR_CACHE; i++) {
         const auto &e = ctx->csr_cache[i];
@@ -633,7 +535,7 @@ int plan_for(cme213_ctx *ctx, const int32_t *row_ptr, const int32_t *col, int64_
     cme213_csr_plan *p = new cme213_csr_plan();
     p->device = ctx->device; p->row_begin = row_begin; p->row_end = row_end; p->num_cols = num_cols; p->elem_bytes = elem_bytes;
     p->ordered_only = ordered_only;
-    int rc = plan_build(ctx, p, row_ptr, col, st);
+    int rc = plan_build(ctx, p, row_ptr, st);
     if (rc) { cme213_csr_plan_destroy(p); return rc; }
     auto &e = ctx->csr_cache[ctx->csr_cache_next++ % cme213_ctx::CSR_CACHE];
     cme213_csr_plan_destroy(e.plan);
@@ -725,21 +627,6 @@ template <typename T> struct Push { T *peer_lo = nullptr, *peer_hi = nullptr; in
 template <typename T>
 int run_plan(cme213_ctx *ctx, const cme213_csr_plan *p, Args<T> a, cudaStream_t st) {
     const int kind = p->kernel & 0xFF;
-    if (kind == CME213_CSR_STREAM && p->order_P && aligned16(a.col) && aligned16(a.val)) {
-        constexpr int THREADS = sizeof(T) == 8 ? 128 : 256, TILE = THREADS * 8;
-        PlaneOrder o{p->order_P, p->order_W, p->order_zc, p->order_planes};
-#ifdef CME213_TUNING   // CME213_PLANE_ORDER="strip_blocks,planes_per_chunk" (tuning builds only)
-        if (const char *cfg = getenv("CME213_PLANE_ORDER")) {
-            int w = 0, z = 0;
-            if (sscanf(cfg, "%d,%d", &w, &z) == 2 && w > 0 && z > 0) { o.W = w < o.P ? w : o.P; o.zc = z; }
-            if (w < 0) return launch_csr<T, MODE_CSR>(ctx, a, p->row_begin, p->row_end, p->kernel, st);   // "-1,0": row order
-        }
-#endif
-        const int64_t blocks = (int64_t)o.P * o.planes;     // = rows / THREADS exactly (checked when the plan was made)
-        csr_stream_lean_kernel<T, MODE_CSR, THREADS, TILE, false, 2><<<(unsigned)blocks, THREADS, 0, st>>>(a, p->row_begin, p->row_end, o);
-        CME213_LAUNCHED(ctx, "csr_stream_lean_kernel<plane order>");
-        return CME213_OK;
-    }
     if (kind != CME213_CSR_BINNED) return launch_csr<T, MODE_CSR>(ctx, a, p->row_begin, p->row_end, p->kernel, st);
     if (!(aligned16(a.col) && aligned16(a.val))) return launch_csr<T, MODE_CSR>(ctx, a, p->row_begin, p->row_end, CME213_CSR_SCALAR, st);
     if (p->n_short > 0) {
@@ -774,7 +661,7 @@ int spmv_csr_impl(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, const int
         // and kept in the context.  The matrix is taken to be about square for the x-residency rule (no column count here;
         // cme213_csr_plan_create takes one).
         cme213_csr_plan *plan = nullptr;
-        int rc = plan_for(ctx, d_row_ptr, d_col, row_begin, row_end, row_end, (int)sizeof(T), (kernel & 0xFF) == CME213_CSR_AUTO_ORDERED, (cudaStream_t)stream, &plan);
+        int rc = plan_for(ctx, d_row_ptr, row_begin, row_end, row_end, (int)sizeof(T), (kernel & 0xFF) == CME213_CSR_AUTO_ORDERED, (cudaStream_t)stream, &plan);
         if (rc) return rc;
         return run_plan<T>(ctx, plan, a, (cudaStream_t)stream);
     }
@@ -861,9 +748,8 @@ int cme213_internal_pagerank_propagate_w(cme213_ctx *ctx, const uint32_t *d_grap
 }
 
 // ---- plans: the dispatcher as an object (inspect once, then launch-only) ----------------------------------------------
-CME213_API int cme213_csr_plan_create_with_columns(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, int64_t num_cols,
-                                                   const int32_t *d_row_ptr, const int32_t *d_col, int elem_bytes, void *stream,
-                                                   cme213_csr_plan **out) {
+CME213_API int cme213_csr_plan_create(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, int64_t num_cols,
+                                      const int32_t *d_row_ptr, int elem_bytes, void *stream, cme213_csr_plan **out) {
     CME213_CHECK_CTX(ctx);
     if (!out) { set_error("csr_plan_create: null out pointer"); return CME213_ERR_INVALID; }
     *out = nullptr;
@@ -878,15 +764,11 @@ CME213_API int cme213_csr_plan_create_with_columns(cme213_ctx *ctx, int64_t row_
     p->device = ctx->device; p->row_begin = row_begin; p->row_end = row_end; p->num_cols = num_cols; p->elem_bytes = elem_bytes;
     p->ordered_only = ordered_only;
     if (row_end > row_begin) {
-        int rc = plan_build(ctx, p, d_row_ptr, d_col, (cudaStream_t)stream);
+        int rc = plan_build(ctx, p, d_row_ptr, (cudaStream_t)stream);
         if (rc) { cme213_csr_plan_destroy(p); return rc; }
     }
     *out = p;
     return CME213_OK;
-}
-CME213_API int cme213_csr_plan_create(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, int64_t num_cols,
-                                      const int32_t *d_row_ptr, int elem_bytes, void *stream, cme213_csr_plan **out) {
-    return cme213_csr_plan_create_with_columns(ctx, row_begin, row_end, num_cols, d_row_ptr, nullptr, elem_bytes, stream, out);
 }
 CME213_API int cme213_ctx_clear_plans(cme213_ctx *ctx) {
     CME213_CHECK_CTX(ctx);

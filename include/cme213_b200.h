@@ -188,13 +188,6 @@ int cme213_spmv_csr_f64(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, con
  * hw/hw_final/programming/paper/Final_Report_DongBang_Tsai.tex:228 (warp-per-segment regresses on short segments). */
 int cme213_csr_plan_create(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, int64_t num_cols, const int32_t *d_row_ptr,
                            int elem_bytes, void *stream, cme213_csr_plan **out);
-/* The same with the column indices at hand: the plan can then also recognise stencil-like matrices (almost every row
- * reaches exactly H rows back and H rows ahead -- the z legs of a 3-D grid -- and 2 H rows of matrix exceed what L2 keeps)
- * and let the stream kernel walk its row blocks plane by plane inside strips, so that the x entries of the neighbouring
- * planes are still in L2 when they are needed again.  Per-row sums are untouched: same bits.  CME213_CSR_AUTO does this too. */
-int cme213_csr_plan_create_with_columns(cme213_ctx *ctx, int64_t row_begin, int64_t row_end, int64_t num_cols,
-                                        const int32_t *d_row_ptr, const int32_t *d_col, int elem_bytes, void *stream,
-                                        cme213_csr_plan **out);
 int cme213_csr_plan_destroy(cme213_csr_plan *plan);
 /* CME213_CSR_AUTO's cached plans are keyed by the ADDRESS of row_ptr (and the row range): if a matrix is freed and another
  * of the same size lands at the same address, the old plan is applied to it.  Every kernel is correct on every matrix, so

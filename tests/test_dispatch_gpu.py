@@ -204,46 +204,3 @@ def test_hyb_with_csr_tail_is_bit_identical_to_the_cpu_loop(ctx, cme, dtype):
         d_y = dev(np.full(rows, -7.0, dtype))
         ctx.call("cme213_spmv_hyb_csrtail_" + sfx, rows, pitch, K, d_ei, d_ev, d_tp if tail.value else None, d_tc, d_tv, d_x, d_y)
         assert np.array_equal(host(d_y), want), K          # ELL columns, then the tail in order = the CPU loop's order
-
-
-@pytest.mark.parametrize("nz", [8, 20])
-def test_plan_walks_stencil_matrices_plane_by_plane_and_keeps_the_bits(ctx, cme, nz):
-    """512 x 512 x nz grid: every interior row reaches exactly 262144 rows back and ahead and two planes of matrix (54 MB)
-    exceed what L2 keeps, so the plan lets the stream kernel walk its row blocks in strips through 8 planes at a time
-    (a chunk of 8, 8 and 4 planes for nz = 20).  The order of the blocks changes, the sums do not."""
-    import torch
-    lib = cme.load()
-    nx = ny = 512
-    rows = nx * ny * nz
-    nnz = C.c_int64()
-    d_ptr = torch.empty(rows + 1, dtype=torch.int32, device="cuda")
-    ctx.call("cme213_gen_laplace3d_f64", nx, ny, nz, 0, rows, d_ptr, None, None, C.byref(nnz))
-    d_col = torch.empty(nnz.value, dtype=torch.int32, device="cuda")
-    d_val = torch.empty(nnz.value, dtype=torch.float64, device="cuda")
-    ctx.call("cme213_gen_laplace3d_f64", nx, ny, nz, 0, rows, d_ptr, d_col, d_val, C.byref(nnz))
-    d_x = torch.empty(rows, dtype=torch.float64, device="cuda")
-    ctx.call("cme213_fill_uniform_f64", d_x, rows, 4)
-    plan = C.c_void_p()
-    P = lambda t: C.c_void_p(t.data_ptr())
-    rc = lib.cme213_csr_plan_create_with_columns(ctx.h, 0, rows, rows, P(d_ptr), P(d_col), 8, None, C.byref(plan))
-    assert rc == 0, lib.cme213_last_error()
-    text = lib.cme213_csr_plan_describe(plan).decode()
-    assert lib.cme213_csr_plan_kernel(plan) == STREAM and "strips" in text and "262144" in text, text
-    y_plan = torch.full((rows,), -7.0, dtype=torch.float64, device="cuda")
-    assert lib.cme213_spmv_csr_plan_f64(ctx.h, plan, P(d_ptr), P(d_col), P(d_val), P(d_x), P(y_plan), None) == 0
-    y_rows = torch.empty_like(y_plan)
-    ctx.call("cme213_spmv_csr_f64", 0, rows, d_ptr, d_col, d_val, d_x, y_rows, STREAM)          # row order
-    y_mf = torch.empty_like(y_plan)
-    ctx.call("cme213_stencil_laplace_f64", nx, ny, nz, 6.0, 0, rows, d_x, y_mf)
-    ctx.lib.cme213_ctx_clear_plans(ctx.h)
-    y_auto = torch.empty_like(y_plan)
-    ctx.call("cme213_spmv_csr_f64", 0, rows, d_ptr, d_col, d_val, d_x, y_auto, 0)               # AUTO finds the same plan
-    torch.cuda.synchronize()
-    assert torch.equal(y_plan, y_rows) and torch.equal(y_plan, y_mf) and torch.equal(y_auto, y_rows)
-    want = oracle.csr_spmv(host(d_ptr[:nx * ny + 1]), host(d_col[:int(d_ptr[nx * ny])]), host(d_val[:int(d_ptr[nx * ny])]), host(d_x[:2 * nx * ny]))
-    assert np.array_equal(host(y_plan[:nx * ny]), want)
-    lib.cme213_csr_plan_destroy(plan)
-    # without the columns the plan cannot know: plain stream
-    rc = lib.cme213_csr_plan_create(ctx.h, 0, rows, rows, P(d_ptr), 8, None, C.byref(plan))
-    assert rc == 0 and "strips" not in lib.cme213_csr_plan_describe(plan).decode()
-    lib.cme213_csr_plan_destroy(plan)
