@@ -31,7 +31,6 @@ struct ShardSync {
                                                // that read ghost entries, whichever reaches further
     unsigned long long *cnt_lo, *cnt_hi;       // local: boundary CTAs finished so far, per side
     const unsigned long long *flag_lo, *flag_hi;   // local, written by the neighbours
-    unsigned long long *seen_lo, *seen_hi;     // local: the highest neighbour flag some CTA of this GPU has already observed
     unsigned long long *peer_flag_lo, *peer_flag_hi;   // this rank's flag word in each neighbour's memory
     unsigned long long *status;                // local: set to 1 when a wait gave up (a neighbour died or never launched)
     unsigned nb_lo, nb_hi;                     // boundary CTAs per side

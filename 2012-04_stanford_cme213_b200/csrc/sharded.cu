@@ -29,10 +29,8 @@ typedef unsigned long long u64;
 constexpr int LINE = 16;   // u64 words per 128-byte line: every word that another agent polls or writes gets its own line
 // cnt_lo / cnt_hi: finished boundary CTAs (HALO); status: a wait gave up; epoch: slices sent (GATHER*); waits: passes that
 // have waited for their input (GATHER*); flag[r]: written by rank r
-// seen_lo / seen_hi: the highest neighbour flag a CTA of this GPU has already observed (HALO: one poller per side republishes it)
-enum { W_CNT_LO = 0, W_CNT_HI = LINE, W_STATUS = 2 * LINE, W_EPOCH = 3 * LINE, W_WAITS = 4 * LINE, W_SEEN_LO = 5 * LINE, W_SEEN_HI = 6 * LINE,
-       W_FLAG0 = 7 * LINE };
-size_t sync_bytes(int world) { return (size_t)(7 + world) * LINE * sizeof(u64); }
+enum { W_CNT_LO = 0, W_CNT_HI = LINE, W_STATUS = 2 * LINE, W_EPOCH = 3 * LINE, W_WAITS = 4 * LINE, W_FLAG0 = 5 * LINE };
+size_t sync_bytes(int world) { return (size_t)(5 + world) * LINE * sizeof(u64); }
 
 struct Blob {   // what a rank tells the others (cme213_shard_export)
     cudaIpcMemHandle_t x[2], sync;
@@ -434,7 +432,6 @@ CME213_API int cme213_shard_step(cme213_shard *s, int src, void *stream) {
         k.nb_lo = k.peer_lo ? (unsigned)div_up(side_lo, B) : 0;
         k.nb_hi = k.peer_hi ? (unsigned)(nblocks - (s->nloc - side_hi) / B) : 0;
         k.cnt_lo = s->sync + W_CNT_LO; k.cnt_hi = s->sync + W_CNT_HI; k.status = s->sync + W_STATUS;
-        k.seen_lo = s->sync + W_SEEN_LO; k.seen_hi = s->sync + W_SEEN_HI;
         if (has_lo) { k.flag_lo = s->sync + W_FLAG0 + (size_t)(s->rank - 1) * LINE; k.peer_flag_lo = s->psync[s->rank - 1] + W_FLAG0 + (size_t)s->rank * LINE; }
         if (has_hi) { k.flag_hi = s->sync + W_FLAG0 + (size_t)(s->rank + 1) * LINE; k.peer_flag_hi = s->psync[s->rank + 1] + W_FLAG0 + (size_t)s->rank * LINE; }
         k.timeout_cycles = s->timeout_cycles;

@@ -63,32 +63,11 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
 __device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v) {
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
-__device__ __forceinline__ unsigned long long ld_acquire_gpu(const unsigned long long *p) {
-    unsigned long long v;
-    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-// Waits until the neighbour's flag says `want`.  Thousands of boundary CTAs start a pass at the same moment; if each of them
-// polled the peer-written word with system-scope acquire loads, those loads to one address would queue up behind each
-// other.  So one CTA per side (`poller`) watches the neighbour's flag and republishes what it saw in a local word with a
-// device-scope release; everybody else watches that word.  peer stores -> fence.sys + flag (peer) -> acquire.sys (poller) ->
-// release.gpu (seen) -> acquire.gpu (others): each link is morally strong, so the neighbour's rows are visible to all.
-__device__ __noinline__ void shard_wait(const unsigned long long *flag, unsigned long long *seen, unsigned long long want, bool poller,
-                                        const ShardSync &s) {
-    if (want == 0 || ld_acquire_gpu(seen) >= want) return;
+__device__ __noinline__ void shard_wait(const unsigned long long *flag, unsigned long long want, const ShardSync &s) {
     const long long t0 = clock64();
-    while (true) {
-        if (poller) {
-            const unsigned long long v = ld_acquire_sys(flag);
-            if (v >= want) {
-                asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(seen), "l"(v) : "memory");
-                return;
-            }
-        } else if (ld_acquire_gpu(seen) >= want) {
-            return;
-        }
-        if (clock64() - t0 > s.timeout_cycles) { atomicExch(s.status, 1ull); return; }   // never hang the GPU: give up, flag it
-        __nanosleep(poller ? 32 : 128);
+    while (ld_acquire_sys(flag) < want) {
+        if (clock64() - t0 > s.timeout_cycles) { atomicExch(s.status, 1ull); break; }   // never hang the GPU: give up, flag it
+        __nanosleep(64);
     }
 }
 
@@ -223,10 +202,8 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename s
         side_hi = sync.peer_hi != nullptr && rl > sync.side_hi_begin;
         if (side_lo || side_hi) {
             if (tid == 0) {
-                // the pollers are the first CTA of each side in launch order (the hi-side blocks come first, then the lo side)
-                if (side_lo) shard_wait(sync.flag_lo, sync.seen_lo, *(volatile unsigned long long *)sync.cnt_lo / sync.nb_lo, blk == 0, sync);
-                if (side_hi) shard_wait(sync.flag_hi, sync.seen_hi, *(volatile unsigned long long *)sync.cnt_hi / sync.nb_hi,
-                                        blockIdx.x == 0, sync);
+                if (side_lo) shard_wait(sync.flag_lo, *(volatile unsigned long long *)sync.cnt_lo / sync.nb_lo, sync);
+                if (side_hi) shard_wait(sync.flag_hi, *(volatile unsigned long long *)sync.cnt_hi / sync.nb_hi, sync);
             }
             __syncthreads();
         }
