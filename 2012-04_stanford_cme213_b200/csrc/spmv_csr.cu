@@ -63,25 +63,10 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
 __device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v) {
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
-__device__ __forceinline__ unsigned long long atom_add_release_sys(unsigned long long *p, unsigned long long v) {
-    unsigned long long old;
-    asm volatile("atom.add.release.sys.global.u64 %0, [%1], %2;" : "=l"(old) : "l"(p), "l"(v) : "memory");
-    return old;
-}
-// Polls the neighbour's flag with RELAXED system-scope loads (they bypass L1), not acquire loads: an acquire makes the SM drop
-// its whole L1 (CCTL.IVALL), and thousands of boundary CTAs wait here every pass while the other CTAs of the SM gather x
-// through that L1.  Nothing stale can sit in L1 for the rows this CTA is about to read: L1 is empty at kernel start, ghost
-// lines are only ever touched by CTAs that have passed this wait, and the neighbour raises the flag only after a system
-// fence behind its stores -- so the first fill of a ghost line after the flag was seen comes from L2 and is current.  The
-// branch on the polled value keeps the hardware from issuing those loads early; the asm memory clobber keeps the compiler.
 __device__ __noinline__ void shard_wait(const unsigned long long *flag, unsigned long long want, const ShardSync &s) {
-    if (want == 0) return;
     const long long t0 = clock64();
-    while (true) {
-        unsigned long long v;
-        asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(flag) : "memory");
-        if (v >= want) return;
-        if (clock64() - t0 > s.timeout_cycles) { atomicExch(s.status, 1ull); return; }   // never hang the GPU: give up, flag it
+    while (ld_acquire_sys(flag) < want) {
+        if (clock64() - t0 > s.timeout_cycles) { atomicExch(s.status, 1ull); break; }   // never hang the GPU: give up, flag it
         __nanosleep(64);
     }
 }
@@ -286,18 +271,15 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename s
             // One system-scope fence per CTA, by the thread that counts: the barrier orders every thread's peer stores before it
             // (the grid-barrier idiom).  A fence per thread measured ~9 us per side and pass: each one waits for the NVLink
             // acknowledgements and invalidates the SM's L1, which the x gathers of the other CTAs live on.
-            // The counting atomic is a RELEASE at system scope (the barrier puts every thread's peer stores before it: the
-            // grid-barrier idiom), not a full fence: a full fence also invalidates the SM's L1 (CCTL.IVALL in the SASS), which
-            // the x gathers of the sixteen other CTAs on the SM live on, and thousands of boundary CTAs do this every pass.
-            // Only the side's last CTA needs the acquire half (to see the others' stores) before it raises the flag.
             __syncthreads();
             if (tid == 0) {
+                __threadfence_system();
                 if (side_lo) {
-                    const unsigned long long done = atom_add_release_sys(sync.cnt_lo, 1ull) + 1;
+                    const unsigned long long done = atomicAdd(sync.cnt_lo, 1ull) + 1;
                     if (done % sync.nb_lo == 0) { __threadfence_system(); st_release_sys(sync.peer_flag_lo, done / sync.nb_lo); }
                 }
                 if (side_hi) {
-                    const unsigned long long done = atom_add_release_sys(sync.cnt_hi, 1ull) + 1;
+                    const unsigned long long done = atomicAdd(sync.cnt_hi, 1ull) + 1;
                     if (done % sync.nb_hi == 0) { __threadfence_system(); st_release_sys(sync.peer_flag_hi, done / sync.nb_hi); }
                 }
             }
