@@ -35,6 +35,7 @@ struct ShardSync {
     unsigned long long *status;                // local: set to 1 when a wait gave up (a neighbour died or never launched)
     unsigned nb_lo, nb_hi;                     // boundary CTAs per side
     long long timeout_cycles;
+    int late;                                  // 1: boundary CTAs LAST, flags raised by the next pass's first CTA (see spmv_csr.cu)
 };
 // x[dst] rows of this shard = A_shard x[src], halo rows pushed to the neighbours and flags raised as described above.
 // d_y / the peers are shifted so that index r is the shard's local row r; one kernel launch.

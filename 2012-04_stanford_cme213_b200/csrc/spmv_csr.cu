@@ -191,8 +191,30 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename s
     if constexpr (SHARD) {
         // boundary CTAs first (they are what the neighbours wait for): a rotation puts the last nb_hi row blocks in
         // front, the first nb_lo follow, then the interior in row order.  Only boundary rows read ghost entries.
-        blk -= sync.nb_hi;
-        if (blk < 0) blk += gridDim.x;
+        if (!sync.late) {
+            blk -= sync.nb_hi;
+            if (blk < 0) blk += gridDim.x;
+        } else {
+            // LATE protocol: interior first, boundary CTAs last.  The previous pass is complete (kernel boundary), so the first CTA
+            // tells the neighbours so; the boundary CTAs, at the end of the grid, wait for the neighbours' same message about THEIR
+            // previous pass (hidden behind the interior), and their pushes are made visible by this kernel's completion: no
+            // fence and no counting on the critical path of any boundary CTA.
+            const int64_t G = gridDim.x, nin = G - (int64_t)sync.nb_lo - (int64_t)sync.nb_hi;
+            if (nin > 0) {
+                if (blk < nin) blk += sync.nb_lo;
+                else if (blk < nin + sync.nb_lo) blk -= nin;
+            }
+            if (blockIdx.x == 0 && threadIdx.x == 0) {
+                unsigned long long e = 0;
+                if (sync.nb_lo) e = *(volatile unsigned long long *)sync.cnt_lo / sync.nb_lo;
+                else if (sync.nb_hi) e = *(volatile unsigned long long *)sync.cnt_hi / sync.nb_hi;
+                if (e > 0) {
+                    __threadfence_system();
+                    if (sync.peer_flag_lo && sync.nb_lo) st_release_sys(sync.peer_flag_lo, e);
+                    if (sync.peer_flag_hi && sync.nb_hi) st_release_sys(sync.peer_flag_hi, e);
+                }
+            }
+        }
     }
     const int64_t r0 = row_begin + blk * THREADS;
     const int64_t r = r0 + tid;
@@ -271,6 +293,14 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename s
             // One system-scope fence per CTA, by the thread that counts: the barrier orders every thread's peer stores before it
             // (the grid-barrier idiom).  A fence per thread measured ~9 us per side and pass: each one waits for the NVLink
             // acknowledgements and invalidates the SM's L1, which the x gathers of the other CTAs live on.
+            if (sync.late) {
+                __syncthreads();
+                if (tid == 0) {     // count only (relaxed): the pass number of the next kernel is read off these counters
+                    if (side_lo) atomicAdd(sync.cnt_lo, 1ull);
+                    if (side_hi) atomicAdd(sync.cnt_hi, 1ull);
+                }
+                return;
+            }
             __syncthreads();
             if (tid == 0) {
                 __threadfence_system();
