@@ -18,12 +18,15 @@ int cme213_internal_pagerank_propagate_w(cme213_ctx *ctx, const uint32_t *d_grap
 
 // ---- row-sharded iterate (sharded.cu drives it, the protocol runs inside spmv_csr.cu's stream kernel) --------------
 // Every rank keeps a small block of 64-bit words in its own memory: how many of its boundary CTAs have finished (per
-// side, counted up for ever), a status word, and one flag per neighbour that the NEIGHBOUR writes: "the halo rows of
-// my first `flag` passes have landed in your vector".  A boundary CTA of pass p first waits until the neighbour's flag
-// says p-1 (its rows of the previous pass are here, and -- because only boundary rows read ghost entries -- it has also
-// finished reading what this pass is about to overwrite), computes, stores its rows locally and into the neighbour's
-// vector, and the last boundary CTA of a side raises this rank's flag in the neighbour's memory to p.  The pass
-// number is not a kernel argument (a CUDA graph would freeze it): it is finished-CTAs / CTAs-per-side.
+// side, counted up for ever: passes completed = count / boundary CTAs per pass), a status word, and one flag per neighbour
+// that the NEIGHBOUR writes: "my first `flag` passes are complete, their halo rows are in your vector".
+// One pass = one launch: interior row blocks first, boundary row blocks last.  The launch's first CTA raises this rank's flag
+// at the neighbours to the number of passes it has completed (the previous kernel has ended, so everything it stored -- into
+// the neighbours' vectors too -- has been performed).  A boundary CTA of pass p waits until the neighbour's flag says p-1:
+// the neighbour's rows of the previous pass are here, and -- because only boundary rows read ghost entries, and the
+// neighbour's pass p-1 is over -- it has also finished reading what this CTA is about to overwrite in its vector.  Then
+// the CTA computes and stores its rows locally and into the neighbour's vector.  The wait sits at the end of the grid,
+// behind the interior, and nothing on a boundary CTA's path is a fence.
 struct ShardSync {
     double *peer_lo, *peer_hi;                 // neighbours' output vectors, shifted like y (null = no neighbour)
     int64_t push_lo_end, push_hi_begin;        // rows < push_lo_end go to peer_lo, rows >= push_hi_begin to peer_hi
@@ -35,7 +38,6 @@ struct ShardSync {
     unsigned long long *status;                // local: set to 1 when a wait gave up (a neighbour died or never launched)
     unsigned nb_lo, nb_hi;                     // boundary CTAs per side
     long long timeout_cycles;
-    int late;                                  // 1: boundary CTAs LAST, flags raised by the next pass's first CTA (see spmv_csr.cu)
 };
 // x[dst] rows of this shard = A_shard x[src], halo rows pushed to the neighbours and flags raised as described above.
 // d_y / the peers are shifted so that index r is the shard's local row r; one kernel launch.

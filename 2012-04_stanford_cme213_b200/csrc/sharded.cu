@@ -8,9 +8,10 @@
 //
 // One object per GPU (cme213_shard), in one process (cme213_shard_connect_local, peer access) or one process per GPU
 // (cme213_shard_export / cme213_shard_connect, CUDA IPC).  No NCCL and no host synchronisation on the data path:
-//   HALO          one kernel launch per pass.  Boundary CTAs run first, store their rows into the local vector AND
-//                 into the neighbour's vector over NVLink, and raise a flag in the neighbour's memory; the next
-//                 pass's boundary CTAs wait for that flag (the protocol is described in internal.cuh / spmv_csr.cu).
+//   HALO          one kernel launch per pass.  Interior row blocks first; the boundary CTAs, last in the grid, wait for the
+//                 neighbour's flag ("my previous pass is complete"), store their rows into the local vector AND into the
+//                 neighbour's vector over NVLink; the next launch's first CTA raises this rank's flag in the neighbours'
+//                 memory (the protocol is described in internal.cuh / spmv_csr.cu).
 //   GATHER        general matrices: after the SpMV every rank copies its slice into every peer's vector (peer copies
 //                 on the copy engines) and raises its flag at every peer.  Row order untouched: bitwise equal to 1 GPU.
 //   GATHER_SPLIT  same exchange on a second stream, overlapped with the next pass's local-column block (the columns a
@@ -19,7 +20,6 @@
 // Row sharding as such does not change the summation order of a row, so HALO and GATHER results are bitwise identical
 // to the single-GPU product (tests/test_sharded_gpu.py, bench.py's parity block).
 #include "internal.cuh"
-#include <stdlib.h>
 #include <string.h>
 #include <vector>
 
@@ -123,7 +123,6 @@ struct cme213_shard {
     bool ipc_opened = false, connected = false;
     int64_t push_lo = 0, push_hi = 0;          // rows the neighbours need from this rank
     long long timeout_cycles = 40000000000LL;  // ~20 s at 1.9 GHz: a peer that never shows up is an error, not a hang
-    int late = 0;
     // GATHER_SPLIT
     cudaStream_t comm = nullptr;
     cudaEvent_t ev_done = nullptr, ev_sent[2] = {nullptr, nullptr};
@@ -258,7 +257,6 @@ CME213_API int cme213_shard_create_f64(cme213_ctx *ctx, int rank, int world, int
     cme213_shard *s = new cme213_shard();
     s->ctx = ctx; s->rank = rank; s->world = world; s->rows_total = num_rows_total; s->wanted_mode = mode;
     s->bounds.assign(bounds, bounds + world + 1);
-    if (const char *e = getenv("CME213_SHARD_LATE")) s->late = atoi(e);   // EXPERIMENT: remove after measuring
     s->lo = bounds[rank]; s->hi = bounds[rank + 1]; s->nloc = s->hi - s->lo;
     s->row_ptr = d_row_ptr_local; s->col = d_col; s->val = d_val;
     if (s->nloc > 0 && (!d_row_ptr_local || !d_col || !d_val)) { delete s; set_error("shard_create: null matrix pointer"); return CME213_ERR_INVALID; }
@@ -438,7 +436,6 @@ CME213_API int cme213_shard_step(cme213_shard *s, int src, void *stream) {
         if (has_lo) { k.flag_lo = s->sync + W_FLAG0 + (size_t)(s->rank - 1) * LINE; k.peer_flag_lo = s->psync[s->rank - 1] + W_FLAG0 + (size_t)s->rank * LINE; }
         if (has_hi) { k.flag_hi = s->sync + W_FLAG0 + (size_t)(s->rank + 1) * LINE; k.peer_flag_hi = s->psync[s->rank + 1] + W_FLAG0 + (size_t)s->rank * LINE; }
         k.timeout_cycles = s->timeout_cycles;
-        k.late = s->late;
         return cme213_internal_spmv_csr_f64_shard(ctx, s->nloc, s->row_ptr, s->col, s->val, s->x[src], y, k, st);
     }
     if (s->mode == CME213_SHARD_GATHER) {

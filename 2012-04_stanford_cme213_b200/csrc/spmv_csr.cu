@@ -191,28 +191,23 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename s
     if constexpr (SHARD) {
         // boundary CTAs first (they are what the neighbours wait for): a rotation puts the last nb_hi row blocks in
         // front, the first nb_lo follow, then the interior in row order.  Only boundary rows read ghost entries.
-        if (!sync.late) {
-            blk -= sync.nb_hi;
-            if (blk < 0) blk += gridDim.x;
-        } else {
-            // LATE protocol: interior first, boundary CTAs last.  The previous pass is complete (kernel boundary), so the first CTA
-            // tells the neighbours so; the boundary CTAs, at the end of the grid, wait for the neighbours' same message about THEIR
-            // previous pass (hidden behind the interior), and their pushes are made visible by this kernel's completion: no
-            // fence and no counting on the critical path of any boundary CTA.
-            const int64_t G = gridDim.x, nin = G - (int64_t)sync.nb_lo - (int64_t)sync.nb_hi;
-            if (nin > 0) {
-                if (blk < nin) blk += sync.nb_lo;
-                else if (blk < nin + sync.nb_lo) blk -= nin;
-            }
-            if (blockIdx.x == 0 && threadIdx.x == 0) {
-                unsigned long long e = 0;
-                if (sync.nb_lo) e = *(volatile unsigned long long *)sync.cnt_lo / sync.nb_lo;
-                else if (sync.nb_hi) e = *(volatile unsigned long long *)sync.cnt_hi / sync.nb_hi;
-                if (e > 0) {
-                    __threadfence_system();
-                    if (sync.peer_flag_lo && sync.nb_lo) st_release_sys(sync.peer_flag_lo, e);
-                    if (sync.peer_flag_hi && sync.nb_hi) st_release_sys(sync.peer_flag_hi, e);
-                }
+        // Interior row blocks first, the boundary blocks (the first nb_lo and the last nb_hi in row order) last.
+        const int64_t G = gridDim.x, nin = G - (int64_t)sync.nb_lo - (int64_t)sync.nb_hi;
+        if (nin > 0) {
+            if (blk < nin) blk += sync.nb_lo;
+            else if (blk < nin + sync.nb_lo) blk -= nin;
+        }
+        // The previous pass of this rank is complete (kernel boundary: all its stores, the ones into the neighbours' vectors
+        // included, have been performed), so the first CTA says so to the neighbours.  The pass number is not a kernel argument
+        // (a CUDA graph would freeze it): it is finished boundary CTAs / boundary CTAs per pass.
+        if (blockIdx.x == 0 && threadIdx.x == 0) {
+            unsigned long long e = 0;
+            if (sync.nb_lo) e = *(volatile unsigned long long *)sync.cnt_lo / sync.nb_lo;
+            else if (sync.nb_hi) e = *(volatile unsigned long long *)sync.cnt_hi / sync.nb_hi;
+            if (e > 0) {
+                __threadfence_system();
+                if (sync.peer_flag_lo && sync.nb_lo) st_release_sys(sync.peer_flag_lo, e);
+                if (sync.peer_flag_hi && sync.nb_hi) st_release_sys(sync.peer_flag_hi, e);
             }
         }
     }
@@ -284,34 +279,17 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename s
     if (r < row_end && (MODE != MODE_CSR_ACC || re > rs)) epilogue_lean<T, MODE>(a, r, sum);   // ACC: rows without entries keep their y untouched
     if constexpr (SHARD) {
         if (side_lo || side_hi) {
-            // the exchange, fused: halo rows go straight into the neighbour's vector over NVLink (peer addresses bypass
-            // the local L2), then the side's last CTA tells the neighbour that this pass has landed
+            // the exchange, fused: halo rows go straight into the neighbour's vector over NVLink (peer addresses bypass the local L2)
             if (r < row_end) {
                 if (side_lo && r < sync.push_lo_end) sync.peer_lo[r] = sum;
                 if (side_hi && r >= sync.push_hi_begin) sync.peer_hi[r] = sum;
             }
-            // One system-scope fence per CTA, by the thread that counts: the barrier orders every thread's peer stores before it
-            // (the grid-barrier idiom).  A fence per thread measured ~9 us per side and pass: each one waits for the NVLink
-            // acknowledgements and invalidates the SM's L1, which the x gathers of the other CTAs live on.
-            if (sync.late) {
-                __syncthreads();
-                if (tid == 0) {     // count only (relaxed): the pass number of the next kernel is read off these counters
-                    if (side_lo) atomicAdd(sync.cnt_lo, 1ull);
-                    if (side_hi) atomicAdd(sync.cnt_hi, 1ull);
-                }
-                return;
-            }
+            // No fence and no flag here: this kernel's completion makes the pushed rows visible, and the next pass's first CTA
+            // announces it (a system fence in every boundary CTA -- the first version -- cost 13-14 us per pass at 8 GPUs).
             __syncthreads();
-            if (tid == 0) {
-                __threadfence_system();
-                if (side_lo) {
-                    const unsigned long long done = atomicAdd(sync.cnt_lo, 1ull) + 1;
-                    if (done % sync.nb_lo == 0) { __threadfence_system(); st_release_sys(sync.peer_flag_lo, done / sync.nb_lo); }
-                }
-                if (side_hi) {
-                    const unsigned long long done = atomicAdd(sync.cnt_hi, 1ull) + 1;
-                    if (done % sync.nb_hi == 0) { __threadfence_system(); st_release_sys(sync.peer_flag_hi, done / sync.nb_hi); }
-                }
+            if (tid == 0) {     // count only (relaxed): the next kernel reads its pass number off these counters
+                if (side_lo) atomicAdd(sync.cnt_lo, 1ull);
+                if (side_hi) atomicAdd(sync.cnt_hi, 1ull);
             }
         }
     }

@@ -262,8 +262,8 @@ int cme213_ipc_close(void *d_ptr);
  * the iteration itself is the ping-pong loop of hw/hw1/programming/pagerank.cu:59-67,128-132.
  * Exchange modes: */
 #define CME213_SHARD_AUTO 0          /* HALO when every rank's columns stay inside its two neighbours' rows, else GATHER */
-#define CME213_SHARD_HALO 1          /* ONE kernel launch per pass: boundary rows first, stored into the neighbours' vectors
-                                        over NVLink by the kernel itself, ordered by flags in peer memory */
+#define CME213_SHARD_HALO 1          /* ONE kernel launch per pass: boundary rows stored into the neighbours' vectors over NVLink
+                                        by the kernel itself, passes ordered by flags in peer memory */
 #define CME213_SHARD_GATHER 2        /* any matrix: SpMV, then every rank copies its slice into every peer's vector */
 #define CME213_SHARD_GATHER_SPLIT 3  /* same exchange overlapped with the next pass's local-column block; the split
                                         changes the summation order of a row (reduction-order tolerance, not bitwise);
