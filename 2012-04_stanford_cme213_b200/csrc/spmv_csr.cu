@@ -179,7 +179,7 @@ struct NoSync {};
 // KEEP: 0 = plain (.cs streams, default-policy gathers), 1 = x gathers evict-last, 2 = 1 + col/val with an explicit
 // evict-first policy and no L1 allocation (tuning builds only)
 template <typename T, int MODE, int THREADS, int TILE, bool PADDED, bool SHARD = false, int KEEP = 0>
-__global__ void __launch_bounds__(THREADS, SHARD ? 2048 / THREADS : 1)   // SHARD: hold the 32 registers (34 without the bound = 12 instead of 16 CTAs per SM)
+__global__ void __launch_bounds__(THREADS, SHARD ? 2048 / THREADS : 0)   // SHARD: hold the 32 registers (34 without the bound = 12 instead of 16 CTAs per SM); 0 = no bound (a 1 here let ptxas take 40-48)
 csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename std::conditional<SHARD, ShardSync, NoSync>::type sync) {
     static_assert(TILE % (4 * THREADS) == 0, "tile must be a whole number of 4-wide vectors per thread");
     constexpr int PAD = 128 / (int)sizeof(T);   // PADDED: one pad element per 128 bytes (see the kernel below)
