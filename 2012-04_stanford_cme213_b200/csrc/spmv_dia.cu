@@ -261,6 +261,118 @@ stencil_vec_kernel(int nx, int ny, int nz, int64_t row_begin, int64_t row_end, T
     }
 }
 
+// Whole grid lines: a thread owns one 16-byte vector of G consecutive lines of one plane.  Against the kernel above:
+//  * the y legs of the G lines are each other's centre loads: 3G + 2 vector loads for G lines instead of 5G (the capture of
+//    the kernel above, profiles/r02_ncu_stencil_vec.txt: DRAM traffic = the algorithmic 2.1 GB, 5.2 GB read from L2, every
+//    unit half busy, warps waiting on loads 15 of 22 cycles per instruction and the issue slots 61 % busy);
+//  * the plane / line coordinates come from one division per thread (not two per vector), no 64-bit index arithmetic;
+//  * a neighbour leg is ONE subtraction: s - v has the bits of s + (-1 * v), the product being exact.
+// Same legs in the same order as the CSR rows, so still bit-identical to the CSR / DIA product.
+// blockDim = (threads along the line: a multiple of 32, line groups per CTA); needs nx % NP == 0, ny % G == 0, whole lines.
+__device__ __forceinline__ float sub_rn(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ double sub_rn(double a, double b) { return __dsub_rn(a, b); }
+
+template <typename T, int G, bool PLANES>
+__global__ void __launch_bounds__(256)
+stencil_lines_kernel(int nx, int ny, int nz, uint32_t first_line, uint32_t num_groups, T centre, const T *__restrict__ x,
+                     T *__restrict__ y) {
+    constexpr int NP = Vec16<T>::NP;
+    uint32_t iz, iy0;
+    if constexpr (PLANES) {     // whole planes: grid = (line groups of a plane / blockDim.y, chunks of a line, planes), no division
+        iy0 = (blockIdx.x * blockDim.y + threadIdx.y) * G;
+        if (iy0 >= (uint32_t)ny) return;                                // the same for a whole warp
+        iz = first_line + blockIdx.z;                                   // first_line is the first PLANE here
+    } else {
+        const uint32_t group = blockIdx.x * blockDim.y + threadIdx.y;
+        if (group >= num_groups) return;
+        const uint32_t line0 = first_line + group * G;
+        iz = line0 / (uint32_t)ny;
+        iy0 = line0 - iz * (uint32_t)ny;
+    }
+    const int lane = threadIdx.x & 31;
+    const int ix = (int)(blockIdx.y * blockDim.x + threadIdx.x) * NP;
+    const bool alive = ix < nx;                                         // dead lanes stay for the shuffles
+    const int64_t plane = (int64_t)nx * ny, i0 = (int64_t)iz * plane + (int64_t)iy0 * nx + ix;
+    const T *p = x + i0;
+    const bool has_zm = iz > 0, has_zp = iz + 1 < (uint32_t)nz, has_ym = iy0 > 0, has_yp = iy0 + G < (uint32_t)ny;
+    const bool edge_l = lane == 0 && ix > 0, edge_r = lane == 31 && ix + NP < nx;
+    // Absent legs stay +0: a - (+0) == a for every a, so the sums below need no boundary tests.
+    T c[G + 2][NP], zm[G][NP], zp[G][NP], el[G], er[G];
+#pragma unroll
+    for (int l = 0; l < G + 2; ++l)
+#pragma unroll
+        for (int t = 0; t < NP; ++t) c[l][t] = T(0);
+#pragma unroll
+    for (int l = 0; l < G; ++l) {
+        el[l] = T(0); er[l] = T(0);
+#pragma unroll
+        for (int t = 0; t < NP; ++t) { zm[l][t] = T(0); zp[l][t] = T(0); }
+    }
+    // every load of the thread before the first use
+    if (alive) {
+        const T *q = p + plane;
+        if (has_zp) {                                                    // the leg that comes from DRAM goes first
+#pragma unroll
+            for (int l = 0; l < G; ++l, q += nx) Vec16<T>::load(q, zp[l]);
+        }
+        q = p - nx;
+#pragma unroll
+        for (int l = 0; l < G + 2; ++l, q += nx)
+            if ((l > 0 || has_ym) && (l < G + 1 || has_yp)) Vec16<T>::load(q, c[l]);
+        q = p - plane;
+        if (has_zm) {
+#pragma unroll
+            for (int l = 0; l < G; ++l, q += nx) Vec16<T>::load(q, zm[l]);
+        }
+        if (edge_l) {
+            q = p - 1;
+#pragma unroll
+            for (int l = 0; l < G; ++l, q += nx) el[l] = __ldg(q);
+        }
+        if (edge_r) {
+            q = p + NP;
+#pragma unroll
+            for (int l = 0; l < G; ++l, q += nx) er[l] = __ldg(q);
+        }
+    }
+    T *out = y + i0;
+#pragma unroll
+    for (int l = 0; l < G; ++l, out += nx) {
+        T left = __shfl_up_sync(0xFFFFFFFFu, c[l + 1][NP - 1], 1), right = __shfl_down_sync(0xFFFFFFFFu, c[l + 1][0], 1);
+        if (lane == 0) left = el[l];          // the loaded neighbour, or +0 at the start of the line
+        if (lane == 31) right = er[l];        // a dead lane's centre is +0, so the last alive lane of a short line needs no test
+        T s[NP];
+#pragma unroll
+        for (int t = 0; t < NP; ++t) {
+            T a = sub_rn(T(0), zm[l][t]);
+            a = sub_rn(a, c[l][t]);
+            a = sub_rn(a, t > 0 ? c[l + 1][t - 1] : left);
+            a = add_rn(a, mul_rn(centre, c[l + 1][t]));
+            a = sub_rn(a, t < NP - 1 ? c[l + 1][t + 1] : right);
+            a = sub_rn(a, c[l + 2][t]);
+            s[t] = sub_rn(a, zp[l][t]);
+        }
+        if (alive) Vec16<T>::store(out, s);
+    }
+}
+
+template <typename T, int G>
+void launch_stencil_lines(int nx, int ny, int nz, int64_t first_line, int64_t lines, T centre, const T *d_x, T *d_y, cudaStream_t st) {
+    constexpr int NP = Vec16<T>::NP;
+    const int vecs = nx / NP;
+    const int tx = vecs >= 256 ? 256 : (vecs + 31) / 32 * 32, ty = 256 / tx > 0 ? 256 / tx : 1;
+    dim3 block((unsigned)tx, (unsigned)ty);
+    const unsigned chunks = (unsigned)div_up(vecs, tx);
+    if (first_line % ny == 0 && lines % ny == 0 && lines / ny <= 65535 && chunks <= 65535) {
+        dim3 grid((unsigned)div_up(ny / G, ty), chunks, (unsigned)(lines / ny));
+        stencil_lines_kernel<T, G, true><<<grid, block, 0, st>>>(nx, ny, nz, (uint32_t)(first_line / ny), 0u, centre, d_x, d_y);
+    } else {
+        const int64_t groups = lines / G;
+        dim3 grid((unsigned)div_up(groups, ty), chunks);
+        stencil_lines_kernel<T, G, false><<<grid, block, 0, st>>>(nx, ny, nz, (uint32_t)first_line, (uint32_t)groups, centre, d_x, d_y);
+    }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 stencil_scalar_kernel(int nx, int ny, int nz, int64_t row_begin, int64_t row_end, T centre, const T *__restrict__ x,
@@ -288,6 +400,23 @@ int stencil_impl(cme213_ctx *ctx, int nx, int ny, int nz, T centre, int64_t row_
     cudaStream_t st = (cudaStream_t)stream;
     const int64_t rows = row_end - row_begin;
     constexpr int NP = Vec16<T>::NP;
+    if (nx % NP == 0 && row_begin % nx == 0 && rows % nx == 0 && aligned16(d_x) && aligned16(d_y)) {
+        const int64_t first_line = row_begin / nx, lines = rows / nx;
+        int g = (ny % 4 == 0 && first_line % 4 == 0 && lines % 4 == 0) ? 4 : (ny % 2 == 0 && first_line % 2 == 0 && lines % 2 == 0) ? 2 : 1;
+#ifdef CME213_TUNING   // CME213_STENCIL_G = 0 (the one-vector kernel below), 1, 2, 4
+        int forced = -1;
+        if (const char *e = getenv("CME213_STENCIL_G")) forced = atoi(e);
+        if (forced > 0 && forced <= g) g = forced;
+        if (forced != 0)
+#endif
+        {
+            if (g == 4) launch_stencil_lines<T, 4>(nx, ny, nz, first_line, lines, centre, d_x, d_y, st);
+            else if (g == 2) launch_stencil_lines<T, 2>(nx, ny, nz, first_line, lines, centre, d_x, d_y, st);
+            else launch_stencil_lines<T, 1>(nx, ny, nz, first_line, lines, centre, d_x, d_y, st);
+            CME213_LAUNCHED(ctx, "stencil_lines_kernel");
+            return CME213_OK;
+        }
+    }
     if (nx % NP == 0 && row_begin % NP == 0 && rows % NP == 0 && aligned16(d_x) && aligned16(d_y)) {
         // 256 threads x one vector each measured best (0.464 ms at 512^3 fp64); 2 or 4 vectors per thread and larger
         // CTAs were slower (0.49-0.85 ms)

@@ -305,10 +305,24 @@ def make_c1(ctx, torch, args):
     torch.cuda.synchronize()
 
     alg = nnz.value * 8 + (rows + 1) * 4 + rows * 8
+
+    # What this size allows at all: a plain device copy moving the same bytes per launch (half read, half written), launched
+    # the same way (graph of 8 back-to-back launches over rotating buffers, cold L2).  A probe for the notes, not a product path.
+    half = (alg // 2 + 15) // 16 * 16
+    bufs = [(torch.empty(half, dtype=torch.uint8, device="cuda"), torch.empty(half, dtype=torch.uint8, device="cuda")) for _ in range(copies)]
+    for a, b in bufs:
+        b.copy_(a)
+    torch.cuda.synchronize()
+    cgraph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(cgraph):
+        for a, b in bufs:
+            b.copy_(a)
+    copy_ms = time_steps(torch, cgraph.replay, 20, 3) / 20 / copies
+    del cgraph, bufs
     return dict(step=graph.replay, alg_bytes=alg * copies, flops=2 * nnz.value * copies, kernel="csr_stream_lean_kernel<float>",
                 launches_per_step=copies,
                 meta={"workload": "C1: CSR SpMV fp32, 2-D 5-point Poisson 1024x1024", "rows": rows, "nnz": nnz.value,
-                      "passes_per_step": copies,
+                      "passes_per_step": copies, "device_copy_of_the_same_bytes_ms_per_launch": copy_ms,
                       "l2": "one step = CUDA graph of %d passes over %d independent copies (%.0f MB total): every pass is cold in L2" % (copies, copies, copies * alg / 1e6)},
                 keep=(mats, graph))
 

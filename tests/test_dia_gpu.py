@@ -145,7 +145,7 @@ def test_dia_full_size_matches_csr(ctx, cme):
 
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
 @pytest.mark.parametrize("shape", [(1, 1, 1), (4, 1, 1), (7, 5, 1), (8, 8, 1), (9, 7, 5), (32, 16, 8), (36, 3, 6), (64, 64, 9), (132, 9, 40),
-                                   (256, 20, 4), (4, 4, 70)])
+                                   (256, 20, 4), (4, 4, 70), (512, 8, 3), (1024, 4, 6), (2048, 2, 3), (520, 6, 2), (96, 10, 7)])
 def test_matrix_free_stencil_equals_csr_bit_exact(ctx, dtype, shape):
     nx, ny, nz = shape
     rows = nx * ny * nz
