@@ -402,16 +402,21 @@ int stencil_impl(cme213_ctx *ctx, int nx, int ny, int nz, T centre, int64_t row_
     constexpr int NP = Vec16<T>::NP;
     if (nx % NP == 0 && row_begin % nx == 0 && rows % nx == 0 && aligned16(d_x) && aligned16(d_y)) {
         const int64_t first_line = row_begin / nx, lines = rows / nx;
-        int g = (ny % 4 == 0 && first_line % 4 == 0 && lines % 4 == 0) ? 4 : (ny % 2 == 0 && first_line % 2 == 0 && lines % 2 == 0) ? 2 : 1;
+        // 512^3 fp64 (profiles/r02_stencil_kernel_sweep.txt): one-vector kernel 0.467 ms, G = 1 0.423, G = 2 0.412, G = 4 0.435 (98 registers)
+        int g = (ny % 2 == 0 && first_line % 2 == 0 && lines % 2 == 0) ? 2 : 1;
 #ifdef CME213_TUNING   // CME213_STENCIL_G = 0 (the one-vector kernel below), 1, 2, 4
         int forced = -1;
         if (const char *e = getenv("CME213_STENCIL_G")) forced = atoi(e);
+        if (forced == 4 && ny % 4 == 0 && first_line % 4 == 0 && lines % 4 == 0) {
+            launch_stencil_lines<T, 4>(nx, ny, nz, first_line, lines, centre, d_x, d_y, st);
+            CME213_LAUNCHED(ctx, "stencil_lines_kernel");
+            return CME213_OK;
+        }
         if (forced > 0 && forced <= g) g = forced;
         if (forced != 0)
 #endif
         {
-            if (g == 4) launch_stencil_lines<T, 4>(nx, ny, nz, first_line, lines, centre, d_x, d_y, st);
-            else if (g == 2) launch_stencil_lines<T, 2>(nx, ny, nz, first_line, lines, centre, d_x, d_y, st);
+            if (g == 2) launch_stencil_lines<T, 2>(nx, ny, nz, first_line, lines, centre, d_x, d_y, st);
             else launch_stencil_lines<T, 1>(nx, ny, nz, first_line, lines, centre, d_x, d_y, st);
             CME213_LAUNCHED(ctx, "stencil_lines_kernel");
             return CME213_OK;
