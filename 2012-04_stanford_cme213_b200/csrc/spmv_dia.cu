@@ -272,8 +272,8 @@ stencil_vec_kernel(int nx, int ny, int nz, int64_t row_begin, int64_t row_end, T
 __device__ __forceinline__ float sub_rn(float a, float b) { return __fsub_rn(a, b); }
 __device__ __forceinline__ double sub_rn(double a, double b) { return __dsub_rn(a, b); }
 
-template <typename T, int G, bool PLANES>
-__global__ void __launch_bounds__(256)
+template <typename T, int G, bool PLANES, int MINB = 0>
+__global__ void __launch_bounds__(256, MINB)
 stencil_lines_kernel(int nx, int ny, int nz, uint32_t first_line, uint32_t num_groups, T centre, const T *__restrict__ x,
                      T *__restrict__ y) {
     constexpr int NP = Vec16<T>::NP;
@@ -356,20 +356,21 @@ stencil_lines_kernel(int nx, int ny, int nz, uint32_t first_line, uint32_t num_g
     }
 }
 
-template <typename T, int G>
-void launch_stencil_lines(int nx, int ny, int nz, int64_t first_line, int64_t lines, T centre, const T *d_x, T *d_y, cudaStream_t st) {
+template <typename T, int G, int MINB = 0>
+void launch_stencil_lines(int nx, int ny, int nz, int64_t first_line, int64_t lines, T centre, const T *d_x, T *d_y, cudaStream_t st,
+                          int cta = 256, int max_tx = 256) {
     constexpr int NP = Vec16<T>::NP;
     const int vecs = nx / NP;
-    const int tx = vecs >= 256 ? 256 : (vecs + 31) / 32 * 32, ty = 256 / tx > 0 ? 256 / tx : 1;
+    const int tx = vecs >= max_tx ? max_tx : (vecs + 31) / 32 * 32, ty = cta / tx > 0 ? cta / tx : 1;
     dim3 block((unsigned)tx, (unsigned)ty);
     const unsigned chunks = (unsigned)div_up(vecs, tx);
     if (first_line % ny == 0 && lines % ny == 0 && lines / ny <= 65535 && chunks <= 65535) {
         dim3 grid((unsigned)div_up(ny / G, ty), chunks, (unsigned)(lines / ny));
-        stencil_lines_kernel<T, G, true><<<grid, block, 0, st>>>(nx, ny, nz, (uint32_t)(first_line / ny), 0u, centre, d_x, d_y);
+        stencil_lines_kernel<T, G, true, MINB><<<grid, block, 0, st>>>(nx, ny, nz, (uint32_t)(first_line / ny), 0u, centre, d_x, d_y);
     } else {
         const int64_t groups = lines / G;
         dim3 grid((unsigned)div_up(groups, ty), chunks);
-        stencil_lines_kernel<T, G, false><<<grid, block, 0, st>>>(nx, ny, nz, (uint32_t)first_line, (uint32_t)groups, centre, d_x, d_y);
+        stencil_lines_kernel<T, G, false, MINB><<<grid, block, 0, st>>>(nx, ny, nz, (uint32_t)first_line, (uint32_t)groups, centre, d_x, d_y);
     }
 }
 
@@ -404,15 +405,19 @@ int stencil_impl(cme213_ctx *ctx, int nx, int ny, int nz, T centre, int64_t row_
         const int64_t first_line = row_begin / nx, lines = rows / nx;
         // 512^3 fp64 (profiles/r02_stencil_kernel_sweep.txt): one-vector kernel 0.467 ms, G = 1 0.423, G = 2 0.412, G = 4 0.435 (98 registers)
         int g = (ny % 2 == 0 && first_line % 2 == 0 && lines % 2 == 0) ? 2 : 1;
-#ifdef CME213_TUNING   // CME213_STENCIL_G = 0 (the one-vector kernel below), 1, 2, 4
-        int forced = -1;
-        if (const char *e = getenv("CME213_STENCIL_G")) forced = atoi(e);
-        if (forced == 4 && ny % 4 == 0 && first_line % 4 == 0 && lines % 4 == 0) {
-            launch_stencil_lines<T, 4>(nx, ny, nz, first_line, lines, centre, d_x, d_y, st);
-            CME213_LAUNCHED(ctx, "stencil_lines_kernel");
-            return CME213_OK;
-        }
-        if (forced > 0 && forced <= g) g = forced;
+#ifdef CME213_TUNING   // CME213_STENCIL_CFG = "g,cta threads,max threads along x,min CTAs per SM"; g = 0: the one-vector kernel below
+        int forced = -1, cta = 256, mtx = 256, minb = 0;
+        if (const char *e = getenv("CME213_STENCIL_CFG")) sscanf(e, "%d,%d,%d,%d", &forced, &cta, &mtx, &minb);
+        const bool ok4 = ny % 4 == 0 && first_line % 4 == 0 && lines % 4 == 0;
+        bool done = true;
+        if (forced == 4 && ok4) launch_stencil_lines<T, 4>(nx, ny, nz, first_line, lines, centre, d_x, d_y, st, cta, mtx);
+        else if (forced == 2 && g == 2 && minb == 5) launch_stencil_lines<T, 2, 5>(nx, ny, nz, first_line, lines, centre, d_x, d_y, st, cta, mtx);
+        else if (forced == 2 && g == 2 && minb == 6) launch_stencil_lines<T, 2, 6>(nx, ny, nz, first_line, lines, centre, d_x, d_y, st, cta, mtx);
+        else if (forced == 2 && g == 2) launch_stencil_lines<T, 2>(nx, ny, nz, first_line, lines, centre, d_x, d_y, st, cta, mtx);
+        else if (forced == 1 && minb == 8) launch_stencil_lines<T, 1, 8>(nx, ny, nz, first_line, lines, centre, d_x, d_y, st, cta, mtx);
+        else if (forced == 1) launch_stencil_lines<T, 1>(nx, ny, nz, first_line, lines, centre, d_x, d_y, st, cta, mtx);
+        else done = false;
+        if (done) { CME213_LAUNCHED(ctx, "stencil_lines_kernel(cfg)"); return CME213_OK; }
         if (forced != 0)
 #endif
         {
