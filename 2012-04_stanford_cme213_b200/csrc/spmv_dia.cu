@@ -403,7 +403,8 @@ int stencil_impl(cme213_ctx *ctx, int nx, int ny, int nz, T centre, int64_t row_
     constexpr int NP = Vec16<T>::NP;
     if (nx % NP == 0 && row_begin % nx == 0 && rows % nx == 0 && aligned16(d_x) && aligned16(d_y)) {
         const int64_t first_line = row_begin / nx, lines = rows / nx;
-        // 512^3 fp64 (profiles/r02_stencil_kernel_sweep.txt): one-vector kernel 0.467 ms, G = 1 0.423, G = 2 0.412, G = 4 0.435 (98 registers)
+        // 512^3 fp64, 256-thread CTAs (profiles/r02_stencil_kernel_sweep.txt): one-vector kernel 0.467 ms, G = 1 0.423, G = 2 0.412,
+        // G = 4 0.435 (98 registers)
         int g = (ny % 2 == 0 && first_line % 2 == 0 && lines % 2 == 0) ? 2 : 1;
 #ifdef CME213_TUNING   // CME213_STENCIL_CFG = "g,cta threads,max threads along x,min CTAs per SM"; g = 0: the one-vector kernel below
         int forced = -1, cta = 256, mtx = 256, minb = 0;
@@ -421,8 +422,10 @@ int stencil_impl(cme213_ctx *ctx, int nx, int ny, int nz, T centre, int64_t row_
         if (forced != 0)
 #endif
         {
-            if (g == 2) launch_stencil_lines<T, 2>(nx, ny, nz, first_line, lines, centre, d_x, d_y, st);
-            else launch_stencil_lines<T, 1>(nx, ny, nz, first_line, lines, centre, d_x, d_y, st);
+            // small CTAs: a slot is refilled as soon as its two warps have stored (G = 2: 256 threads 0.410, 128 0.391, 64 0.380 ms,
+            // 32 0.547 -- 32 CTAs per SM at most; G = 1: 128 threads 0.421, 64 0.547: the CTA launch rate)
+            if (g == 2) launch_stencil_lines<T, 2>(nx, ny, nz, first_line, lines, centre, d_x, d_y, st, 64, 64);
+            else launch_stencil_lines<T, 1>(nx, ny, nz, first_line, lines, centre, d_x, d_y, st, 128, 128);
             CME213_LAUNCHED(ctx, "stencil_lines_kernel");
             return CME213_OK;
         }
