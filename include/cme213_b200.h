@@ -427,7 +427,8 @@ int cme213_csr_to_dia_f64(cme213_ctx *ctx, int64_t num_rows, const int32_t *d_ro
  * centre 6): y[i] = centre * x[i] - sum of the existing grid neighbours of point i, for rows [row_begin, row_end) of
  * the nx * ny * nz grid in natural order (x fastest).  Legs and summation order are those of the CSR rows, so y is
  * bit-identical to the CSR / DIA product; only x and y move (16 / 8 bytes per row): the upper bound for C1 / C5.
- * d_x and d_y are full-length vectors and must not alias.
+ * d_x and d_y are full-length vectors and must not alias.  Fastest when the range is whole grid lines (row_begin and
+ * row_end multiples of nx), nx a multiple of 4 (fp32) / 2 (fp64) and the vectors 16-byte aligned; any range works.
  * reference: hw/hw2/programming/2dHeat.cu:361-366 (stencil2) and :431-461 (gpuGlobal). */
 int cme213_stencil_laplace_f32(cme213_ctx *ctx, int nx, int ny, int nz, float centre, int64_t row_begin,
                                int64_t row_end, const float *d_x, float *d_y, void *stream);
