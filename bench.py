@@ -1116,6 +1116,7 @@ def main():
     ap.add_argument("--exchange", default="flags", choices=["flags", "gather", "split", "fused", "p2p", "halo", "full"],
                     help="N>1: flags (default) = the C ABI's sharded iterate: ONE launch per pass, the kernel stores the halo rows into the neighbours' vectors and the passes are ordered by flags in peer memory (no NCCL on the data path); gather / split = its whole-vector modes for general matrices.  The others are the round-1 torch.distributed paths, kept as fallbacks: fused = the boundary launch stores the halo planes into the neighbours' vectors over peer memory (falls back to p2p when CUDA IPC or the shape does not allow it); p2p = NCCL send/recv of the halo planes between neighbours; halo = one all-gather of every rank's boundary planes; full = all-gather of the whole vector")
     ap.add_argument("--csr-kernel", type=int, default=0)
+    ap.add_argument("--l2-fetch-gran", type=int, default=0, help="experiment: set the device's maximum L2 fetch granularity (bytes) before the run")
     ap.add_argument("--l2-persist-mb", type=int, default=-1, help="experiment: set the device's persisting-L2 set-aside (MB) before the run")
     ap.add_argument("--graph", type=int, default=0, help="N>1: 1 = replay CUDA graphs of the passes instead of calling cme213_shard_step per pass (measured 0.4 %% slower at 8 GPUs); the NCCL fallback modes always use a graph of two passes")
     ap.add_argument("--order-strip", type=int, default=0, help="C5: CTA order = z fastest inside strips of this many grid lines (0 = row order)")
@@ -1156,6 +1157,14 @@ def main():
         got = ctypes.c_size_t()
         cu.cuCtxGetLimit(ctypes.byref(got), 6)
         log("l2 persisting set-aside: rc", rc, "now", got.value >> 20, "MB")
+    if args.l2_fetch_gran > 0:    # experiment: CU_LIMIT_MAX_L2_FETCH_GRANULARITY (32 / 64 / 128 bytes)
+        import ctypes
+        torch.zeros(1, device="cuda")
+        cu = ctypes.CDLL("libcuda.so.1")
+        rc = cu.cuCtxSetLimit(5, ctypes.c_size_t(args.l2_fetch_gran))
+        got = ctypes.c_size_t()
+        cu.cuCtxGetLimit(ctypes.byref(got), 5)
+        log("l2 max fetch granularity: rc", rc, "now", got.value, "bytes")
     peak, peak_kind = measured_peak()
 
     wl = build_workload(args.workload, ctx, torch, args, rank, world, dist)
