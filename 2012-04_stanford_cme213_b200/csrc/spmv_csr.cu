@@ -84,38 +84,6 @@ __device__ __forceinline__ T product_keep(const Args<T> &a, T v, int c, uint64_t
     if (MODE == MODE_PAGERANK) return mul_rn(ld_keep(a.x + c, pol), ld_keep(a.inv + c, pol));
     return ld_keep(a.x + c, pol);
 }
-#ifdef CME213_TUNING
-// gathers / streams with an L2 prefetch-size hint (tuning builds: does a sector miss that drags its whole line in save DRAM bursts?)
-template <int BYTES> __device__ __forceinline__ double ld_pf(const double *p) {
-    double v;
-    if constexpr (BYTES == 128) asm volatile("ld.global.nc.L2::128B.f64 %0, [%1];" : "=d"(v) : "l"(p));
-    else if constexpr (BYTES == 256) asm volatile("ld.global.nc.L2::256B.f64 %0, [%1];" : "=d"(v) : "l"(p));
-    else asm volatile("ld.global.nc.L2::64B.f64 %0, [%1];" : "=d"(v) : "l"(p));
-    return v;
-}
-template <int BYTES> __device__ __forceinline__ float ld_pf(const float *p) {
-    float v;
-    if constexpr (BYTES == 128) asm volatile("ld.global.nc.L2::128B.f32 %0, [%1];" : "=f"(v) : "l"(p));
-    else if constexpr (BYTES == 256) asm volatile("ld.global.nc.L2::256B.f32 %0, [%1];" : "=f"(v) : "l"(p));
-    else asm volatile("ld.global.nc.L2::64B.f32 %0, [%1];" : "=f"(v) : "l"(p));
-    return v;
-}
-__device__ __forceinline__ int4 ld_stream_pf(const int4 *p) {
-    int4 v;
-    asm volatile("ld.global.nc.L1::no_allocate.L2::256B.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
-    return v;
-}
-__device__ __forceinline__ double2 ld_stream_pf(const double2 *p) {
-    double2 v;
-    asm volatile("ld.global.nc.L1::no_allocate.L2::256B.v2.f64 {%0,%1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p));
-    return v;
-}
-__device__ __forceinline__ float4 ld_stream_pf(const float4 *p) {
-    float4 v;
-    asm volatile("ld.global.nc.L1::no_allocate.L2::256B.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
-    return v;
-}
-#endif
 template <typename T, int MODE>
 __device__ __forceinline__ void epilogue(const Args<T> &a, int64_t r, T sum) {
     if (is_csr(MODE)) {
@@ -172,12 +140,6 @@ template <> struct V4<float> {
         float4 t = ld_stream(reinterpret_cast<const float4 *>(p));
         return V4{{t.x, t.y, t.z, t.w}};
     }
-#ifdef CME213_TUNING
-    __device__ static V4 load_pf(const float *p) {
-        float4 t = ld_stream_pf(reinterpret_cast<const float4 *>(p));
-        return V4{{t.x, t.y, t.z, t.w}};
-    }
-#endif
     __device__ static V4 load_first(const float *p, uint64_t pol) {
         float4 t = ld_first(reinterpret_cast<const float4 *>(p), pol);
         return V4{{t.x, t.y, t.z, t.w}};
@@ -190,13 +152,6 @@ template <> struct V4<double> {
         double2 t1 = ld_stream(reinterpret_cast<const double2 *>(p) + 1);
         return V4{{t0.x, t0.y, t1.x, t1.y}};
     }
-#ifdef CME213_TUNING
-    __device__ static V4 load_pf(const double *p) {
-        double2 t0 = ld_stream_pf(reinterpret_cast<const double2 *>(p));
-        double2 t1 = ld_stream_pf(reinterpret_cast<const double2 *>(p) + 1);
-        return V4{{t0.x, t0.y, t1.x, t1.y}};
-    }
-#endif
     __device__ static V4 load_first(const double *p, uint64_t pol) {
         double2 t0 = ld_first(reinterpret_cast<const double2 *>(p), pol);
         double2 t1 = ld_first(reinterpret_cast<const double2 *>(p) + 1, pol);
@@ -278,7 +233,7 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename s
     const int b0 = __ldg(a.row_ptr + r0), b1 = __ldg(a.row_ptr + rl);  // this CTA's nonzero range
     T sum = T(0);
     if (MODE == MODE_CSR_ACC && re > rs) sum = a.y[r];
-    [[maybe_unused]] const uint64_t keep = (KEEP == 1 || KEEP == 2) ? l2_policy_evict_last() : 0;
+    [[maybe_unused]] const uint64_t keep = KEEP ? l2_policy_evict_last() : 0;
     [[maybe_unused]] const uint64_t first = KEEP == 2 ? l2_policy_evict_first() : 0;
     for (int base = b0 & ~3; base < b1; base += TILE) {
 #pragma unroll
@@ -291,31 +246,15 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename s
                 if constexpr (KEEP == 2) {
                     c = ld_first(reinterpret_cast<const int4 *>(a.col + j), first);
                     w = V4<T>::load_first(a.val + j, first);
-#ifdef CME213_TUNING
-                } else if constexpr (KEEP == 5 || KEEP == 6) {   // streams with a 256-byte L2 prefetch hint
-                    c = ld_stream_pf(reinterpret_cast<const int4 *>(a.col + j));
-                    w = V4<T>::load_pf(a.val + j);
-#endif
                 } else {
                     c = ld_stream(reinterpret_cast<const int4 *>(a.col + j));
                     if (is_csr(MODE)) w = V4<T>::load(a.val + j);
                     else w = V4<T>{{T(0), T(0), T(0), T(0)}};
                 }
                 T p0, p1, p2, p3;
-                if constexpr (KEEP == 1 || KEEP == 2) {   // x entries marked evict-last in L2: for vectors that fit L2 but are gathered at random
+                if constexpr (KEEP != 0) {   // x entries marked evict-last in L2: for vectors that fit L2 but are gathered at random
                     p0 = product_keep<T, MODE>(a, w.v[0], c.x, keep); p1 = product_keep<T, MODE>(a, w.v[1], c.y, keep);
                     p2 = product_keep<T, MODE>(a, w.v[2], c.z, keep); p3 = product_keep<T, MODE>(a, w.v[3], c.w, keep);
-#ifdef CME213_TUNING
-                } else if constexpr (KEEP >= 3) {          // 3 / 6: x gathers with a 128-byte L2 prefetch hint, 4: 256, 5: plain gathers
-                    constexpr int PF = KEEP == 4 ? 256 : 128;
-                    if constexpr (KEEP == 5) {
-                        p0 = product<T, MODE>(a, w.v[0], c.x); p1 = product<T, MODE>(a, w.v[1], c.y);
-                        p2 = product<T, MODE>(a, w.v[2], c.z); p3 = product<T, MODE>(a, w.v[3], c.w);
-                    } else {
-                        p0 = mul_rn(w.v[0], ld_pf<PF>(a.x + c.x)); p1 = mul_rn(w.v[1], ld_pf<PF>(a.x + c.y));
-                        p2 = mul_rn(w.v[2], ld_pf<PF>(a.x + c.z)); p3 = mul_rn(w.v[3], ld_pf<PF>(a.x + c.w));
-                    }
-#endif
                 } else {
                     p0 = product<T, MODE>(a, w.v[0], c.x); p1 = product<T, MODE>(a, w.v[1], c.y);
                     p2 = product<T, MODE>(a, w.v[2], c.z); p3 = product<T, MODE>(a, w.v[3], c.w);
@@ -666,11 +605,6 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
                 if (T_ == TH && L_ == TL) { \
                     const int64_t nb = div_up(rows, TH); \
                     if (K_ == 2) { if constexpr (MODE == MODE_CSR) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, 2><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); } \
-                    else if (K_ >= 3 && K_ <= 6 && TH == 128 && TL == 1024) { if constexpr (MODE == MODE_CSR && TH == 128 && TL == 1024) { \
-                        if (K_ == 3) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, 3><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); \
-                        if (K_ == 4) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, 4><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); \
-                        if (K_ == 5) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, 5><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); \
-                        if (K_ == 6) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, 6><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); } } \
                     else if (K_) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, 1><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); \
                     else csr_stream_lean_kernel<T, MODE, TH, TL, false><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); \
                     CME213_LAUNCHED(ctx, "csr_stream_lean_kernel(cfg)"); \
