@@ -295,6 +295,71 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename s
     }
 }
 
+// The stream kernel with the CTA's col / val range brought in by the bulk-copy engine (cp.async.bulk, the 1-D mode of TMA)
+// instead of through registers.  The lean kernel above is bound by its chain of dependent memory round trips, not by DRAM
+// (profiles/r02_notes.md: with in-order gathers it runs at the copy peak, with the stencil's gathers at 0.855): row pointers ->
+// col / val, first half -> gathers -> col / val, second half -> gathers -> sums, 32 registers leaving room for one 4-entry
+// vector in flight per thread.  Here thread 0 asks for the whole range at once, nothing of it waits in registers, and every
+// thread then has all its gathers in flight together: row pointers -> col / val -> gathers -> sums.
+// Products overwrite the values in place; the sums run over them in row order as everywhere else (bit-identical to the CPU loop).
+template <typename T, int THREADS, int TILE>
+__global__ void __launch_bounds__(THREADS, 2048 / THREADS)
+csr_stream_bulk_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
+    static_assert(TILE % 4 == 0, "whole 16-byte groups");
+    __shared__ __align__(16) T s_val[TILE];
+    __shared__ __align__(16) int s_col[TILE];
+    __shared__ __align__(8) uint64_t bar;
+    const int tid = threadIdx.x;
+    const int64_t r0 = row_begin + (int64_t)blockIdx.x * THREADS;
+    const int64_t rl = r0 + THREADS < row_end ? r0 + THREADS : row_end;
+    const int64_t r = r0 + tid;
+    int rs = 0, re = 0;
+    if (r < row_end) { rs = __ldg(a.row_ptr + r); re = __ldg(a.row_ptr + r + 1); }
+    const int b0 = __ldg(a.row_ptr + r0), b1 = __ldg(a.row_ptr + rl);
+    if (tid == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
+    __syncthreads();
+    unsigned phase = 0;
+    T sum = T(0);
+    for (int base = b0 & ~3; base < b1; base += TILE) {            // one pass unless the CTA's rows hold more than TILE entries
+        const int end = base + TILE < b1 ? base + TILE : b1;
+        const int bulk_end = end == b1 ? (b1 & ~3) : end;           // whole 16-byte groups go by bulk copy ...
+        const int nb = bulk_end - base, n = end - base;
+        if (tid == 0 && nb > 0) {
+            mbar_expect_tx(&bar, (unsigned)nb * (unsigned)(sizeof(int) + sizeof(T)));
+            bulk_load(s_col, a.col + base, (unsigned)nb * (unsigned)sizeof(int), &bar);
+            bulk_load(s_val, a.val + base, (unsigned)nb * (unsigned)sizeof(T), &bar);
+        }
+        if (tid < n - nb) {                                          // ... the last one to three entries of the range by hand
+            s_col[nb + tid] = __ldg(a.col + bulk_end + tid);
+            s_val[nb + tid] = __ldg(a.val + bulk_end + tid);
+        }
+        if (nb > 0) { mbar_wait(&bar, phase); phase ^= 1u; }
+        __syncthreads();
+#pragma unroll 2
+        for (int o = tid * 4; o < n; o += THREADS * 4) {
+            if (o + 4 <= n) {
+                const int4 c = *reinterpret_cast<const int4 *>(s_col + o);
+                T v[4];
+#pragma unroll
+                for (int t = 0; t < 4; ++t) v[t] = s_val[o + t];
+                const T x0 = __ldg(a.x + c.x), x1 = __ldg(a.x + c.y), x2 = __ldg(a.x + c.z), x3 = __ldg(a.x + c.w);
+                s_val[o + 0] = mul_rn(v[0], x0); s_val[o + 1] = mul_rn(v[1], x1);
+                s_val[o + 2] = mul_rn(v[2], x2); s_val[o + 3] = mul_rn(v[3], x3);
+            } else {
+                for (int t = 0; o + t < n; ++t) s_val[o + t] = mul_rn(s_val[o + t], __ldg(a.x + s_col[o + t]));
+            }
+        }
+        __syncthreads();
+        const int lo = rs > base ? rs : base, hi = re < end ? re : end;
+        for (int j = lo; j < hi; ++j) sum = add_rn(sum, s_val[j - base]);
+        if (end < b1) {                 // another pass: the buffers are read by the generic proxy, then written by the async one
+            __syncthreads();
+            if (tid == 0) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        }
+    }
+    if (r < row_end) st_stream(a.y + r, sum);
+}
+
 template <typename T, int MODE, int THREADS, int RPT, int TILE, bool PADDED, bool ORDERED = true, bool KEEP = true>
 __global__ void __launch_bounds__(THREADS)
 csr_stream_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
@@ -604,7 +669,8 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
 #define CME213_TRY_CSR(TH, TL) \
                 if (T_ == TH && L_ == TL) { \
                     const int64_t nb = div_up(rows, TH); \
-                    if (K_ == 2) { if constexpr (MODE == MODE_CSR) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, 2><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); } \
+                    if (K_ == 7) { if constexpr (MODE == MODE_CSR && TL * (sizeof(T) + 4) + 64 <= 48 * 1024) csr_stream_bulk_kernel<T, TH, TL><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end); } \
+                    else if (K_ == 2) { if constexpr (MODE == MODE_CSR) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, 2><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); } \
                     else if (K_) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, 1><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); \
                     else csr_stream_lean_kernel<T, MODE, TH, TL, false><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); \
                     CME213_LAUNCHED(ctx, "csr_stream_lean_kernel(cfg)"); \
