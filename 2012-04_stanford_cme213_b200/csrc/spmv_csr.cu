@@ -302,8 +302,8 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename s
 // vector in flight per thread.  Here thread 0 asks for the whole range at once, nothing of it waits in registers, and every
 // thread then has all its gathers in flight together: row pointers -> col / val -> gathers -> sums.
 // Products overwrite the values in place; the sums run over them in row order as everywhere else (bit-identical to the CPU loop).
-template <typename T, int THREADS, int TILE>
-__global__ void __launch_bounds__(THREADS, 2048 / THREADS)
+template <typename T, int THREADS, int TILE, int RESIDENT = 2048>
+__global__ void __launch_bounds__(THREADS, RESIDENT / THREADS)
 csr_stream_bulk_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
     static_assert(TILE % 4 == 0, "whole 16-byte groups");
     __shared__ __align__(16) T s_val[TILE];
@@ -335,6 +335,20 @@ csr_stream_bulk_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
         }
         if (nb > 0) { mbar_wait(&bar, phase); phase ^= 1u; }
         __syncthreads();
+        if constexpr (TILE == 8 * THREADS) {
+            // the usual case, two whole groups per thread: all eight gathers in flight before the first product
+            const int o1 = tid * 4, o2 = o1 + THREADS * 4;
+            if (o2 + 4 <= n) {
+                const int4 c1 = *reinterpret_cast<const int4 *>(s_col + o1), c2 = *reinterpret_cast<const int4 *>(s_col + o2);
+                const T x0 = __ldg(a.x + c1.x), x1 = __ldg(a.x + c1.y), x2 = __ldg(a.x + c1.z), x3 = __ldg(a.x + c1.w);
+                const T x4 = __ldg(a.x + c2.x), x5 = __ldg(a.x + c2.y), x6 = __ldg(a.x + c2.z), x7 = __ldg(a.x + c2.w);
+                s_val[o1 + 0] = mul_rn(s_val[o1 + 0], x0); s_val[o1 + 1] = mul_rn(s_val[o1 + 1], x1);
+                s_val[o1 + 2] = mul_rn(s_val[o1 + 2], x2); s_val[o1 + 3] = mul_rn(s_val[o1 + 3], x3);
+                s_val[o2 + 0] = mul_rn(s_val[o2 + 0], x4); s_val[o2 + 1] = mul_rn(s_val[o2 + 1], x5);
+                s_val[o2 + 2] = mul_rn(s_val[o2 + 2], x6); s_val[o2 + 3] = mul_rn(s_val[o2 + 3], x7);
+                goto products_done;
+            }
+        }
 #pragma unroll 2
         for (int o = tid * 4; o < n; o += THREADS * 4) {
             if (o + 4 <= n) {
@@ -349,6 +363,7 @@ csr_stream_bulk_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
                 for (int t = 0; o + t < n; ++t) s_val[o + t] = mul_rn(s_val[o + t], __ldg(a.x + s_col[o + t]));
             }
         }
+    products_done:
         __syncthreads();
         const int lo = rs > base ? rs : base, hi = re < end ? re : end;
         for (int j = lo; j < hi; ++j) sum = add_rn(sum, s_val[j - base]);
@@ -670,6 +685,7 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
                 if (T_ == TH && L_ == TL) { \
                     const int64_t nb = div_up(rows, TH); \
                     if (K_ == 7) { if constexpr (MODE == MODE_CSR && TL * (sizeof(T) + 4) + 64 <= 48 * 1024) csr_stream_bulk_kernel<T, TH, TL><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end); } \
+                    else if (K_ == 8) { if constexpr (MODE == MODE_CSR && TL == 8 * TH && TH <= 256) csr_stream_bulk_kernel<T, TH, TL, 1536><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end); } \
                     else if (K_ == 2) { if constexpr (MODE == MODE_CSR) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, 2><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); } \
                     else if (K_) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, 1><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); \
                     else csr_stream_lean_kernel<T, MODE, TH, TL, false><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); \

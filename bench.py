@@ -278,9 +278,9 @@ def make_c5(ctx, torch, args, rank, world, dist):
 
 def make_c1(ctx, torch, args):
     import ctypes as C
-    n = 1024
+    n = args.c1_n
     rows = n * n
-    copies = 8  # 8 x 54 MB > 126 MB L2: rotate so every step streams from HBM
+    copies = 8 if n >= 1024 else min(64, 8 * (1024 // n) ** 2)  # 8 x 54 MB > 126 MB L2: rotate so every step streams from HBM
     mats = []
     nnz = C.c_int64()
     for _ in range(copies):
@@ -321,7 +321,7 @@ def make_c1(ctx, torch, args):
     del cgraph, bufs
     return dict(step=graph.replay, alg_bytes=alg * copies, flops=2 * nnz.value * copies, kernel="csr_stream_lean_kernel<float>",
                 launches_per_step=copies,
-                meta={"workload": "C1: CSR SpMV fp32, 2-D 5-point Poisson 1024x1024", "rows": rows, "nnz": nnz.value,
+                meta={"workload": "C1: CSR SpMV fp32, 2-D 5-point Poisson %dx%d" % (n, n), "rows": rows, "nnz": nnz.value,
                       "passes_per_step": copies, "device_copy_of_the_same_bytes_ms_per_launch": copy_ms,
                       "l2": "one step = CUDA graph of %d passes over %d independent copies (%.0f MB total): every pass is cold in L2" % (copies, copies, copies * alg / 1e6)},
                 keep=(mats, graph))
@@ -1116,6 +1116,7 @@ def main():
     ap.add_argument("--exchange", default="flags", choices=["flags", "gather", "split", "fused", "p2p", "halo", "full"],
                     help="N>1: flags (default) = the C ABI's sharded iterate: ONE launch per pass, the kernel stores the halo rows into the neighbours' vectors and the passes are ordered by flags in peer memory (no NCCL on the data path); gather / split = its whole-vector modes for general matrices.  The others are the round-1 torch.distributed paths, kept as fallbacks: fused = the boundary launch stores the halo planes into the neighbours' vectors over peer memory (falls back to p2p when CUDA IPC or the shape does not allow it); p2p = NCCL send/recv of the halo planes between neighbours; halo = one all-gather of every rank's boundary planes; full = all-gather of the whole vector")
     ap.add_argument("--csr-kernel", type=int, default=0)
+    ap.add_argument("--c1-n", type=int, default=1024, help="C1: grid edge (1024 = the configuration of BASELINE.json)")
     ap.add_argument("--l2-fetch-gran", type=int, default=0, help="experiment: set the device's maximum L2 fetch granularity (bytes) before the run")
     ap.add_argument("--l2-persist-mb", type=int, default=-1, help="experiment: set the device's persisting-L2 set-aside (MB) before the run")
     ap.add_argument("--graph", type=int, default=0, help="N>1: 1 = replay CUDA graphs of the passes instead of calling cme213_shard_step per pass (measured 0.4 %% slower at 8 GPUs); the NCCL fallback modes always use a graph of two passes")
