@@ -302,8 +302,8 @@ csr_stream_lean_kernel(Args<T> a, int64_t row_begin, int64_t row_end, typename s
 // vector in flight per thread.  Here thread 0 asks for the whole range at once, nothing of it waits in registers, and every
 // thread then has all its gathers in flight together: row pointers -> col / val -> gathers -> sums.
 // Products overwrite the values in place; the sums run over them in row order as everywhere else (bit-identical to the CPU loop).
-template <typename T, int THREADS, int TILE, int RESIDENT = 2048>
-__global__ void __launch_bounds__(THREADS, RESIDENT / THREADS)
+template <typename T, int THREADS, int TILE>
+__global__ void __launch_bounds__(THREADS, 2048 / THREADS)
 csr_stream_bulk_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
     static_assert(TILE % 4 == 0, "whole 16-byte groups");
     __shared__ __align__(16) T s_val[TILE];
@@ -335,20 +335,6 @@ csr_stream_bulk_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
         }
         if (nb > 0) { mbar_wait(&bar, phase); phase ^= 1u; }
         __syncthreads();
-        if constexpr (TILE == 8 * THREADS) {
-            // the usual case, two whole groups per thread: all eight gathers in flight before the first product
-            const int o1 = tid * 4, o2 = o1 + THREADS * 4;
-            if (o2 + 4 <= n) {
-                const int4 c1 = *reinterpret_cast<const int4 *>(s_col + o1), c2 = *reinterpret_cast<const int4 *>(s_col + o2);
-                const T x0 = __ldg(a.x + c1.x), x1 = __ldg(a.x + c1.y), x2 = __ldg(a.x + c1.z), x3 = __ldg(a.x + c1.w);
-                const T x4 = __ldg(a.x + c2.x), x5 = __ldg(a.x + c2.y), x6 = __ldg(a.x + c2.z), x7 = __ldg(a.x + c2.w);
-                s_val[o1 + 0] = mul_rn(s_val[o1 + 0], x0); s_val[o1 + 1] = mul_rn(s_val[o1 + 1], x1);
-                s_val[o1 + 2] = mul_rn(s_val[o1 + 2], x2); s_val[o1 + 3] = mul_rn(s_val[o1 + 3], x3);
-                s_val[o2 + 0] = mul_rn(s_val[o2 + 0], x4); s_val[o2 + 1] = mul_rn(s_val[o2 + 1], x5);
-                s_val[o2 + 2] = mul_rn(s_val[o2 + 2], x6); s_val[o2 + 3] = mul_rn(s_val[o2 + 3], x7);
-                goto products_done;
-            }
-        }
 #pragma unroll 2
         for (int o = tid * 4; o < n; o += THREADS * 4) {
             if (o + 4 <= n) {
@@ -363,7 +349,6 @@ csr_stream_bulk_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
                 for (int t = 0; o + t < n; ++t) s_val[o + t] = mul_rn(s_val[o + t], __ldg(a.x + s_col[o + t]));
             }
         }
-    products_done:
         __syncthreads();
         const int lo = rs > base ? rs : base, hi = re < end ? re : end;
         for (int j = lo; j < hi; ++j) sum = add_rn(sum, s_val[j - base]);
@@ -476,6 +461,7 @@ struct cme213_csr_plan {
 
 namespace {
 constexpr int PLAN_BLOCK_ROWS = 256;       // = cme213_spmv_csr_block_rows()
+constexpr double PLAN_BULK_MEAN = 8.0;     // 128 rows of the bulk kernel's block fill its 1024-entry buffers in one pass
 // Thresholds read from profiles/r02_csr_kernel_sweep.csv (134 M nonzeros per matrix, uniform and banded columns):
 //   rows of 1-2 entries: one thread per row is already coalesced enough and skips the shared-memory round trip (scalar 0.59 ms
 //     vs stream 0.66 on 2 per row);
@@ -601,7 +587,10 @@ int plan_build(cme213_ctx *ctx, cme213_csr_plan *p, const int32_t *d_row_ptr, cu
             p->d_short = p->d_long = nullptr;
         }
     }
-    const char *names[] = {"auto", "scalar", "vector", "stream", "stream-padded", "stream-keep", "binned", "(unused)", "auto-ordered"};
+    // fp32, short rows: the bulk-copy-fed stream kernel (2-D 5-point grids 512^2 ... 4096^2: 1.12-1.24x the register-fed one;
+    // profiles/r02_exp_csr_bulk.txt).  fp64 (C5: 2.61 against 2.52 ms) and longer rows (more than one pass per block) stay.
+    if (p->kernel == CME213_CSR_STREAM && p->elem_bytes == 4 && p->mean <= PLAN_BULK_MEAN) p->kernel = CME213_CSR_STREAM_BULK;
+    const char *names[] = {"auto", "scalar", "vector", "stream", "stream-padded", "stream-keep", "binned", "stream-bulk", "auto-ordered"};
     const int kind = p->kernel & 0xFF;
     char lanes[24] = "";
     if (kind == CME213_CSR_VECTOR) snprintf(lanes, sizeof(lanes), " (%d lanes)", (p->kernel >> 8) & 0xFF);
@@ -641,7 +630,8 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
     const int lanes = (kernel >> 8) & 0xFF;
     const bool padded = kind == CME213_CSR_STREAM_PADDED;
     const bool keep = kind == CME213_CSR_STREAM_KEEP;
-    if (padded || keep) kind = CME213_CSR_STREAM;
+    const bool bulk = kind == CME213_CSR_STREAM_BULK;
+    if (padded || keep || bulk) kind = CME213_CSR_STREAM;
     const bool vec_ok = aligned16(a.col) && (MODE != MODE_CSR || aligned16(a.val));
     if (kind == CME213_CSR_AUTO || kind == CME213_CSR_AUTO_ORDERED) kind = CME213_CSR_STREAM;   // (CSR products resolve AUTO through a plan before they get here)
     if (kind == CME213_CSR_STREAM && !vec_ok) kind = CME213_CSR_SCALAR;
@@ -685,7 +675,6 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
                 if (T_ == TH && L_ == TL) { \
                     const int64_t nb = div_up(rows, TH); \
                     if (K_ == 7) { if constexpr (MODE == MODE_CSR && TL * (sizeof(T) + 4) + 64 <= 48 * 1024) csr_stream_bulk_kernel<T, TH, TL><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end); } \
-                    else if (K_ == 8) { if constexpr (MODE == MODE_CSR && TL == 8 * TH && TH <= 256) csr_stream_bulk_kernel<T, TH, TL, 1536><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end); } \
                     else if (K_ == 2) { if constexpr (MODE == MODE_CSR) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, 2><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); } \
                     else if (K_) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, 1><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); \
                     else csr_stream_lean_kernel<T, MODE, TH, TL, false><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); \
@@ -698,6 +687,13 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
 #undef CME213_TRY_CSR
             }
 #endif
+            if constexpr (MODE == MODE_CSR) {
+                if (bulk) {
+                    csr_stream_bulk_kernel<T, 128, 1024><<<(unsigned)div_up(rows, 128), 128, 0, st>>>(a, row_begin, row_end);
+                    CME213_LAUNCHED(ctx, "csr_stream_bulk_kernel");
+                    return CME213_OK;
+                }
+            }
             const int64_t blocks = div_up(rows, THREADS);
             if (padded) csr_stream_lean_kernel<T, MODE, THREADS, TILE, true><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end, NoSync());
             else if (keep) csr_stream_lean_kernel<T, MODE, THREADS, TILE, false, false, 1><<<(unsigned)blocks, THREADS, 0, st>>>(a, row_begin, row_end, NoSync());

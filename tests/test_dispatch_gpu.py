@@ -58,9 +58,10 @@ def test_plan_picks_by_row_length_and_every_choice_matches_the_cpu_loop(ctx, cme
     eb = np.dtype(dtype).itemsize
     cases = []
     ptr, col, val = g.laplace2d(200, 150, dtype)                                 # short irregular rows
-    cases.append(("laplace", ptr, col, val, 200 * 150, (STREAM,)))
+    BULK = 7                                                                     # fp32 rows of 8 or fewer: bulk-copy-fed stream kernel
+    cases.append(("laplace", ptr, col, val, 200 * 150, (BULK,) if eb == 4 else (STREAM,)))
     cases.append(("regular16",) + regular_csr(20000, 30000, 16, 1, dtype) + (30000, (PADDED,)))
-    cases.append(("regular7",) + regular_csr(20000, 30000, 7, 2, dtype) + (30000, (STREAM,)))
+    cases.append(("regular7",) + regular_csr(20000, 30000, 7, 2, dtype) + (30000, (BULK,) if eb == 4 else (STREAM,)))
     cases.append(("regular64",) + regular_csr(6000, 50000, 64, 3, dtype) + (50000, (PADDED,)))
     cases.append(("short2",) + regular_csr(50000, 50000, 2, 6, dtype) + (50000, (SCALAR,)))
     cases.append(("long300",) + regular_csr(1500, 50000, 300, 4, dtype) + (50000, (VECTOR,)))
@@ -91,7 +92,7 @@ def test_ordered_plans_stay_bit_identical_on_long_rows(ctx, cme):
     x = np.random.default_rng(1).uniform(-1, 1, 50000).astype(np.float32)
     want = oracle.csr_spmv(ptr, col, val, x)
     plan, d_ptr = make_plan(ctx, cme, ptr, 50000, 4 | cme.capi.PLAN_ORDERED)
-    assert lib.cme213_csr_plan_kernel(plan) & 0xFF in (SCALAR, STREAM, PADDED), lib.cme213_csr_plan_describe(plan)
+    assert lib.cme213_csr_plan_kernel(plan) & 0xFF in (SCALAR, STREAM, PADDED, 7), lib.cme213_csr_plan_describe(plan)
     assert np.array_equal(run_plan(ctx, cme, plan, d_ptr, col, val, x), want)
     lib.cme213_csr_plan_destroy(plan)
     d_y = dev(np.zeros(1500, np.float32))

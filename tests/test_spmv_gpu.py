@@ -31,7 +31,7 @@ def check_tol(got, ptr, col, val, x, extra=1):
 
 
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
-@pytest.mark.parametrize("kernel", [SCALAR, STREAM, AUTO])
+@pytest.mark.parametrize("kernel", [SCALAR, STREAM, AUTO, 7])
 def test_csr_sequential_kernels_bit_exact_on_laplacian(ctx, dtype, kernel):
     # config C1 in miniature: 5-point Laplacian, natural order
     ptr, col, val = g.laplace2d(67, 45, dtype)
@@ -48,6 +48,7 @@ def test_csr_kernels_on_random_matrices(ctx, dtype, rows, cols, mean):
     assert np.array_equal(gpu_csr(ctx, ptr, col, val, x, SCALAR), want)
     assert np.array_equal(gpu_csr(ctx, ptr, col, val, x, STREAM), want)
     assert np.array_equal(gpu_csr(ctx, ptr, col, val, x, 4), want)   # CME213_CSR_STREAM_PADDED
+    assert np.array_equal(gpu_csr(ctx, ptr, col, val, x, 7), want)   # CME213_CSR_STREAM_BULK (mean 40: several passes per block)
     assert np.array_equal(gpu_csr(ctx, ptr, col, val, x, AUTO), want)
     for lanes in (2, 4, 8, 16, 32):
         check_tol(gpu_csr(ctx, ptr, col, val, x, VECTOR | (lanes << 8)), ptr, col, val, x)
