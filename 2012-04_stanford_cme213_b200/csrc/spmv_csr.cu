@@ -20,6 +20,7 @@
 // code is built without FMA (x86-64 baseline), and its 10-ULP check (pagerank.cu:216-239) then
 // holds with zero slack.
 #include "internal.cuh"
+#include <algorithm>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -360,6 +361,117 @@ csr_stream_bulk_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
     if (r < row_end) st_stream(a.y + r, sum);
 }
 
+// The bulk-copy-fed kernel as a pipeline: a persistent CTA walks its row blocks (block b, b + grid, b + 2 grid ...: the resident
+// CTAs always cover one contiguous window of rows) with STAGES buffers, the bulk copies of block i + STAGES - 1 in flight while
+// block i gathers.  Only for matrices whose 128-row blocks fit one buffer (longest row <= TILE / THREADS: the dispatcher checks).
+__device__ __forceinline__ void mbar_wait_bounded(uint64_t *bar, unsigned parity) {
+#pragma unroll 1
+    for (int spin = 0; spin < (1 << 26); ++spin) {
+        unsigned ok;
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+                     : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+        if (ok) return;
+    }
+    __trap();   // a copy that never lands is a bug, not something to wait for
+}
+template <typename T, int THREADS, int TILE, int STAGES>
+__global__ void __launch_bounds__(THREADS, 1024 / THREADS)   // shared memory allows 8 CTAs of 128 threads (two stages): 64 registers each
+csr_stream_pipe_kernel(Args<T> a, int64_t row_begin, int64_t row_end, int64_t nblk) {
+    extern __shared__ __align__(16) unsigned char pipe_smem[];
+    T *s_val = reinterpret_cast<T *>(pipe_smem);                          // [STAGES][TILE] values, then products in place
+    int *s_col = reinterpret_cast<int *>(s_val + STAGES * TILE);          // [STAGES][TILE]
+    uint64_t *bar = reinterpret_cast<uint64_t *>(s_col + STAGES * TILE);  // [STAGES]
+    const int tid = threadIdx.x;
+    const int64_t G = gridDim.x;
+    const int limit4 = __ldg(a.row_ptr + row_end) & ~3;                   // bulk copies stay inside the arrays
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) mbar_init(&bar[s], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    // thread 0: start the copies of row block `blk` into stage `st` (whole 16-byte groups, from the group that holds the
+    // block's first entry to the one that holds its last; the neighbours' entries in those groups are harmless)
+    auto issue = [&](int64_t blk, int st) {
+        const int64_t r0 = row_begin + blk * THREADS, rl = r0 + THREADS < row_end ? r0 + THREADS : row_end;
+        const int b0 = __ldg(a.row_ptr + r0), b1 = __ldg(a.row_ptr + rl);
+        const int base = b0 & ~3;
+        int end4 = (b1 + 3) & ~3;
+        if (end4 > limit4) end4 = limit4;
+        const int nb = end4 - base;
+        if (nb > 0 && nb <= TILE) {
+            mbar_expect_tx(&bar[st], (unsigned)nb * (unsigned)(sizeof(int) + sizeof(T)));
+            bulk_load(s_col + st * TILE, a.col + base, (unsigned)nb * (unsigned)sizeof(int), &bar[st]);
+            bulk_load(s_val + st * TILE, a.val + base, (unsigned)nb * (unsigned)sizeof(T), &bar[st]);
+        }
+    };
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES - 1; ++s)
+            if ((int64_t)blockIdx.x + s * G < nblk) issue((int64_t)blockIdx.x + s * G, s);
+    }
+    unsigned phases = 0;     // bit s: parity of the next completion of stage s
+    int it = 0;
+    for (int64_t blk = blockIdx.x; blk < nblk; blk += G, ++it) {
+        const int st = it % STAGES;
+        const int64_t r0 = row_begin + blk * THREADS, rl = r0 + THREADS < row_end ? r0 + THREADS : row_end, r = r0 + tid;
+        int rs = 0, re = 0;
+        if (r < row_end) { rs = __ldg(a.row_ptr + r); re = __ldg(a.row_ptr + r + 1); }
+        const int b0 = __ldg(a.row_ptr + r0), b1 = __ldg(a.row_ptr + rl);
+        if (tid == 0) {      // the stage read in the previous iteration is free (the barrier at the end of it): refill it
+            const int64_t nxt = blk + (int64_t)(STAGES - 1) * G;
+            if (nxt < nblk) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                issue(nxt, (it + STAGES - 1) % STAGES);
+            }
+        }
+        const int base = b0 & ~3;
+        int end4 = (b1 + 3) & ~3;
+        if (end4 > limit4) end4 = limit4;
+        const int nb = end4 - base, n = b1 - base;
+        if (n > TILE) __trap();                                           // the dispatcher never sends such a matrix here
+        T *val = s_val + st * TILE;
+        int *col = s_col + st * TILE;
+        if (nb > 0) { mbar_wait_bounded(&bar[st], (phases >> st) & 1u); phases ^= 1u << st; }
+        if (end4 < b1) {                                                  // the last entries of the arrays, by hand
+            const int first = nb > 0 ? nb : 0;
+            if (tid < n - first) { col[first + tid] = __ldg(a.col + base + first + tid); val[first + tid] = __ldg(a.val + base + first + tid); }
+            __syncthreads();
+        }
+        bool done = false;
+        if constexpr (TILE == 8 * THREADS) {      // the usual case, two whole groups per thread: eight gathers in flight, then the products
+            const int o1 = tid * 4, o2 = o1 + THREADS * 4;
+            if (o2 + 4 <= n) {
+                const int4 c1 = *reinterpret_cast<const int4 *>(col + o1), c2 = *reinterpret_cast<const int4 *>(col + o2);
+                const T x0 = __ldg(a.x + c1.x), x1 = __ldg(a.x + c1.y), x2 = __ldg(a.x + c1.z), x3 = __ldg(a.x + c1.w);
+                const T x4 = __ldg(a.x + c2.x), x5 = __ldg(a.x + c2.y), x6 = __ldg(a.x + c2.z), x7 = __ldg(a.x + c2.w);
+                val[o1 + 0] = mul_rn(val[o1 + 0], x0); val[o1 + 1] = mul_rn(val[o1 + 1], x1);
+                val[o1 + 2] = mul_rn(val[o1 + 2], x2); val[o1 + 3] = mul_rn(val[o1 + 3], x3);
+                val[o2 + 0] = mul_rn(val[o2 + 0], x4); val[o2 + 1] = mul_rn(val[o2 + 1], x5);
+                val[o2 + 2] = mul_rn(val[o2 + 2], x6); val[o2 + 3] = mul_rn(val[o2 + 3], x7);
+                done = true;
+            }
+        }
+        if (!done)
+#pragma unroll 2
+        for (int o = tid * 4; o < n; o += THREADS * 4) {
+            if (o + 4 <= n) {
+                const int4 c = *reinterpret_cast<const int4 *>(col + o);
+                const T x0 = __ldg(a.x + c.x), x1 = __ldg(a.x + c.y), x2 = __ldg(a.x + c.z), x3 = __ldg(a.x + c.w);
+                val[o + 0] = mul_rn(val[o + 0], x0); val[o + 1] = mul_rn(val[o + 1], x1);
+                val[o + 2] = mul_rn(val[o + 2], x2); val[o + 3] = mul_rn(val[o + 3], x3);
+            } else {
+                for (int t = 0; o + t < n; ++t) val[o + t] = mul_rn(val[o + t], __ldg(a.x + col[o + t]));
+            }
+        }
+        __syncthreads();
+        T sum = T(0);
+        for (int j = rs; j < re; ++j) sum = add_rn(sum, val[j - base]);
+        if (r < row_end) st_stream(a.y + r, sum);
+        __syncthreads();                                                  // the stage is free
+    }
+}
+
 template <typename T, int MODE, int THREADS, int RPT, int TILE, bool PADDED, bool ORDERED = true, bool KEEP = true>
 __global__ void __launch_bounds__(THREADS)
 csr_stream_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
@@ -674,7 +786,13 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
 #define CME213_TRY_CSR(TH, TL) \
                 if (T_ == TH && L_ == TL) { \
                     const int64_t nb = div_up(rows, TH); \
-                    if (K_ == 7) { if constexpr (MODE == MODE_CSR && TL * (sizeof(T) + 4) + 64 <= 48 * 1024) csr_stream_bulk_kernel<T, TH, TL><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end); } \
+                    if (K_ == 9 || K_ == 10) { if constexpr (MODE == MODE_CSR && TH == 128 && TL == 1024) { \
+                        const int64_t nblk = div_up(rows, TH); \
+                        if (K_ == 9) { const size_t sm = 2 * TL * (sizeof(T) + 4) + 32; int per = 1; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, csr_stream_pipe_kernel<T, TH, TL, 2>, TH, sm); \
+                            const int64_t g = std::min<int64_t>(nblk, (int64_t)per * ctx->sm_count); csr_stream_pipe_kernel<T, TH, TL, 2><<<(unsigned)g, TH, sm, st>>>(a, row_begin, row_end, nblk); } \
+                        else { const size_t sm = 3 * TL * (sizeof(T) + 4) + 32; int per = 1; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, csr_stream_pipe_kernel<T, TH, TL, 3>, TH, sm); \
+                            const int64_t g = std::min<int64_t>(nblk, (int64_t)per * ctx->sm_count); csr_stream_pipe_kernel<T, TH, TL, 3><<<(unsigned)g, TH, sm, st>>>(a, row_begin, row_end, nblk); } } } \
+                    else if (K_ == 7) { if constexpr (MODE == MODE_CSR && TL * (sizeof(T) + 4) + 64 <= 48 * 1024) csr_stream_bulk_kernel<T, TH, TL><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end); } \
                     else if (K_ == 2) { if constexpr (MODE == MODE_CSR) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, 2><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); } \
                     else if (K_) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, 1><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); \
                     else csr_stream_lean_kernel<T, MODE, TH, TL, false><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); \
