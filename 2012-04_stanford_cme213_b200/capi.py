@@ -13,6 +13,7 @@ OK = 0
 ERR_INVALID, ERR_CUDA, ERR_ALLOC, ERR_UNSUPPORTED, ERR_TIMEOUT = -1, -2, -3, -4, -5
 SHARD_AUTO, SHARD_HALO, SHARD_GATHER, SHARD_GATHER_SPLIT = 0, 1, 2, 3
 CSR_AUTO, CSR_SCALAR, CSR_VECTOR, CSR_STREAM, CSR_STREAM_PADDED, CSR_STREAM_KEEP, CSR_BINNED, CSR_STREAM_BULK = 0, 1, 2, 3, 4, 5, 6, 7
+CSR_STREAM_PIPE = CSR_STREAM_BULK | (1 << 8)
 CSR_AUTO_ORDERED = 8
 PLAN_ORDERED = 0x100
 FORMAT_CSR, FORMAT_ELL, FORMAT_HYB = 0, 1, 2

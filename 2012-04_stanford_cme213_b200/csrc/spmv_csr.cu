@@ -363,7 +363,8 @@ csr_stream_bulk_kernel(Args<T> a, int64_t row_begin, int64_t row_end) {
 
 // The bulk-copy-fed kernel as a pipeline: a persistent CTA walks its row blocks (block b, b + grid, b + 2 grid ...: the resident
 // CTAs always cover one contiguous window of rows) with STAGES buffers, the bulk copies of block i + STAGES - 1 in flight while
-// block i gathers.  Only for matrices whose 128-row blocks fit one buffer (longest row <= TILE / THREADS: the dispatcher checks).
+// block i gathers.  For matrices whose 128-row blocks fit one buffer (the dispatcher asks for a longest row of 7); a block that
+// does not fit is summed one thread per row straight from global memory (correct, slow).
 __device__ __forceinline__ void mbar_wait_bounded(uint64_t *bar, unsigned parity) {
 #pragma unroll 1
     for (int spin = 0; spin < (1 << 26); ++spin) {
@@ -375,7 +376,7 @@ __device__ __forceinline__ void mbar_wait_bounded(uint64_t *bar, unsigned parity
     __trap();   // a copy that never lands is a bug, not something to wait for
 }
 template <typename T, int THREADS, int TILE, int STAGES>
-__global__ void __launch_bounds__(THREADS, 1024 / THREADS)   // shared memory allows 8 CTAs of 128 threads (two stages): 64 registers each
+__global__ void __launch_bounds__(THREADS, (sizeof(T) == 4 ? 1536 : 1024) / THREADS)   // two stages in shared memory allow 12 (fp32) / 8 (fp64) CTAs of 128 threads: 40 / 64 registers
 csr_stream_pipe_kernel(Args<T> a, int64_t row_begin, int64_t row_end, int64_t nblk) {
     extern __shared__ __align__(16) unsigned char pipe_smem[];
     T *s_val = reinterpret_cast<T *>(pipe_smem);                          // [STAGES][TILE] values, then products in place
@@ -429,9 +430,15 @@ csr_stream_pipe_kernel(Args<T> a, int64_t row_begin, int64_t row_end, int64_t nb
         int end4 = (b1 + 3) & ~3;
         if (end4 > limit4) end4 = limit4;
         const int nb = end4 - base, n = b1 - base;
-        if (n > TILE) __trap();                                           // the dispatcher never sends such a matrix here
         T *val = s_val + st * TILE;
         int *col = s_col + st * TILE;
+        if (n > TILE || nb > TILE) {       // a block that does not fit a stage (issue() skipped it as well): one thread per row, same order
+            T sum = T(0);
+            for (int j = rs; j < re; ++j) sum = add_rn(sum, mul_rn(__ldg(a.val + j), __ldg(a.x + __ldg(a.col + j))));
+            if (r < row_end) st_stream(a.y + r, sum);
+            __syncthreads();               // (keeps the refill at the top of the next iteration behind every thread of this one)
+            continue;
+        }
         if (nb > 0) { mbar_wait_bounded(&bar[st], (phases >> st) & 1u); phases ^= 1u << st; }
         if (end4 < b1) {                                                  // the last entries of the arrays, by hand
             const int first = nb > 0 ? nb : 0;
@@ -573,6 +580,7 @@ struct cme213_csr_plan {
 
 namespace {
 constexpr int PLAN_BLOCK_ROWS = 256;       // = cme213_spmv_csr_block_rows()
+constexpr int PLAN_PIPE_MAX_ROW = 7;       // 128 rows of 7 entries + the 3 entries a 16-byte group may reach back = 899 <= 1024
 constexpr double PLAN_BULK_MEAN = 8.0;     // 128 rows of the bulk kernel's block fill its 1024-entry buffers in one pass
 // Thresholds read from profiles/r02_csr_kernel_sweep.csv (134 M nonzeros per matrix, uniform and banded columns):
 //   rows of 1-2 entries: one thread per row is already coalesced enough and skips the shared-memory round trip (scalar 0.59 ms
@@ -701,11 +709,17 @@ int plan_build(cme213_ctx *ctx, cme213_csr_plan *p, const int32_t *d_row_ptr, cu
     }
     // fp32, short rows: the bulk-copy-fed stream kernel (2-D 5-point grids 512^2 ... 4096^2: 1.12-1.24x the register-fed one;
     // profiles/r02_exp_csr_bulk.txt).  fp64 (C5: 2.61 against 2.52 ms) and longer rows (more than one pass per block) stay.
-    if (p->kernel == CME213_CSR_STREAM && p->elem_bytes == 4 && p->mean <= PLAN_BULK_MEAN) p->kernel = CME213_CSR_STREAM_BULK;
+    // The same as a two-stage pipeline in persistent CTAs when every 128-row block is sure to fit a stage (longest row 7):
+    // 1024^2 14.8 against 15.4 us, 4096^2 0.82 against 0.74-0.78 of the copy peak (profiles/r02_exp_csr_pipe.txt); fp64: 2.88 ms on C5.
+    if (p->kernel == CME213_CSR_STREAM && p->elem_bytes == 4) {
+        if (p->max_len <= PLAN_PIPE_MAX_ROW) p->kernel = CME213_CSR_STREAM_PIPE;
+        else if (p->mean <= PLAN_BULK_MEAN) p->kernel = CME213_CSR_STREAM_BULK;
+    }
     const char *names[] = {"auto", "scalar", "vector", "stream", "stream-padded", "stream-keep", "binned", "stream-bulk", "auto-ordered"};
     const int kind = p->kernel & 0xFF;
     char lanes[24] = "";
     if (kind == CME213_CSR_VECTOR) snprintf(lanes, sizeof(lanes), " (%d lanes)", (p->kernel >> 8) & 0xFF);
+    if (p->kernel == CME213_CSR_STREAM_PIPE) snprintf(lanes, sizeof(lanes), " (pipelined)");
     snprintf(p->text, sizeof(p->text), "%s%s%s: rows %lld, mean row %.2f, longest %d, %s, %.1f%% of the nonzeros in rows >= %d%s", names[kind], lanes,
              ordered_only ? " [order-preserving kernels only]" : "", (long long)rows, p->mean, p->max_len,
              regular ? "all rows equally long" : "irregular rows", 100.0 * p->long_nnz_fraction, PLAN_LONG_ROW,
@@ -786,13 +800,7 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
 #define CME213_TRY_CSR(TH, TL) \
                 if (T_ == TH && L_ == TL) { \
                     const int64_t nb = div_up(rows, TH); \
-                    if (K_ == 9 || K_ == 10) { if constexpr (MODE == MODE_CSR && TH == 128 && TL == 1024) { \
-                        const int64_t nblk = div_up(rows, TH); \
-                        if (K_ == 9) { const size_t sm = 2 * TL * (sizeof(T) + 4) + 32; int per = 1; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, csr_stream_pipe_kernel<T, TH, TL, 2>, TH, sm); \
-                            const int64_t g = std::min<int64_t>(nblk, (int64_t)per * ctx->sm_count); csr_stream_pipe_kernel<T, TH, TL, 2><<<(unsigned)g, TH, sm, st>>>(a, row_begin, row_end, nblk); } \
-                        else { const size_t sm = 3 * TL * (sizeof(T) + 4) + 32; int per = 1; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, csr_stream_pipe_kernel<T, TH, TL, 3>, TH, sm); \
-                            const int64_t g = std::min<int64_t>(nblk, (int64_t)per * ctx->sm_count); csr_stream_pipe_kernel<T, TH, TL, 3><<<(unsigned)g, TH, sm, st>>>(a, row_begin, row_end, nblk); } } } \
-                    else if (K_ == 7) { if constexpr (MODE == MODE_CSR && TL * (sizeof(T) + 4) + 64 <= 48 * 1024) csr_stream_bulk_kernel<T, TH, TL><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end); } \
+                    if (K_ == 7) { if constexpr (MODE == MODE_CSR && TL * (sizeof(T) + 4) + 64 <= 48 * 1024) csr_stream_bulk_kernel<T, TH, TL><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end); } \
                     else if (K_ == 2) { if constexpr (MODE == MODE_CSR) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, 2><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); } \
                     else if (K_) csr_stream_lean_kernel<T, MODE, TH, TL, false, false, 1><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); \
                     else csr_stream_lean_kernel<T, MODE, TH, TL, false><<<(unsigned)nb, TH, 0, st>>>(a, row_begin, row_end, NoSync()); \
@@ -806,6 +814,21 @@ int launch_csr(cme213_ctx *ctx, const Args<T> &a, int64_t row_begin, int64_t row
             }
 #endif
             if constexpr (MODE == MODE_CSR) {
+                if (bulk && lanes == 1) {      // CME213_CSR_STREAM_PIPE: persistent CTAs, two stages
+                    constexpr int PT = 128, PL = 1024;
+                    constexpr size_t smem = 2 * PL * (sizeof(T) + sizeof(int)) + 32;
+                    static int per_sm = 0;         // the same for every device of this build (sm_100a only)
+                    if (per_sm == 0) {
+                        int v = 0;
+                        CME213_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, csr_stream_pipe_kernel<T, PT, PL, 2>, PT, smem));
+                        per_sm = v > 0 ? v : 1;
+                    }
+                    const int64_t nblk = div_up(rows, PT);
+                    const int64_t grid = std::min<int64_t>(nblk, (int64_t)per_sm * ctx->sm_count);
+                    csr_stream_pipe_kernel<T, PT, PL, 2><<<(unsigned)grid, PT, smem, st>>>(a, row_begin, row_end, nblk);
+                    CME213_LAUNCHED(ctx, "csr_stream_pipe_kernel");
+                    return CME213_OK;
+                }
                 if (bulk) {
                     csr_stream_bulk_kernel<T, 128, 1024><<<(unsigned)div_up(rows, 128), 128, 0, st>>>(a, row_begin, row_end);
                     CME213_LAUNCHED(ctx, "csr_stream_bulk_kernel");

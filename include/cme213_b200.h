@@ -56,6 +56,10 @@ extern "C" {
                                   * once.  Same order of summation (bit-identical).  The dispatcher takes it for fp32 matrices with a mean
                                   * row of 8 entries or fewer (5-point grids: 0.63 -> 0.78 of the copy peak at 4096^2, C1 0.49 -> 0.57);
                                   * fp64 stays with CSR_STREAM (C5: 2.61 against 2.52 ms).  Needs 16-byte aligned col / val (else CSR_STREAM). */
+#define CME213_CSR_STREAM_PIPE (CME213_CSR_STREAM_BULK | (1 << 8)) /* the same as a two-stage pipeline in persistent CTAs: the bulk copies of a CTA's next
+                                  * row block are in flight while this one gathers.  Meant for matrices whose 128-row blocks hold at most 1024
+                                  * entries (the dispatcher takes it for fp32 when the longest row has 7 or fewer: C1 0.57, 4096^2 0.82 of the
+                                  * copy peak); a block that holds more is summed one thread per row (correct, slow).  Bit-identical as well. */
 #define CME213_CSR_BINNED 6 /* plans only: 256-row blocks split into a short list (stream kernel) and a long list (vector kernel) */
 
 typedef struct cme213_ctx cme213_ctx;

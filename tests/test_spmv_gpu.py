@@ -31,7 +31,7 @@ def check_tol(got, ptr, col, val, x, extra=1):
 
 
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
-@pytest.mark.parametrize("kernel", [SCALAR, STREAM, AUTO, 7])
+@pytest.mark.parametrize("kernel", [SCALAR, STREAM, AUTO, 7, 7 | (1 << 8)])
 def test_csr_sequential_kernels_bit_exact_on_laplacian(ctx, dtype, kernel):
     # config C1 in miniature: 5-point Laplacian, natural order
     ptr, col, val = g.laplace2d(67, 45, dtype)
@@ -49,6 +49,7 @@ def test_csr_kernels_on_random_matrices(ctx, dtype, rows, cols, mean):
     assert np.array_equal(gpu_csr(ctx, ptr, col, val, x, STREAM), want)
     assert np.array_equal(gpu_csr(ctx, ptr, col, val, x, 4), want)   # CME213_CSR_STREAM_PADDED
     assert np.array_equal(gpu_csr(ctx, ptr, col, val, x, 7), want)   # CME213_CSR_STREAM_BULK (mean 40: several passes per block)
+    assert np.array_equal(gpu_csr(ctx, ptr, col, val, x, 7 | (1 << 8)), want)   # CME213_CSR_STREAM_PIPE (mean 9 / 40: blocks that do not fit a stage)
     assert np.array_equal(gpu_csr(ctx, ptr, col, val, x, AUTO), want)
     for lanes in (2, 4, 8, 16, 32):
         check_tol(gpu_csr(ctx, ptr, col, val, x, VECTOR | (lanes << 8)), ptr, col, val, x)
@@ -83,7 +84,7 @@ def test_csr_stream_rows_longer_than_a_tile(ctx):
     check_tol(gpu_csr(ctx, ptr, col, val, x, VECTOR | (32 << 8)), ptr, col, val, x)
 
 
-@pytest.mark.parametrize("kernel", [SCALAR, STREAM, VECTOR | (8 << 8)])
+@pytest.mark.parametrize("kernel", [SCALAR, STREAM, VECTOR | (8 << 8), 7, 7 | (1 << 8)])
 def test_csr_row_ranges_leave_other_rows_untouched(ctx, kernel):
     # the multi-GPU path launches boundary rows and interior rows separately
     ptr, col, val = g.laplace3d(9, 8, 7)
