@@ -319,7 +319,7 @@ def make_c1(ctx, torch, args):
             b.copy_(a)
     copy_ms = time_steps(torch, cgraph.replay, 20, 3) / 20 / copies
     del cgraph, bufs
-    return dict(step=graph.replay, alg_bytes=alg * copies, flops=2 * nnz.value * copies, kernel="csr_stream_bulk_kernel<float>" if args.csr_kernel in (0, 7, 8) else "csr_stream_lean_kernel<float>",
+    return dict(step=graph.replay, alg_bytes=alg * copies, flops=2 * nnz.value * copies, kernel="csr_stream_pipe_kernel<float>" if args.csr_kernel in (0, 8, 263) else "csr_stream_bulk_kernel<float>" if args.csr_kernel == 7 else "csr_stream_lean_kernel<float>",
                 launches_per_step=copies,
                 meta={"workload": "C1: CSR SpMV fp32, 2-D 5-point Poisson %dx%d" % (n, n), "rows": rows, "nnz": nnz.value,
                       "passes_per_step": copies, "device_copy_of_the_same_bytes_ms_per_launch": copy_ms,
