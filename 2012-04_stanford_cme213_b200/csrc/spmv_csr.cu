@@ -432,14 +432,16 @@ csr_stream_pipe_kernel(Args<T> a, int64_t row_begin, int64_t row_end, int64_t nb
         const int nb = end4 - base, n = b1 - base;
         T *val = s_val + st * TILE;
         int *col = s_col + st * TILE;
-        if (n > TILE || nb > TILE) {       // a block that does not fit a stage (issue() skipped it as well): one thread per row, same order
+        // exactly issue()'s condition: a copy that was started is waited for, whatever happens to the block afterwards (no copy may
+        // still be in flight when the CTA leaves, and the stage's parity has to stay in step)
+        if (nb > 0 && nb <= TILE) { mbar_wait_bounded(&bar[st], (phases >> st) & 1u); phases ^= 1u << st; }
+        if (n > TILE || nb > TILE) {       // a block that does not fit a stage: one thread per row, same order
             T sum = T(0);
             for (int j = rs; j < re; ++j) sum = add_rn(sum, mul_rn(__ldg(a.val + j), __ldg(a.x + __ldg(a.col + j))));
             if (r < row_end) st_stream(a.y + r, sum);
             __syncthreads();               // (keeps the refill at the top of the next iteration behind every thread of this one)
             continue;
         }
-        if (nb > 0) { mbar_wait_bounded(&bar[st], (phases >> st) & 1u); phases ^= 1u << st; }
         if (end4 < b1) {                                                  // the last entries of the arrays, by hand
             const int first = nb > 0 ? nb : 0;
             if (tid < n - first) { col[first + tid] = __ldg(a.col + base + first + tid); val[first + tid] = __ldg(a.val + base + first + tid); }
