@@ -79,3 +79,9 @@ def test_stream_kernels_keep_their_register_budget():
                  "float,0,256,2048,false,false,0", "float,0,256,2048,false,false,1"):
         assert regs[inst] <= 32, (inst, regs[inst])
     assert max(regs.values()) <= 40, regs
+    # the bulk-copy-fed kernels: 16 CTAs of 128 threads (32 registers) / 12 CTAs for the pipelined fp32 one (40)
+    other = {}
+    for m in re.finditer(r"Function properties for void \(anonymous namespace\)::(csr_stream_bulk_kernel|csr_stream_pipe_kernel)<([^>]*)>.*?\n.*?\n.*?Used (\d+) registers", text):
+        other[m.group(1) + "<" + m.group(2).replace(" ", "") + ">"] = int(m.group(3))
+    assert other["csr_stream_bulk_kernel<float,128,1024>"] <= 32 and other["csr_stream_bulk_kernel<double,128,1024>"] <= 32, other
+    assert other["csr_stream_pipe_kernel<float,128,1024,2>"] <= 40, other
