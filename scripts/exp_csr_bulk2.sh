@@ -1,3 +1,5 @@
+# NOTE: K = 8 (1536 resident threads) was removed after the measurement; K = 7 is kernel id CME213_CSR_STREAM_BULK now.  Record of how
+# profiles/r02_exp_csr_bulk.txt was taken.
 # second round: bulk kernel with 1536 resident threads (K = 8: all eight gathers of a thread in flight), and 2-D grids of several sizes
 cd /root/repo 2>/dev/null || cd "$GRAFT_REPO_ROOT"
 out=gpurun_out/r2_exp_csr_bulk2.txt; : > $out

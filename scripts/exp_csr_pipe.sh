@@ -1,3 +1,5 @@
+# NOTE: the K = 9 / 10 hooks were removed when the two-stage kernel became kernel id CME213_CSR_STREAM_PIPE (7 | 1 << 8); the three-stage form
+# lost and was not kept.  Record of how profiles/r02_exp_csr_pipe.txt was taken; scripts/exp_c1_kernels.py times the shipped ids.
 # pipelined persistent bulk-copy-fed stream kernel (tuning build): CME213_CSR_CFG=128,1024,9 (2 stages) / ,10 (3 stages)
 cd /root/repo 2>/dev/null || cd "$GRAFT_REPO_ROOT"
 out=gpurun_out/r2_exp_csr_pipe.txt; : > $out

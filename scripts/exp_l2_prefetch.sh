@@ -1,3 +1,5 @@
+# NOTE: the K = 3..6 variants this script drives were removed after the measurement (no effect; profiles/r02_exp_l2_prefetch_hints.txt,
+# git log -S'LTC128B' finds the commit); kept as the record of how the numbers were taken.
 # C5 (tuning build): x gathers / matrix streams with L2 prefetch-size hints, and the device's L2 fetch granularity
 # CME213_CSR_CFG=128,1024,K: K = 0 plain, 3 gathers .L2::128B, 4 gathers .L2::256B, 5 streams .L2::256B, 6 = 3 + 5
 cd /root/repo 2>/dev/null || cd "$GRAFT_REPO_ROOT"
